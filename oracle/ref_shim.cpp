@@ -1,0 +1,179 @@
+// TEST ORACLE / CPU BASELINE ONLY -- never linked or imported by the product path.
+//
+// Thin extern "C" batch wrapper over the UNMODIFIED reference classes (compiled against the headers where
+// they lie under /root/reference/include; output goes to oracle/_ref/libref_shim.so). It lets tests/ and
+// bench.py's cpu_baseline leg drive the reference's own per-codeword API over a batch:
+//   PolarCode::Decoding::create            (reference src/polarcode/decoding/decoder.cpp:26-52)
+//   Decoder::decode_vector(char*/float*)   (decoder.cpp:154-181)
+//   Encoding::ButterflyFipPacked           (src/polarcode/encoding/butterfly_fip_packed.cpp:45-59)
+//   ErrorDetection::create                 (src/polarcode/errordetection/errordetector.cpp:27-88)
+//   Construction::frozen_bits              (src/polarcode/construction/constructor.cpp:41-63)
+// Threading mirrors pcsim's worker model (src/simulation/simulator.cpp:87-116): one private codec object
+// per std::thread, frames split into contiguous slices.
+#include <polarcode/construction/constructor.h>
+#include <polarcode/decoding/decoder.h>
+#include <polarcode/encoding/butterfly_fip_packed.h>
+#include <polarcode/errordetection/errordetector.h>
+
+#include <chrono>
+#include <cstring>
+#include <string>
+#include <thread>
+#include <vector>
+
+using namespace PolarCode;
+
+static std::vector<unsigned> mkfrozen(const unsigned* f, int nf) { return std::vector<unsigned>(f, f + nf); }
+
+extern "C" {
+
+// returns number of frozen positions written (N-K) or -1
+int ref_frozen_bits(int N, int K, float dsnr, const char* type, unsigned* out)
+{
+    try {
+        auto v = Construction::frozen_bits(N, K, dsnr, std::string(type));
+        for (size_t i = 0; i < v.size(); ++i) out[i] = v[i];
+        return (int)v.size();
+    } catch (...) {
+        return -1;
+    }
+}
+
+// kind: "char" / "float" / "mixed"; crc_bits<0 => keep the factory default (CRC-8, decoder.cpp:85);
+// is_float: llr points to float[B][N] else int8[B][N]. Returns seconds spent inside the decode loops
+// (max over threads), or a negative value on error.
+double ref_decode_batch(int N, int L, const unsigned* frozen, int nf, const char* kind, int crc_bits,
+                        const char* crc_type, int systematic, int is_float, const void* llr, long B,
+                        unsigned char* out, unsigned char* ok, int threads, int repeat)
+{
+    try {
+        const int K = N - nf;
+        const int kb = (K + 7) / 8;
+        if (threads < 1) threads = 1;
+        if (repeat < 1) repeat = 1;
+        std::vector<double> secs(threads, 0.0);
+        std::vector<std::thread> pool;
+        auto fz = mkfrozen(frozen, nf);
+        for (int t = 0; t < threads; ++t) {
+            pool.emplace_back([&, t]() {
+                Decoding::Decoder* dec = Decoding::create(N, L, fz, std::string(kind));
+                ErrorDetection::Detector* det = nullptr;
+                if (crc_bits >= 0) {
+                    det = ErrorDetection::create(crc_bits, std::string(crc_type));
+                    dec->setErrorDetection(det);
+                }
+                dec->setSystematic(systematic != 0);
+                long lo = B * t / threads, hi = B * (t + 1) / threads;
+                std::vector<unsigned char> tmp(kb + 64);
+                auto t0 = std::chrono::high_resolution_clock::now();
+                for (int r = 0; r < repeat; ++r) {
+                    for (long i = lo; i < hi; ++i) {
+                        bool res;
+                        if (is_float)
+                            res = dec->decode_vector(reinterpret_cast<const float*>(llr) + i * N, tmp.data());
+                        else
+                            res = dec->decode_vector(reinterpret_cast<const char*>(llr) + i * N, tmp.data());
+                        memcpy(out + i * kb, tmp.data(), kb);
+                        if (ok) ok[i] = res ? 1 : 0;
+                    }
+                }
+                auto t1 = std::chrono::high_resolution_clock::now();
+                secs[t] = std::chrono::duration<double>(t1 - t0).count();
+                delete dec;
+                delete det;
+            });
+        }
+        for (auto& th : pool) th.join();
+        double mx = 0;
+        for (double s : secs) mx = s > mx ? s : mx;
+        return mx;
+    } catch (...) {
+        return -1.0;
+    }
+}
+
+// info: uint8[B][ceil(K/8)] (a private copy is made per frame because encode() writes the CRC in place,
+// butterfly_fip_packed.cpp:47-49; the copy incl. CRC is returned through info_out when non-null).
+double ref_encode_batch(int N, const unsigned* frozen, int nf, int crc_bits, const char* crc_type,
+                        int systematic, const unsigned char* info, long B, unsigned char* code,
+                        unsigned char* info_out, int threads, int repeat)
+{
+    try {
+        const int K = N - nf;
+        const int kb = (K + 7) / 8;
+        if (threads < 1) threads = 1;
+        if (repeat < 1) repeat = 1;
+        auto fz = mkfrozen(frozen, nf);
+        std::vector<double> secs(threads, 0.0);
+        std::vector<std::thread> pool;
+        for (int t = 0; t < threads; ++t) {
+            pool.emplace_back([&, t]() {
+                Encoding::ButterflyFipPacked enc(N, fz);
+                ErrorDetection::Detector* det = nullptr;
+                if (crc_bits >= 0) {
+                    det = ErrorDetection::create(crc_bits, std::string(crc_type));
+                    enc.setErrorDetection(det);
+                }
+                enc.setSystematic(systematic != 0);
+                long lo = B * t / threads, hi = B * (t + 1) / threads;
+                std::vector<unsigned char> tmp(kb + 64);
+                auto t0 = std::chrono::high_resolution_clock::now();
+                for (int r = 0; r < repeat; ++r) {
+                    for (long i = lo; i < hi; ++i) {
+                        memcpy(tmp.data(), info + i * kb, kb);
+                        enc.encode_vector(tmp.data(), code + i * (N / 8));
+                        if (info_out) memcpy(info_out + i * kb, tmp.data(), kb);
+                    }
+                }
+                auto t1 = std::chrono::high_resolution_clock::now();
+                secs[t] = std::chrono::duration<double>(t1 - t0).count();
+                delete det;
+            });
+        }
+        for (auto& th : pool) th.join();
+        double mx = 0;
+        for (double s : secs) mx = s > mx ? s : mx;
+        return mx;
+    } catch (...) {
+        return -1.0;
+    }
+}
+
+// op: 0 generate (writes CRC into the tail of each row), 1 check (ok[i]), 2 calculate over `bits` bits (val[i])
+int ref_crc_batch(int crc_bits, const char* crc_type, int op, unsigned char* data, int bytes, long bits, long B,
+                  unsigned char* ok, unsigned long long* val)
+{
+    try {
+        ErrorDetection::Detector* det = ErrorDetection::create(crc_bits, std::string(crc_type));
+        for (long i = 0; i < B; ++i) {
+            unsigned char* row = data + i * bytes;
+            if (op == 0)
+                det->generate(row, bytes);
+            else if (op == 1)
+                ok[i] = det->check(row, bytes) ? 1 : 0;
+            else
+                val[i] = det->calculate(row, bits);
+        }
+        delete det;
+        return 0;
+    } catch (...) {
+        return -1;
+    }
+}
+
+// float -> int8 quantiser of the char decoders' input container (src/polarcode/bitcontainer.cpp:468-516)
+int ref_quantize(int N, const float* in, long B, signed char* out)
+{
+    try {
+        CharContainer c(N);
+        for (long i = 0; i < B; ++i) {
+            c.insertLlr(in + i * N);
+            memcpy(out + i * N, c.data(), N);
+        }
+        return 0;
+    } catch (...) {
+        return -1;
+    }
+}
+
+} // extern "C"
