@@ -1,0 +1,139 @@
+/* polar_b200 -- C-ABI of the B200-native batched polar codec (libpolar_b200.so).
+ *
+ * Drop-in boundary for the hot path of ant-uni-bremen/polar-codes: every entry point below is what a
+ * binding of the reference's per-codeword classes would call once the loop over codewords moves onto
+ * the GPU. Reference interface each one replaces (paths relative to the reference tree):
+ *
+ *   pc_frozen_bits          PolarCode::Construction::frozen_bits            include/polarcode/construction/constructor.h:58-62
+ *   pc_code_create          PolarCode::Decoding::create / makeDecoder       src/polarcode/decoding/decoder.cpp:26-87
+ *                           + Encoding::ButterflyFipPacked ctor             include/polarcode/encoding/butterfly_fip_packed.h:25-49
+ *   pc_code_set_crc         Decoder/Encoder::setErrorDetection              decoder.cpp:133-136, src/polarcode/encoding/encoder.cpp
+ *   pc_code_set_systematic  Decoder/Encoder::setSystematic                  decoder.h:118, encoder.h
+ *   pc_decode_batch         Decoder::decode_vector(const char*/float*, void*)   decoder.cpp:154-181   (B codewords per call)
+ *   pc_encode_batch         Encoder::encode_vector(void*, void*)            src/polarcode/encoding/encoder.cpp:79-90
+ *   pc_crc_generate_batch   ErrorDetection::Detector::generate              include/polarcode/errordetection/errordetector.h:57-63
+ *   pc_crc_check_batch      Detector::check                                 errordetector.h:65-70
+ *   pc_crc_calculate        Detector::calculate                             errordetector.h:48
+ *   pc_quantize_batch       CharContainer::insertLlr(const float*)          src/polarcode/bitcontainer.cpp:505-516
+ *   pc_awgn_generate        pcsim SimulationWorker::generateData/encode/modulate/transmit  src/simulation/simulator.cpp:632-672,832-867
+ *   pc_count_errors         SimulationWorker::countErrors                   src/simulation/simulator.cpp:939-965
+ *
+ * Conventions: plain pointers and sizes only; no exceptions cross this boundary (int status, 0 = OK,
+ * message via pc_last_error()). Pointers named d_* are DEVICE pointers on the current CUDA device,
+ * h_* are host pointers. `stream` is a cudaStream_t passed as void* (NULL = default stream).
+ * Bit order is the reference's: code/info bit i lives in byte i/8, bit 7-(i%8) (MSB first).
+ * LLR >= 0 decodes to bit 0. Frames are rows: llr[B][N], info[B][ceil(K/8)], code[B][N/8].
+ * There is no CPU fallback: every compute entry point fails with PC_ERR_CUDA when no GPU is usable. */
+#ifndef POLAR_B200_H
+#define POLAR_B200_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct pc_code pc_code;
+
+/* decoder kinds -- the implementations Decoding::makeDecoder selects (decoder.cpp:54-87) */
+enum {
+    PC_DEC_FASTSSC_I8 = 0, /* 'char',  L == 1 : FastSscFipChar  */
+    PC_DEC_FASTSSC_F32 = 1, /* 'float', L == 1 : FastSscAvxFloat */
+    PC_DEC_SCL_I8 = 2,     /* 'char',  L  > 1 : SclFipChar      */
+    PC_DEC_SCL_F32 = 3,    /* 'float', L  > 1 : SclAvxFloat     */
+    PC_DEC_ADAPTIVE_F32 = 4 /* 'mixed', L  > 1 : AdaptiveFloat   */
+};
+
+/* error detectors -- ErrorDetection::create(size, type) (errordetector.cpp:27-88) */
+enum {
+    PC_CRC_NONE = 0,  /* Dummy: check() is always true */
+    PC_CRC_6NR = 6,   /* poly 0x21,     init 0, stored in 1 byte  */
+    PC_CRC_8 = 8,     /* poly 0x07,     init 0                    */
+    PC_CRC_11NR = 11, /* poly 0x621,    init 0, stored in 2 bytes */
+    PC_CRC_16 = 16,   /* CCITT-FALSE 0x1021 init 0xFFFF           */
+    PC_CRC_16NR = 17, /* XMODEM      0x1021 init 0 ("nr" type)    */
+    PC_CRC_24NRC = 24, /* poly 0xB2B117, init 0                   */
+    PC_CRC_32C = 32   /* CRC-32C over little-endian words         */
+};
+
+enum {
+    PC_OK = 0,
+    PC_ERR_ARG = 1,    /* invalid argument (std::invalid_argument / std::logic_error in the reference) */
+    PC_ERR_CUDA = 2,   /* CUDA runtime failure or no device */
+    PC_ERR_UNSUPPORTED = 3
+};
+
+const char* pc_last_error(void);
+const char* pc_version(void);
+
+/* host-only: frozen set for (N, K) by "BB" (Bhattacharyya, design SNR in dB), "BE" (beta expansion) or
+ * "5G"; writes N-K sorted indices to out (capacity N), returns N-K or a negative status */
+int pc_frozen_bits(int N, int K, float design_snr_db, const char* type, unsigned* out);
+
+/* error detector id from the reference's (size, type) pair; negative on the sizes create() rejects */
+int pc_crc_kind(unsigned size, const char* type);
+int pc_crc_bytes(int crc_kind); /* bytes the detector occupies at the tail of the info block */
+
+/* Builds the code object: host-side tree compilation (node program, info-bit runs, masks) and upload to
+ * the current device. kind is one of PC_DEC_*; L is the list size (1 for Fast-SSC). Defaults mirror
+ * the reference: systematic = true, detector = CRC-8 (makeDecoder installs one, decoder.cpp:85). */
+pc_code* pc_code_create(int N, const unsigned* frozen, int n_frozen, int kind, int L);
+void pc_code_destroy(pc_code* c);
+int pc_code_set_crc(pc_code* c, int crc_kind);
+int pc_code_set_systematic(pc_code* c, int systematic);
+int pc_code_N(const pc_code* c);
+int pc_code_K(const pc_code* c);
+int pc_code_info_bytes(const pc_code* c); /* ceil(K/8) */
+/* introspection for tests and reports: number of node-program instructions, frames per CTA, smem bytes */
+int pc_code_program_length(const pc_code* c);
+int pc_code_program(const pc_code* c, uint32_t* out, int capacity);
+int pc_code_launch_info(const pc_code* c, int* threads_per_cta, int* smem_bytes, int* frames_per_cta);
+
+/* Decode B codewords. llr_is_float selects the float32 overload of decode_vector (quantised on device
+ * with the reference's quantiser for the int8 kinds), otherwise int8. d_ok (may be NULL) receives the
+ * detector verdict per frame (decode()'s return value). Asynchronous on `stream`. */
+int pc_decode_batch(pc_code* c, const void* d_llr, int llr_is_float, uint8_t* d_info, uint8_t* d_ok, size_t B,
+                    void* stream);
+/* Same call with HOST buffers: pinned staging, H2D, decode, D2H, synchronised on return. This is the
+ * path the per-codeword decode_vector() wrappers use (B = 1) and bench.py's e2e leg. */
+int pc_decode_batch_host(pc_code* c, const void* h_llr, int llr_is_float, uint8_t* h_info, uint8_t* h_ok,
+                         size_t B);
+
+/* Encode B info blocks of ceil(K/8) bytes. The detector's check bytes are generated into the tail of a
+ * device-side copy of each block (the reference writes them into the caller's buffer,
+ * butterfly_fip_packed.cpp:47-49); d_info_crc (may be NULL) receives that copy. */
+int pc_encode_batch(pc_code* c, const uint8_t* d_info, uint8_t* d_code, uint8_t* d_info_crc, size_t B, void* stream);
+int pc_encode_batch_host(pc_code* c, const uint8_t* h_info, uint8_t* h_code, uint8_t* h_info_crc, size_t B);
+
+/* Detector batch operations on rows of `bytes` bytes (device pointers) */
+int pc_crc_generate_batch(int crc_kind, uint8_t* d_data, int bytes, size_t B, void* stream);
+int pc_crc_check_batch(int crc_kind, const uint8_t* d_data, int bytes, uint8_t* d_ok, size_t B, void* stream);
+/* host-only single call: Detector::calculate(data, bits) */
+uint64_t pc_crc_calculate(int crc_kind, const uint8_t* h_data, size_t bits);
+
+/* float32 -> int8 LLR with the reference quantiser for block length N (rounding mode depends on N) */
+int pc_quantize_batch(int N, const float* d_in, int8_t* d_out, size_t B, void* stream);
+
+/* Device-side channel simulation for BLER sweeps (Philox4x32-10, counter = first_frame + row index):
+ * random info bits -> detector generate -> encode -> BPSK (0 -> +1) -> AWGN at Eb/N0 -> LLR.
+ * llr_is_float == 0: int8 LLR = quantise(amplification * y); == 1: float LLR = amplification * y.
+ * d_info_out[B][ceil(K/8)] receives the transmitted info blocks (incl. check bytes). */
+int pc_awgn_generate(pc_code* c, uint64_t seed, uint64_t first_frame, float ebn0_db, float amplification,
+                     int llr_is_float, void* d_llr_out, uint8_t* d_info_out, size_t B, void* stream);
+/* counts[0] += frames, [1] += frame errors, [2] += bit errors over the K info bits, [3] += frames
+ * whose detector verdict was false. d_counts is uint64[4] on the device. */
+int pc_count_errors(const uint8_t* d_info_ref, const uint8_t* d_info_dec, const uint8_t* d_ok, int K, size_t B,
+                    unsigned long long* d_counts, void* stream);
+
+/* device memory helpers so that non-CUDA hosts (ctypes, cgo, JNI) can drive the library alone */
+void* pc_device_alloc(size_t bytes);
+void pc_device_free(void* d);
+int pc_memcpy_h2d(void* d, const void* h, size_t bytes);
+int pc_memcpy_d2h(void* h, const void* d, size_t bytes);
+int pc_device_synchronize(void);
+/* number of kernel launches issued by this library since load (bench.py's gpu_launches) */
+unsigned long long pc_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,502 @@
+// Fast-SSC int8 decoder core: one THREAD decodes one codeword by interpreting the node program of
+// pc_program.h. Four int8 LLRs per 32-bit word (pc_swar.h); hard decisions are one bit per element.
+//
+// On-chip layout (shared memory on the device): an arena of 16-byte chunks, chunk-major across the
+// threads of the CTA -- chunk c of thread t lives at word (c*T + t)*4 -- so every access of a warp is a
+// conflict-free LDS.128/STS.128. Per thread:
+//   chunk 0            LLR stages 1..3   (word 0: n=2, word 1: n=4, words 2-3: n=8)
+//   chunks [2^(s-4), 2^(s-3))   LLR stage s >= 4 (n = 2^s int8 values), up to s = S-1
+//                      (s = S too when the root is staged on chip, FastSscProgram::staged_root)
+//   chunks bbase..     hard decisions, 32 per word, element i -> word i/32 bit i%32
+// The root LLRs (the channel row) are read straight from HBM by the two top-level ops.
+//
+// Semantics follow reference src/polarcode/decoding/fastssc_fip_char.cpp (node decode functions
+// :202-492) and include/polarcode/decoding/fip_char.h; the hard decision of a node is the MSB of the
+// reference's "bit byte", which is all any consumer reads (g's blendv, CombineBits, info extraction).
+//
+// __host__ __device__ throughout: tests/host_emul.cpp runs this exact code for one emulated thread.
+#ifndef PC_FASTSSC_I8_CORE_H
+#define PC_FASTSSC_I8_CORE_H
+#include "pc_program.h"
+#include "pc_swar.h"
+
+namespace pc {
+
+struct alignas(16) u4 {
+    uint32_t x, y, z, w;
+};
+
+// per-thread view of the chunk-major arena
+struct TMem {
+    uint32_t* base; // word 0 of this thread's chunk 0
+    int cs;         // chunk stride in words (4 * threads per CTA)
+    PC_HD u4 ld4(int chunk) const { return *reinterpret_cast<const u4*>(base + chunk * cs); }
+    PC_HD void st4(int chunk, const u4& v) const { *reinterpret_cast<u4*>(base + chunk * cs) = v; }
+    PC_HD uint32_t ld(int chunk, int sub) const { return base[chunk * cs + sub]; }
+    PC_HD void st(int chunk, int sub, uint32_t v) const { base[chunk * cs + sub] = v; }
+};
+
+// LLR source of a node with >= 32 elements: either the on-chip stage or the channel row in HBM
+struct SmemSrc {
+    TMem m;
+    int cb;
+    PC_HD u4 ld4(int i) const { return m.ld4(cb + i); }
+};
+struct GlobalSrc {
+    const u4* row;
+    PC_HD u4 ld4(int i) const
+    {
+#ifdef __CUDA_ARCH__
+        uint4 v = __ldg(reinterpret_cast<const uint4*>(row) + i);
+        return u4{ v.x, v.y, v.z, v.w };
+#else
+        return row[i];
+#endif
+    }
+};
+
+struct Ctx {
+    TMem m;
+    int S;        // log2 N
+    int bbase;    // first chunk of the hard-decision words
+    uint32_t cur; // hard decisions of the 32-element block being decoded (nodes with n <= 32)
+    PC_HD uint32_t bld(int word) const { return m.ld(bbase + (word >> 2), word & 3); }
+    PC_HD void bst(int word, uint32_t v) const { m.st(bbase + (word >> 2), word & 3, v); }
+};
+
+PC_HD int stage_chunk(int s) { return 1 << (s - 4); } // s >= 4
+PC_HD uint32_t lowmask(int nbits) { return nbits >= 32 ? 0xFFFFFFFFu : ((1u << nbits) - 1u); }
+
+PC_HD u4 f4(const u4& a, const u4& b) { return u4{ sw_f(a.x, b.x), sw_f(a.y, b.y), sw_f(a.z, b.z), sw_f(a.w, b.w) }; }
+PC_HD u4 adds4(const u4& a, const u4& b)
+{
+    return u4{ sw_adds(a.x, b.x), sw_adds(a.y, b.y), sw_adds(a.z, b.z), sw_adds(a.w, b.w) };
+}
+// 16 hard decisions select add/sub per lane
+PC_HD u4 g4(const u4& a, const u4& b, uint32_t bits16)
+{
+    return u4{ sw_g(a.x, b.x, sw_expand4(bits16)), sw_g(a.y, b.y, sw_expand4(bits16 >> 4)),
+               sw_g(a.z, b.z, sw_expand4(bits16 >> 8)), sw_g(a.w, b.w, sw_expand4(bits16 >> 12)) };
+}
+PC_HD uint32_t movemask16(const u4& v)
+{
+    return sw_movemask(v.x) | (sw_movemask(v.y) << 4) | (sw_movemask(v.z) << 8) | (sw_movemask(v.w) << 12);
+}
+
+// ------------------------------------------------------------------ internal nodes -----------------
+
+// RateRNode / ShortRateRNode left step (fastssc_fip_char.cpp:401-404,414-417): child = f(lo, hi)
+template <class Src>
+PC_HD void op_f_big(const Ctx& c, const Src& src, int s)
+{
+    const int half = 1 << (s - 5), dst = half; // stage s-1 starts at chunk 2^(s-5)
+#pragma unroll 2
+    for (int i = 0; i < half; ++i) c.m.st4(dst + i, f4(src.ld4(i), src.ld4(half + i)));
+}
+PC_HD void op_f_small(const Ctx& c, int s)
+{
+    if (s == 4) {
+        u4 v = c.m.ld4(1);
+        c.m.st(0, 2, sw_f(v.x, v.z));
+        c.m.st(0, 3, sw_f(v.y, v.w));
+    } else if (s == 3) {
+        c.m.st(0, 1, sw_f(c.m.ld(0, 2), c.m.ld(0, 3)));
+    } else { // s == 2
+        uint32_t w = c.m.ld(0, 1);
+        c.m.st(0, 0, sw_f(w, w >> 16));
+    }
+}
+
+// ZeroRNode (fastssc_fip_char.cpp:476-483): left child is rate-0, child llr = sat(lo + hi)
+template <class Src>
+PC_HD void op_g0_big(const Ctx& c, const Src& src, int s)
+{
+    const int half = 1 << (s - 5), dst = half;
+#pragma unroll 2
+    for (int i = 0; i < half; ++i) c.m.st4(dst + i, adds4(src.ld4(i), src.ld4(half + i)));
+}
+PC_HD void op_g0_small(const Ctx& c, int s)
+{
+    if (s == 4) {
+        u4 v = c.m.ld4(1);
+        c.m.st(0, 2, sw_adds(v.x, v.z));
+        c.m.st(0, 3, sw_adds(v.y, v.w));
+    } else if (s == 3) {
+        c.m.st(0, 1, sw_adds(c.m.ld(0, 2), c.m.ld(0, 3)));
+    } else {
+        uint32_t w = c.m.ld(0, 1);
+        c.m.st(0, 0, sw_adds(w, w >> 16));
+    }
+}
+
+// right step (fastssc_fip_char.cpp:406-408): child = g(lo, hi, left hard decisions)
+template <class Src>
+PC_HD void op_g_big(const Ctx& c, const Src& src, int s, int off)
+{
+    const int half = 1 << (s - 5), dst = half;
+    if (s == 5) {
+        c.m.st4(dst, g4(src.ld4(0), src.ld4(1), c.cur & 0xFFFFu));
+        return;
+    }
+    const int wo = off >> 5;
+    for (int j = 0; j < (half >> 1); ++j) {
+        uint32_t bl = c.bld(wo + j);
+        c.m.st4(dst + 2 * j, g4(src.ld4(2 * j), src.ld4(half + 2 * j), bl & 0xFFFFu));
+        c.m.st4(dst + 2 * j + 1, g4(src.ld4(2 * j + 1), src.ld4(half + 2 * j + 1), bl >> 16));
+    }
+}
+PC_HD void op_g_small(const Ctx& c, int s, int off)
+{
+    const uint32_t lb = c.cur >> (off & 31);
+    if (s == 4) {
+        u4 v = c.m.ld4(1);
+        c.m.st(0, 2, sw_g(v.x, v.z, sw_expand4(lb)));
+        c.m.st(0, 3, sw_g(v.y, v.w, sw_expand4(lb >> 4)));
+    } else if (s == 3) {
+        c.m.st(0, 1, sw_g(c.m.ld(0, 2), c.m.ld(0, 3), sw_expand4(lb)));
+    } else {
+        uint32_t w = c.m.ld(0, 1);
+        c.m.st(0, 0, sw_g(w, w >> 16, sw_expand4(lb & 3u)));
+    }
+}
+
+// ROneNode (fastssc_fip_char.cpp:427-474): the right child is rate-1, so its hard decision is the sign
+// of g and the combine is fused: bits = [left ^ right, right]
+template <class Src>
+PC_HD void op_g1_big(Ctx& c, const Src& src, int s, int off)
+{
+    const int half = 1 << (s - 5);
+    if (s == 5) {
+        uint32_t left = c.cur & 0xFFFFu;
+        uint32_t r = movemask16(g4(src.ld4(0), src.ld4(1), left));
+        c.cur = (left ^ r) | (r << 16);
+        return;
+    }
+    const int wo = off >> 5, hw = half >> 1;
+    for (int j = 0; j < hw; ++j) {
+        uint32_t bl = c.bld(wo + j);
+        uint32_t r = movemask16(g4(src.ld4(2 * j), src.ld4(half + 2 * j), bl & 0xFFFFu));
+        r |= movemask16(g4(src.ld4(2 * j + 1), src.ld4(half + 2 * j + 1), bl >> 16)) << 16;
+        c.bst(wo + hw + j, r);
+        c.bst(wo + j, bl ^ r);
+    }
+}
+PC_HD void op_g1_small(Ctx& c, int s, int off)
+{
+    const int pos = off & 31, h = 1 << (s - 1);
+    const uint32_t lb = c.cur >> pos;
+    uint32_t r;
+    if (s == 4) {
+        u4 v = c.m.ld4(1);
+        r = sw_movemask(sw_g(v.x, v.z, sw_expand4(lb))) | (sw_movemask(sw_g(v.y, v.w, sw_expand4(lb >> 4))) << 4);
+    } else if (s == 3) {
+        r = sw_movemask(sw_g(c.m.ld(0, 2), c.m.ld(0, 3), sw_expand4(lb)));
+    } else {
+        uint32_t w = c.m.ld(0, 1);
+        r = sw_movemask(sw_g(w, w >> 16, sw_expand4(lb & 3u))) & 3u;
+    }
+    c.cur ^= r << pos;       // left ^= right
+    c.cur |= r << (pos + h); // right (those positions were still zero)
+}
+
+// CombineInPlace / CombineBitsShort (fip_char.h:164-207) on one bit per element
+PC_HD void op_comb(Ctx& c, int s, int off, bool zero_left)
+{
+    if (s >= 6) {
+        const int wo = off >> 5, hw = 1 << (s - 6);
+        for (int j = 0; j < hw; ++j) {
+            uint32_t r = c.bld(wo + hw + j);
+            c.bst(wo + j, zero_left ? r : (c.bld(wo + j) ^ r));
+        }
+    } else {
+        const int pos = off & 31, h = 1 << (s - 1);
+        uint32_t r = (c.cur >> (pos + h)) & lowmask(h);
+        c.cur ^= r << pos; // left bits are zero when zero_left, so xor == copy
+    }
+}
+
+// ------------------------------------------------------------------ leaves --------------------------
+
+// LLRs of a node with n = 2^S <= 32 elements into x[0 .. max(1, n/4)); unused high bytes zeroed for n = 2
+template <int S>
+PC_HD void load_small(const Ctx& c, uint32_t (&x)[8])
+{
+    if (S == 5) {
+        u4 a = c.m.ld4(2), b = c.m.ld4(3);
+        x[0] = a.x; x[1] = a.y; x[2] = a.z; x[3] = a.w;
+        x[4] = b.x; x[5] = b.y; x[6] = b.z; x[7] = b.w;
+    } else if (S == 4) {
+        u4 a = c.m.ld4(1);
+        x[0] = a.x; x[1] = a.y; x[2] = a.z; x[3] = a.w;
+    } else if (S == 3) {
+        x[0] = c.m.ld(0, 2);
+        x[1] = c.m.ld(0, 3);
+    } else if (S == 2) {
+        x[0] = c.m.ld(0, 1);
+    } else {
+        x[0] = c.m.ld(0, 0) & 0xFFFFu;
+    }
+}
+// x = sat(lo + hi) of a node with n = 2^S <= 32 elements: n/2 lanes in x[0 .. max(1, n/8))
+template <int S>
+PC_HD void load_small_sum(const Ctx& c, uint32_t (&x)[8])
+{
+    if (S == 5) {
+        u4 r = adds4(c.m.ld4(2), c.m.ld4(3));
+        x[0] = r.x; x[1] = r.y; x[2] = r.z; x[3] = r.w;
+    } else if (S == 4) {
+        u4 a = c.m.ld4(1);
+        x[0] = sw_adds(a.x, a.z);
+        x[1] = sw_adds(a.y, a.w);
+    } else if (S == 3) {
+        x[0] = sw_adds(c.m.ld(0, 2), c.m.ld(0, 3));
+    } else { // S == 2: two lanes
+        uint32_t w = c.m.ld(0, 1);
+        x[0] = sw_adds(w, w >> 16) & 0xFFFFu;
+    }
+}
+
+// reduce_adds_epi8 (avxconvenience.h:92-101) over NW words = 4*NW lanes, zero lanes above: the pairing
+// (i,i+16) (i,i+8) (i,i+4) (i,i+2) (0,1) is normative because saturation is not associative.
+// Returns the word after the stride-4 level (lanes 0..3 live); callers finish with sw_hreduce2/1.
+template <int NW>
+PC_HD uint32_t reduce_words(uint32_t (&x)[8])
+{
+    if (NW == 8) {
+        x[0] = sw_adds(x[0], x[4]); x[1] = sw_adds(x[1], x[5]);
+        x[2] = sw_adds(x[2], x[6]); x[3] = sw_adds(x[3], x[7]);
+    }
+    if (NW >= 4) {
+        x[0] = sw_adds(x[0], x[2]);
+        x[1] = sw_adds(x[1], x[3]);
+    }
+    if (NW >= 2) x[0] = sw_adds(x[0], x[1]);
+    return x[0];
+}
+
+// per-lane saturating accumulation of the n/32 vectors of a long node, in order
+// (RepetitionDecoder::decode fastssc_fip_char.cpp:225-236)
+PC_HD void accumulate_vectors(const Ctx& c, int s, uint32_t (&acc)[8])
+{
+    const int cb = stage_chunk(s), nv = 1 << (s - 5);
+    u4 a = c.m.ld4(cb), b = c.m.ld4(cb + 1);
+    acc[0] = a.x; acc[1] = a.y; acc[2] = a.z; acc[3] = a.w;
+    acc[4] = b.x; acc[5] = b.y; acc[6] = b.z; acc[7] = b.w; // sat(0 + x) == x
+    for (int v = 1; v < nv; ++v) {
+        a = c.m.ld4(cb + 2 * v);
+        b = c.m.ld4(cb + 2 * v + 1);
+        acc[0] = sw_adds(acc[0], a.x); acc[1] = sw_adds(acc[1], a.y);
+        acc[2] = sw_adds(acc[2], a.z); acc[3] = sw_adds(acc[3], a.w);
+        acc[4] = sw_adds(acc[4], b.x); acc[5] = sw_adds(acc[5], b.y);
+        acc[6] = sw_adds(acc[6], b.z); acc[7] = sw_adds(acc[7], b.w);
+    }
+}
+
+PC_HD void store_block_bits(Ctx& c, int s, int off, uint32_t word)
+{ // same 32-bit pattern for every word of a node with n >= 64
+    const int wo = off >> 5, nw = 1 << (s - 5);
+    for (int j = 0; j < nw; ++j) c.bst(wo + j, word);
+}
+
+// RepetitionDecoder / ShortRepetitionDecoder (fastssc_fip_char.cpp:225-240,265-272)
+template <int S>
+PC_HD void leaf_rep_small(Ctx& c, int off)
+{
+    uint32_t x[8];
+    load_small<S>(c, x);
+    uint32_t t = reduce_words<(S >= 2 ? (1 << (S - 2)) : 1)>(x);
+    t = sw_hreduce1(sw_hreduce2(t));
+    if (sw_byte0_negative(t)) c.cur |= lowmask(1 << S) << (off & 31);
+}
+PC_HD void leaf_rep_big(Ctx& c, int s, int off)
+{
+    uint32_t acc[8];
+    accumulate_vectors(c, s, acc);
+    uint32_t t = sw_hreduce1(sw_hreduce2(reduce_words<8>(acc)));
+    store_block_bits(c, s, off, sw_byte0_negative(t) ? 0xFFFFFFFFu : 0u);
+}
+
+// DoubleRepetitionDecoder (fastssc_fip_char.cpp:249-263), n >= 32: half_reduce_adds_epi8 stops at stride 2,
+// even elements take the sign of the even-lane sum, odd elements of the odd-lane sum
+PC_HD void leaf_drep(Ctx& c, int s, int off)
+{
+    uint32_t acc[8];
+    accumulate_vectors(c, s, acc);
+    uint32_t t = sw_hreduce2(reduce_words<8>(acc));
+    uint32_t word = (((t >> 7) & 1u) ? 0x55555555u : 0u) | (((t >> 15) & 1u) ? 0xAAAAAAAAu : 0u);
+    if (s == 5)
+        c.cur = word;
+    else
+        store_block_bits(c, s, off, word);
+}
+
+// RateOneDecoder (fastssc_fip_char.cpp:210-215): hard decision = sign (LLR 0 -> bit 0)
+template <int S>
+PC_HD void leaf_r1_small(Ctx& c, int off)
+{
+    uint32_t x[8];
+    load_small<S>(c, x);
+    constexpr int NW = S >= 2 ? (1 << (S - 2)) : 1;
+    uint32_t bits = 0;
+#pragma unroll
+    for (int w = 0; w < NW; ++w) bits |= sw_movemask(x[w]) << (4 * w);
+    c.cur |= (bits & lowmask(1 << S)) << (off & 31);
+}
+PC_HD void leaf_r1_big(Ctx& c, int s, int off)
+{
+    const int cb = stage_chunk(s), wo = off >> 5, nw = 1 << (s - 5);
+    for (int j = 0; j < nw; ++j)
+        c.bst(wo + j, movemask16(c.m.ld4(cb + 2 * j)) | (movemask16(c.m.ld4(cb + 2 * j + 1)) << 16));
+}
+
+// minpos_epu8 (src/polarcode/avxconvenience.cpp:13-56) restated on keys: value*32 + lane in 16-bit
+// fields, so an unsigned 16-bit minimum returns the FIRST lane holding the smallest |LLR|.
+PC_HD uint32_t minu16x2(uint32_t a, uint32_t b)
+{
+#ifdef __CUDA_ARCH__
+    return __vminu2(a, b);
+#else
+    uint32_t lo = (a & 0xFFFFu) < (b & 0xFFFFu) ? (a & 0xFFFFu) : (b & 0xFFFFu);
+    uint32_t hi = (a >> 16) < (b >> 16) ? (a >> 16) : (b >> 16);
+    return lo | (hi << 16);
+#endif
+}
+// folds word w (lanes 4w..4w+3) of |LLR| bytes into the running key minimum
+PC_HD uint32_t minkey_word(uint32_t kmin, uint32_t absw, int w)
+{
+    const uint32_t ce = (uint32_t)(4 * w) | ((uint32_t)(4 * w + 2) << 16);
+    const uint32_t co = (uint32_t)(4 * w + 1) | ((uint32_t)(4 * w + 3) << 16);
+    kmin = minu16x2(kmin, ((absw << 5) & 0x1FE01FE0u) | ce);
+    kmin = minu16x2(kmin, ((absw >> 3) & 0x1FE01FE0u) | co);
+    return kmin;
+}
+PC_HD uint32_t minkey_finish(uint32_t kmin)
+{
+    uint32_t lo = kmin & 0xFFFFu, hi = kmin >> 16;
+    return lo < hi ? lo : hi; // (min |LLR|) * 32 + first lane
+}
+PC_HD uint32_t parity_of_msbs(uint32_t p)
+{
+    p ^= p >> 16;
+    p ^= p >> 8;
+    return (p >> 7) & 1u;
+}
+
+// ShortSpcDecoder (fastssc_fip_char.cpp:305-319) on NW words of real lanes (pad lanes hold 127 in the
+// reference: never the unique minimum, never change the parity). Returns the hard decisions.
+// The flip is a two's complement negate of the stored byte (:316), so 0 and -128 keep their sign.
+template <int NW>
+PC_HD uint32_t spc_short_bits(const uint32_t (&x)[8])
+{
+    uint32_t bits = 0, par = 0, kmin = 0xFFFFFFFFu;
+#pragma unroll
+    for (int w = 0; w < NW; ++w) {
+        bits |= sw_movemask(x[w]) << (4 * w);
+        par ^= x[w];
+        kmin = minkey_word(kmin, sw_abs(x[w]), w);
+    }
+    uint32_t k = minkey_finish(kmin), m = k >> 5, idx = k & 31u;
+    uint32_t flip = parity_of_msbs(par) & (m != 0u) & (m != 128u);
+    return bits ^ (flip << idx);
+}
+template <int S>
+PC_HD void leaf_spc_small(Ctx& c, int off)
+{
+    uint32_t x[8];
+    load_small<S>(c, x);
+    c.cur |= spc_short_bits<(1 << (S - 2))>(x) << (off & 31);
+}
+
+// SpcDecoder (n > 32, fastssc_fip_char.cpp:274-303) and ZeroSpcDecoder (n >= 64, :321-359) share the
+// cross-vector search: minAbs starts at 127, a 32-lane vector is only searched while minAbs > 0 and only
+// a strictly smaller per-vector minimum (signed-char compare) moves minIdx; the flip is a negate.
+struct SpcSearch {
+    uint32_t par = 0;
+    int minAbs = 127, minIdx = 0;
+    uint32_t flipOk = 0;
+    PC_HD void vector(const uint32_t (&x)[8], int v)
+    {
+        uint32_t kmin = 0xFFFFFFFFu;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) {
+            par ^= x[w];
+            kmin = minkey_word(kmin, sw_abs(x[w]), w);
+        }
+        if (v == 0) { // minIdx stays 0 when no vector has a minimum below 127
+            uint32_t b0 = x[0] & 0xFFu;
+            flipOk = (b0 != 0u) & (b0 != 0x80u);
+        }
+        uint32_t k = minkey_finish(kmin), m = k >> 5;
+        int testAbs = m == 128u ? -128 : (int)m; // value is returned through a char* (avxconvenience.cpp:51)
+        if (minAbs > 0 && testAbs < minAbs) {
+            minAbs = testAbs;
+            minIdx = (int)(k & 31u) + 32 * v;
+            flipOk = (m != 0u) & (m != 128u);
+        }
+    }
+    PC_HD bool flips() const { return (parity_of_msbs(par) & flipOk) != 0u; }
+};
+
+PC_HD void leaf_spc_big(Ctx& c, int s, int off)
+{
+    const int cb = stage_chunk(s), wo = off >> 5, nv = 1 << (s - 5);
+    SpcSearch q;
+    for (int v = 0; v < nv; ++v) {
+        u4 a = c.m.ld4(cb + 2 * v), b = c.m.ld4(cb + 2 * v + 1);
+        uint32_t x[8] = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w };
+        c.bst(wo + v, movemask16(a) | (movemask16(b) << 16));
+        q.vector(x, v);
+    }
+    if (q.flips()) {
+        int w = wo + (q.minIdx >> 5);
+        c.bst(w, c.bld(w) ^ (1u << (q.minIdx & 31)));
+    }
+}
+
+// ShortZeroOneDecoder (fastssc_fip_char.cpp:390-399): x = sat(lo + hi), bits = [x, x]
+template <int S>
+PC_HD void leaf_s01(Ctx& c, int off)
+{
+    uint32_t x[8];
+    load_small_sum<S>(c, x);
+    constexpr int H = 1 << (S - 1);
+    constexpr int NW = H >= 4 ? H / 4 : 1;
+    uint32_t bits = 0;
+#pragma unroll
+    for (int w = 0; w < NW; ++w) bits |= sw_movemask(x[w]) << (4 * w);
+    bits &= lowmask(H);
+    c.cur |= (bits | (bits << H)) << (off & 31);
+}
+
+// ShortZeroSpcDecoder (fastssc_fip_char.cpp:361-388), 8 <= n <= 32
+template <int S>
+PC_HD void leaf_0spc_small(Ctx& c, int off)
+{
+    uint32_t x[8];
+    load_small_sum<S>(c, x);
+    constexpr int H = 1 << (S - 1);
+    uint32_t bits = spc_short_bits<H / 4>(x);
+    c.cur |= (bits | (bits << H)) << (off & 31);
+}
+// ZeroSpcDecoder (fastssc_fip_char.cpp:321-359), n >= 64
+template <class Src>
+PC_HD void leaf_0spc_big(Ctx& c, const Src& src, int s, int off)
+{
+    const int half = 1 << (s - 5), wo = off >> 5, nv = half >> 1; // n/2 elements = nv vectors of 32
+    SpcSearch q;
+    for (int v = 0; v < nv; ++v) {
+        u4 a = adds4(src.ld4(2 * v), src.ld4(half + 2 * v));
+        u4 b = adds4(src.ld4(2 * v + 1), src.ld4(half + 2 * v + 1));
+        uint32_t x[8] = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w };
+        uint32_t bits = movemask16(a) | (movemask16(b) << 16);
+        c.bst(wo + v, bits);
+        c.bst(wo + nv + v, bits);
+        q.vector(x, v);
+    }
+    if (q.flips()) {
+        int w = wo + (q.minIdx >> 5);
+        uint32_t nb = c.bld(w) ^ (1u << (q.minIdx & 31));
+        c.bst(w, nb);
+        c.bst(w + nv, nb);
+    }
+}

@@ -1,0 +1,139 @@
+#include "pc_program.h"
+
+#include <algorithm>
+
+namespace pc {
+
+namespace {
+
+constexpr int kV = 32; // lanes of the reference's fipv register (include/polarcode/avxconvenience.h:52-54)
+
+struct Builder {
+    FastSscProgram& p;
+    int blockS; // nodes of this size own the register-held block of hard decisions
+
+    // frozen: sorted indices relative to the node; mirrors splitFrozenBits (src/polarcode/polarcode.cpp:14-34)
+    static void split(const std::vector<unsigned>& fz, unsigned half, std::vector<unsigned>& l, std::vector<unsigned>& r)
+    {
+        for (unsigned v : fz) {
+            if (v < half)
+                l.push_back(v);
+            else
+                r.push_back(v - half);
+        }
+    }
+
+    void emit(uint32_t op, int s, unsigned off)
+    {
+        p.code.push_back(mk_instr(op, (uint32_t)s, off));
+        p.census[op]++;
+    }
+
+    void node(int s, unsigned off, const std::vector<unsigned>& fz)
+    {
+        const unsigned n = 1u << s, h = n >> 1;
+        const size_t nf = fz.size();
+        bool done = true;
+        // order of FastSscFip::createDecoder (fastssc_fip_char.cpp:496-569)
+        if (nf == n)
+            emit(OP_R0, s, off);
+        else if (nf == 0)
+            emit(OP_R1, s, off);
+        else if (nf == n - 1)
+            emit(OP_REP, s, off);
+        else if (nf == 1)
+            emit(OP_SPC, s, off);
+        else if (nf == n - 2 && n >= (unsigned)kV)
+            emit(OP_DREP, s, off);
+        else
+            done = false;
+        if (!done) {
+            std::vector<unsigned> lf, rf;
+            split(fz, h, lf, rf);
+            const bool leftZero = lf.size() == h, rightOne = rf.empty();
+            if (n <= (unsigned)kV && leftZero && rightOne) {
+                emit(OP_S01, s, off);
+            } else if (leftZero && rf.size() == 1) {
+                emit(OP_0SPC, s, off); // short variant for n <= 32, long for n >= 64: decided by s in the kernel
+            } else if (rightOne) {
+                emit(OP_F, s, off);
+                node(s - 1, off, lf);
+                emit(OP_G1, s, off);
+            } else if (leftZero) {
+                emit(OP_G0, s, off);
+                node(s - 1, off + h, rf);
+                emit(OP_COMB0, s, off);
+            } else {
+                emit(OP_F, s, off);
+                node(s - 1, off, lf);
+                emit(OP_G, s, off);
+                node(s - 1, off + h, rf);
+                emit(OP_COMB, s, off);
+            }
+        }
+        if (s == blockS) emit(OP_FLUSH, s, off);
+    }
+};
+
+} // namespace
+
+bool compile_fastssc_i8(int N, const unsigned* frozen, int nf, FastSscProgram& out, const char** msg)
+{
+    static const char* e_n = "block length must be a power of two in [2, 65536]";
+    static const char* e_f = "frozen indices must be unique and < N";
+    int S = 0;
+    while ((1 << S) < N) S++;
+    if (N < 2 || (1 << S) != N || N > 65536) {
+        if (msg) *msg = e_n;
+        return false;
+    }
+    std::vector<unsigned> fz(frozen, frozen + nf);
+    std::sort(fz.begin(), fz.end());
+    for (size_t i = 0; i < fz.size(); ++i) {
+        if (fz[i] >= (unsigned)N || (i && fz[i] == fz[i - 1])) {
+            if (msg) *msg = e_f;
+            return false;
+        }
+    }
+    out = FastSscProgram();
+    out.N = N;
+    out.K = N - nf;
+    out.S = S;
+    Builder b{ out, S < 5 ? S : 5 };
+    b.node(S, 0, fz);
+    b.emit(OP_END, 0, 0);
+    // the root's LLRs stay in HBM unless the root itself is a leaf or narrower than one 16-byte chunk pair
+    uint32_t rootop = instr_op(out.code[0]);
+    out.staged_root = (S < 5) || !(rootop == OP_F || rootop == OP_G0);
+
+    // info positions, mask and gather runs
+    out.info_mask.assign((N + 31) / 32, 0u);
+    {
+        size_t fc = 0;
+        for (int i = 0; i < N; ++i) {
+            if (fc < fz.size() && fz[fc] == (unsigned)i) {
+                fc++;
+            } else {
+                out.lut.push_back((uint32_t)i);
+                out.info_mask[i >> 5] |= 1u << (i & 31);
+            }
+        }
+    }
+    const int K = out.K;
+    int k = 0;
+    while (k < K) {
+        // maximal run of consecutive positions inside one source word and one destination word
+        uint32_t pos = out.lut[k];
+        int len = 1;
+        while (k + len < K && out.lut[k + len] == pos + len && ((pos + len) >> 5) == (pos >> 5) &&
+               ((k + len) >> 5) == (k >> 5))
+            len++;
+        int kend = k + len;
+        uint32_t last = (kend == K || (kend & 31) == 0) ? 1u : 0u;
+        out.runs.push_back(mk_run(pos >> 5, pos & 31, (uint32_t)len, (uint32_t)(k & 31), last));
+        k = kend;
+    }
+    return true;
+}
+
+} // namespace pc
