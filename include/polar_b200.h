@@ -9,7 +9,7 @@
  *                           + Encoding::ButterflyFipPacked ctor             include/polarcode/encoding/butterfly_fip_packed.h:25-49
  *   pc_code_set_crc         Decoder/Encoder::setErrorDetection              decoder.cpp:133-136, src/polarcode/encoding/encoder.cpp
  *   pc_code_set_systematic  Decoder/Encoder::setSystematic                  decoder.h:118, encoder.h
- *   pc_decode_batch         Decoder::decode_vector(const char*/float*, void*)   decoder.cpp:154-181   (B codewords per call)
+ *   pc_decode_batch         Decoder::decode_vector(const char* | const float*, void*)   decoder.cpp:154-181   (B codewords per call)
  *   pc_encode_batch         Encoder::encode_vector(void*, void*)            src/polarcode/encoding/encoder.cpp:79-90
  *   pc_crc_generate_batch   ErrorDetection::Detector::generate              include/polarcode/errordetection/errordetector.h:57-63
  *   pc_crc_check_batch      Detector::check                                 errordetector.h:65-70
@@ -127,6 +127,8 @@ int pc_count_errors(const uint8_t* d_info_ref, const uint8_t* d_info_dec, const 
 /* device memory helpers so that non-CUDA hosts (ctypes, cgo, JNI) can drive the library alone */
 void* pc_device_alloc(size_t bytes);
 void pc_device_free(void* d);
+void* pc_host_alloc(size_t bytes); /* pinned host memory for the *_host entry points */
+void pc_host_free(void* h);
 int pc_memcpy_h2d(void* d, const void* h, size_t bytes);
 int pc_memcpy_d2h(void* h, const void* d, size_t bytes);
 int pc_device_synchronize(void);

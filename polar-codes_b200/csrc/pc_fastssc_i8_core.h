@@ -1,14 +1,16 @@
 // Fast-SSC int8 decoder core: one THREAD decodes one codeword by interpreting the node program of
 // pc_program.h. Four int8 LLRs per 32-bit word (pc_swar.h); hard decisions are one bit per element.
 //
-// On-chip layout (shared memory on the device): an arena of 16-byte chunks, chunk-major across the
-// threads of the CTA -- chunk c of thread t lives at word (c*T + t)*4 -- so every access of a warp is a
-// conflict-free LDS.128/STS.128. Per thread:
-//   chunk 0            LLR stages 1..3   (word 0: n=2, word 1: n=4, words 2-3: n=8)
-//   chunks [2^(s-4), 2^(s-3))   LLR stage s >= 4 (n = 2^s int8 values), up to s = S-1
-//                      (s = S too when the root is staged on chip, FastSscProgram::staged_root)
-//   chunks bbase..     hard decisions, 32 per word, element i -> word i/32 bit i%32
-// The root LLRs (the channel row) are read straight from HBM by the two top-level ops.
+// On-chip layout (shared memory on the device), T = threads per CTA, thread t:
+//   small words   word j (0..3) at small[j*T + t]: LLR stages n=2 (word 0), n=4 (word 1), n=8 (words 2,3)
+//   chunks        16-byte chunk c >= 1 at chunks[((c-1)*T + t)*4]: LLR stage s >= 4 (n = 2^s int8 values)
+//                 occupies chunks [2^(s-4), 2^(s-3)), up to s = S-1 (s = S too when the root is staged,
+//                 FastSscProgram::staged_root). A warp's access to one chunk index is one conflict-free
+//                 LDS.128/STS.128.
+//   bit words     hard decisions, 32 per word, element i -> word i/32 bit i%32, word w at bits[w*T + t]
+// Stages with s >= Sg (HYB variant, long codes) live in a global-memory arena with the same
+// thread-interleaved layout, so that every warp access is one coalesced 512-byte transaction.
+// The root LLRs (the channel row) are read straight from HBM by the top-level ops.
 //
 // Semantics follow reference src/polarcode/decoding/fastssc_fip_char.cpp (node decode functions
 // :202-492) and include/polarcode/decoding/fip_char.h; the hard decision of a node is the MSB of the
@@ -17,6 +19,7 @@
 // __host__ __device__ throughout: tests/host_emul.cpp runs this exact code for one emulated thread.
 #ifndef PC_FASTSSC_I8_CORE_H
 #define PC_FASTSSC_I8_CORE_H
+#include "pc_crc.h"
 #include "pc_program.h"
 #include "pc_swar.h"
 
@@ -26,14 +29,25 @@ struct alignas(16) u4 {
     uint32_t x, y, z, w;
 };
 
-// per-thread view of the chunk-major arena
+// per-thread view of the thread-interleaved arena
 struct TMem {
-    uint32_t* base; // word 0 of this thread's chunk 0
-    int cs;         // chunk stride in words (4 * threads per CTA)
-    PC_HD u4 ld4(int chunk) const { return *reinterpret_cast<const u4*>(base + chunk * cs); }
-    PC_HD void st4(int chunk, const u4& v) const { *reinterpret_cast<u4*>(base + chunk * cs) = v; }
-    PC_HD uint32_t ld(int chunk, int sub) const { return base[chunk * cs + sub]; }
-    PC_HD void st(int chunk, int sub, uint32_t v) const { base[chunk * cs + sub] = v; }
+    uint32_t* small;   // word 0 of this thread's small words
+    uint32_t* chunks;  // chunk 1 of this thread
+    uint32_t* bits;    // bit word 0 of this thread
+    int ws;            // word stride of the small words (threads per CTA)
+    int bws;           // word stride of the bit words
+    int cs;            // chunk stride in words (4 * ws)
+    uint32_t* gchunks; // chunk `gsplit` of this thread in the global arena (long codes), else null
+    int gcs;           // its chunk stride in words
+    int gsplit;        // first chunk index held in the global arena (INT_MAX when none)
+    PC_HD uint32_t* cptr(int chunk) const
+    {
+        return chunk >= gsplit ? gchunks + (size_t)(chunk - gsplit) * gcs : chunks + (chunk - 1) * cs;
+    }
+    PC_HD u4 ld4(int chunk) const { return *reinterpret_cast<const u4*>(cptr(chunk)); }
+    PC_HD void st4(int chunk, const u4& v) const { *reinterpret_cast<u4*>(cptr(chunk)) = v; }
+    PC_HD uint32_t sld(int j) const { return small[j * ws]; }
+    PC_HD void sst(int j, uint32_t v) const { small[j * ws] = v; }
 };
 
 // LLR source of a node with >= 32 elements: either the on-chip stage or the channel row in HBM
@@ -58,10 +72,9 @@ struct GlobalSrc {
 struct Ctx {
     TMem m;
     int S;        // log2 N
-    int bbase;    // first chunk of the hard-decision words
     uint32_t cur; // hard decisions of the 32-element block being decoded (nodes with n <= 32)
-    PC_HD uint32_t bld(int word) const { return m.ld(bbase + (word >> 2), word & 3); }
-    PC_HD void bst(int word, uint32_t v) const { m.st(bbase + (word >> 2), word & 3, v); }
+    PC_HD uint32_t bld(int word) const { return m.bits[word * m.bws]; }
+    PC_HD void bst(int word, uint32_t v) const { m.bits[word * m.bws] = v; }
 };
 
 PC_HD int stage_chunk(int s) { return 1 << (s - 4); } // s >= 4
@@ -97,13 +110,13 @@ PC_HD void op_f_small(const Ctx& c, int s)
 {
     if (s == 4) {
         u4 v = c.m.ld4(1);
-        c.m.st(0, 2, sw_f(v.x, v.z));
-        c.m.st(0, 3, sw_f(v.y, v.w));
+        c.m.sst(2, sw_f(v.x, v.z));
+        c.m.sst(3, sw_f(v.y, v.w));
     } else if (s == 3) {
-        c.m.st(0, 1, sw_f(c.m.ld(0, 2), c.m.ld(0, 3)));
+        c.m.sst(1, sw_f(c.m.sld(2), c.m.sld(3)));
     } else { // s == 2
-        uint32_t w = c.m.ld(0, 1);
-        c.m.st(0, 0, sw_f(w, w >> 16));
+        uint32_t w = c.m.sld(1);
+        c.m.sst(0, sw_f(w, w >> 16));
     }
 }
 
@@ -119,13 +132,13 @@ PC_HD void op_g0_small(const Ctx& c, int s)
 {
     if (s == 4) {
         u4 v = c.m.ld4(1);
-        c.m.st(0, 2, sw_adds(v.x, v.z));
-        c.m.st(0, 3, sw_adds(v.y, v.w));
+        c.m.sst(2, sw_adds(v.x, v.z));
+        c.m.sst(3, sw_adds(v.y, v.w));
     } else if (s == 3) {
-        c.m.st(0, 1, sw_adds(c.m.ld(0, 2), c.m.ld(0, 3)));
+        c.m.sst(1, sw_adds(c.m.sld(2), c.m.sld(3)));
     } else {
-        uint32_t w = c.m.ld(0, 1);
-        c.m.st(0, 0, sw_adds(w, w >> 16));
+        uint32_t w = c.m.sld(1);
+        c.m.sst(0, sw_adds(w, w >> 16));
     }
 }
 
@@ -150,13 +163,13 @@ PC_HD void op_g_small(const Ctx& c, int s, int off)
     const uint32_t lb = c.cur >> (off & 31);
     if (s == 4) {
         u4 v = c.m.ld4(1);
-        c.m.st(0, 2, sw_g(v.x, v.z, sw_expand4(lb)));
-        c.m.st(0, 3, sw_g(v.y, v.w, sw_expand4(lb >> 4)));
+        c.m.sst(2, sw_g(v.x, v.z, sw_expand4(lb)));
+        c.m.sst(3, sw_g(v.y, v.w, sw_expand4(lb >> 4)));
     } else if (s == 3) {
-        c.m.st(0, 1, sw_g(c.m.ld(0, 2), c.m.ld(0, 3), sw_expand4(lb)));
+        c.m.sst(1, sw_g(c.m.sld(2), c.m.sld(3), sw_expand4(lb)));
     } else {
-        uint32_t w = c.m.ld(0, 1);
-        c.m.st(0, 0, sw_g(w, w >> 16, sw_expand4(lb & 3u)));
+        uint32_t w = c.m.sld(1);
+        c.m.sst(0, sw_g(w, w >> 16, sw_expand4(lb & 3u)));
     }
 }
 
@@ -190,9 +203,9 @@ PC_HD void op_g1_small(Ctx& c, int s, int off)
         u4 v = c.m.ld4(1);
         r = sw_movemask(sw_g(v.x, v.z, sw_expand4(lb))) | (sw_movemask(sw_g(v.y, v.w, sw_expand4(lb >> 4))) << 4);
     } else if (s == 3) {
-        r = sw_movemask(sw_g(c.m.ld(0, 2), c.m.ld(0, 3), sw_expand4(lb)));
+        r = sw_movemask(sw_g(c.m.sld(2), c.m.sld(3), sw_expand4(lb)));
     } else {
-        uint32_t w = c.m.ld(0, 1);
+        uint32_t w = c.m.sld(1);
         r = sw_movemask(sw_g(w, w >> 16, sw_expand4(lb & 3u))) & 3u;
     }
     c.cur ^= r << pos;       // left ^= right
@@ -229,12 +242,12 @@ PC_HD void load_small(const Ctx& c, uint32_t (&x)[8])
         u4 a = c.m.ld4(1);
         x[0] = a.x; x[1] = a.y; x[2] = a.z; x[3] = a.w;
     } else if (S == 3) {
-        x[0] = c.m.ld(0, 2);
-        x[1] = c.m.ld(0, 3);
+        x[0] = c.m.sld(2);
+        x[1] = c.m.sld(3);
     } else if (S == 2) {
-        x[0] = c.m.ld(0, 1);
+        x[0] = c.m.sld(1);
     } else {
-        x[0] = c.m.ld(0, 0) & 0xFFFFu;
+        x[0] = c.m.sld(0) & 0xFFFFu;
     }
 }
 // x = sat(lo + hi) of a node with n = 2^S <= 32 elements: n/2 lanes in x[0 .. max(1, n/8))
@@ -249,9 +262,9 @@ PC_HD void load_small_sum(const Ctx& c, uint32_t (&x)[8])
         x[0] = sw_adds(a.x, a.z);
         x[1] = sw_adds(a.y, a.w);
     } else if (S == 3) {
-        x[0] = sw_adds(c.m.ld(0, 2), c.m.ld(0, 3));
+        x[0] = sw_adds(c.m.sld(2), c.m.sld(3));
     } else { // S == 2: two lanes
-        uint32_t w = c.m.ld(0, 1);
+        uint32_t w = c.m.sld(1);
         x[0] = sw_adds(w, w >> 16) & 0xFFFFu;
     }
 }
@@ -500,3 +513,218 @@ PC_HD void leaf_0spc_big(Ctx& c, const Src& src, int s, int off)
         c.bst(w + nv, nb);
     }
 }
+
+// RateZeroDecoder (fastssc_fip_char.cpp:202-208): all hard decisions 0
+PC_HD void leaf_r0(Ctx& c, int s, int off)
+{
+    if (s >= 6) store_block_bits(c, s, off, 0u); // n <= 32: the block word already holds zeros there
+}
+
+// ------------------------------------------------------------------ interpreter --------------------
+
+// Copies the channel row into stage S of the arena (FastSscProgram::staged_root: the root is a leaf or
+// N < 32). Rows of N < 16 bytes are not 16-byte aligned in HBM, so those go byte by byte.
+PC_HD void stage_root(const Ctx& c, const int8_t* row)
+{
+    const int S = c.S;
+    if (S >= 4) {
+        const int cb = stage_chunk(S), nc = 1 << (S - 4);
+        GlobalSrc g{ reinterpret_cast<const u4*>(row) };
+        for (int i = 0; i < nc; ++i) c.m.st4(cb + i, g.ld4(i));
+    } else {
+        uint32_t w[2] = { 0u, 0u };
+        for (int i = 0; i < (1 << S); ++i) w[i >> 2] |= (uint32_t)(uint8_t)row[i] << (8 * (i & 3));
+        if (S == 3) {
+            c.m.sst(2, w[0]);
+            c.m.sst(3, w[1]);
+        } else {
+            c.m.sst(S - 1, w[0]); // S == 2 -> word 1, S == 1 -> word 0
+        }
+    }
+}
+
+template <int S>
+PC_HD void leaf_small(Ctx& c, uint32_t op, int off)
+{
+    switch (op) {
+    case OP_R1: leaf_r1_small<S>(c, off); break;
+    case OP_REP: leaf_rep_small<S>(c, off); break;
+    case OP_SPC:
+        if (S >= 2) leaf_spc_small<(S >= 2 ? S : 2)>(c, off);
+        break;
+    case OP_S01:
+        if (S >= 2) leaf_s01<(S >= 2 ? S : 2)>(c, off);
+        break;
+    case OP_0SPC:
+        if (S >= 3) leaf_0spc_small<(S >= 3 ? S : 3)>(c, off);
+        break;
+    default: break; // OP_R0: nothing to do
+    }
+}
+
+// Runs the node program for one codeword. `row` is the channel LLR row (N int8) in HBM.
+PC_HD void fastssc_i8_run(Ctx& c, const uint32_t* code, const int8_t* row, bool staged_root)
+{
+    const int S = c.S;
+    c.cur = 0u;
+    if (staged_root) stage_root(c, row);
+    const GlobalSrc groot{ reinterpret_cast<const u4*>(row) };
+    for (int pc = 0;; ++pc) {
+        const uint32_t ins = code[pc];
+        const uint32_t op = instr_op(ins);
+        const int s = (int)instr_s(ins), off = (int)instr_off(ins);
+        if (op == OP_END) break;
+        const bool from_hbm = (s == S) && !staged_root;
+        switch (op) {
+        case OP_F:
+            if (from_hbm)
+                op_f_big(c, groot, s);
+            else if (s >= 5)
+                op_f_big(c, SmemSrc{ c.m, stage_chunk(s) }, s);
+            else
+                op_f_small(c, s);
+            break;
+        case OP_G:
+            if (from_hbm)
+                op_g_big(c, groot, s, off);
+            else if (s >= 5)
+                op_g_big(c, SmemSrc{ c.m, stage_chunk(s) }, s, off);
+            else
+                op_g_small(c, s, off);
+            break;
+        case OP_G0:
+            if (from_hbm)
+                op_g0_big(c, groot, s);
+            else if (s >= 5)
+                op_g0_big(c, SmemSrc{ c.m, stage_chunk(s) }, s);
+            else
+                op_g0_small(c, s);
+            break;
+        case OP_G1:
+            if (from_hbm)
+                op_g1_big(c, groot, s, off);
+            else if (s >= 5)
+                op_g1_big(c, SmemSrc{ c.m, stage_chunk(s) }, s, off);
+            else
+                op_g1_small(c, s, off);
+            break;
+        case OP_COMB: op_comb(c, s, off, false); break;
+        case OP_COMB0: op_comb(c, s, off, true); break;
+        case OP_FLUSH:
+            c.bst(off >> 5, c.cur);
+            c.cur = 0u;
+            break;
+        case OP_0SPC:
+            if (s >= 6) {
+                if (from_hbm)
+                    leaf_0spc_big(c, groot, s, off);
+                else
+                    leaf_0spc_big(c, SmemSrc{ c.m, stage_chunk(s) }, s, off);
+                break;
+            }
+            // fall through: short variant
+        default: // leaves
+            if (s >= 6 || (s == 5 && op == OP_DREP)) {
+                switch (op) {
+                case OP_R0: leaf_r0(c, s, off); break;
+                case OP_R1: leaf_r1_big(c, s, off); break;
+                case OP_REP: leaf_rep_big(c, s, off); break;
+                case OP_DREP: leaf_drep(c, s, off); break;
+                case OP_SPC: leaf_spc_big(c, s, off); break;
+                default: break;
+                }
+            } else {
+                switch (s) {
+                case 5: leaf_small<5>(c, op, off); break;
+                case 4: leaf_small<4>(c, op, off); break;
+                case 3: leaf_small<3>(c, op, off); break;
+                case 2: leaf_small<2>(c, op, off); break;
+                default: leaf_small<1>(c, op, off); break;
+                }
+            }
+            break;
+        }
+    }
+}
+
+// ------------------------------------------------------------------ output --------------------------
+
+// Non-systematic codes: the information is u = x F^{(x)n} (fastssc_fip_char.cpp:619-622 re-encodes the
+// hard decisions with the non-systematic butterfly). In-place on the bit words: stage d xors element
+// i + 2^d into element i (reference src/polarcode/encoding/butterfly_fip.cpp:15-63).
+PC_HD void transform_bits_inplace(const Ctx& c)
+{
+    const int nw = c.S > 5 ? (1 << (c.S - 5)) : 1;
+    const uint32_t lim = lowmask(1 << (c.S < 5 ? c.S : 5));
+    for (int w = 0; w < nw; ++w) {
+        uint32_t x = c.bld(w);
+        x ^= (x >> 1) & 0x55555555u & lim;
+        if (c.S > 1) x ^= (x >> 2) & 0x33333333u & lim;
+        if (c.S > 2) x ^= (x >> 4) & 0x0F0F0F0Fu & lim;
+        if (c.S > 3) x ^= (x >> 8) & 0x00FF00FFu & lim;
+        if (c.S > 4) x ^= (x >> 16) & 0x0000FFFFu;
+        c.bst(w, x);
+    }
+    for (int d = 1; d < nw; d <<= 1)
+        for (int g = 0; g < nw; g += 2 * d)
+            for (int i = g; i < g + d; ++i) c.bst(i, c.bld(i) ^ c.bld(i + d));
+}
+
+// element i%32 in bit i%32 (LSB first) -> the reference's MSB-first bytes as a little-endian word
+PC_HD uint32_t msb_first_word(uint32_t w)
+{
+#ifdef __CUDA_ARCH__
+    return __byte_perm(__brev(w), 0, 0x0123);
+#else
+    uint32_t r = 0;
+    for (int i = 0; i < 32; ++i)
+        if (w & (1u << i)) r |= 1u << (8 * (i >> 3) + 7 - (i & 7));
+    return r;
+#endif
+}
+
+// CharContainer::getPackedInformationBits (src/polarcode/bitcontainer.cpp:536-564) through the run list,
+// then Detector::check over the ceil(K/8) output bytes (fastssc_fip_char.cpp:627-629).
+// Returns the detector verdict. `crc_table` may live in shared memory.
+PC_HD bool extract_info(const Ctx& c, const uint32_t* runs, int nruns, int K, uint8_t* out_row, const CrcSpec& crc,
+                        const uint32_t* crc_table)
+{
+    const int kb = (K + 7) >> 3;
+    const bool word_stores = (kb & 3) == 0;
+    const int payload = crc.reflected ? 4 * ((kb >> 2) - 1) : kb - crc.bytes;
+    CrcStream cs;
+    cs.begin(crc);
+    uint32_t acc = 0u;
+    int ob = 0; // output byte index
+    for (int r = 0; r < nruns; ++r) {
+        const uint32_t run = runs[r];
+        const uint32_t sword = run & 0x7FFu, sshift = (run >> 11) & 31u, len = ((run >> 16) & 31u) + 1u,
+                       dshift = (run >> 21) & 31u, last = (run >> 26) & 1u;
+        acc |= ((c.bld((int)sword) >> sshift) & lowmask((int)len)) << dshift;
+        if (last) {
+            const uint32_t w = msb_first_word(acc);
+            const int nb = (kb - ob) < 4 ? (kb - ob) : 4;
+            if (word_stores) {
+                *reinterpret_cast<uint32_t*>(out_row + ob) = w;
+            } else {
+                for (int j = 0; j < nb; ++j) out_row[ob + j] = (uint8_t)(w >> (8 * j));
+            }
+            if (crc.width) {
+                for (int j = 0; j < nb; ++j) {
+                    const uint32_t byte = (w >> (8 * j)) & 0xFFu;
+                    const int idx = ob + j;
+                    if (idx < payload)
+                        cs.payload_byte(crc, crc_table, byte);
+                    else if (idx < payload + crc.bytes)
+                        cs.stored_byte(byte);
+                }
+            }
+            ob += nb;
+            acc = 0u;
+        }
+    }
+    return cs.ok(crc);
+}
+
+} // namespace pc
+#endif

@@ -1,0 +1,48 @@
+// Internal definition of the opaque pc_code handle of include/polar_b200.h.
+#ifndef PC_INTERNAL_H
+#define PC_INTERNAL_H
+#include <cuda_runtime.h>
+
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/polar_b200.h"
+#include "pc_crc.h"
+#include "pc_kernels.cuh"
+#include "pc_program.h"
+
+struct pc_code {
+    int N = 0, K = 0, S = 0, kind = 0, L = 1;
+    int systematic = 1;
+    int crc_kind = PC_CRC_8;
+    int device = 0;
+    std::vector<unsigned> frozen;
+    pc::FastSscProgram prog;      // Fast-SSC int8 node program (also used for its lut / info mask by the encoder)
+    // device copies
+    uint32_t* d_code = nullptr;
+    uint32_t* d_runs = nullptr;
+    uint32_t* d_crc_table = nullptr;
+    uint32_t* d_lut = nullptr;        // K info positions
+    uint32_t* d_info_mask = nullptr;  // N/32 words
+    int const_code = -1, const_runs = -1, const_words = 0;
+    // Fast-SSC launch plan
+    pc::FastSscLaunch plan;
+    bool plan_valid = false;
+    uint32_t* arena = nullptr;
+    size_t arena_bytes = 0;
+    // staging for the *_host entry points
+    void* d_stage_in = nullptr;
+    void* d_stage_out = nullptr;
+    uint8_t* d_stage_ok = nullptr;
+    size_t stage_in_bytes = 0, stage_out_bytes = 0, stage_ok_bytes = 0;
+    cudaStream_t streams[2] = { nullptr, nullptr };
+};
+
+namespace pc {
+void set_error(const std::string& s);
+int fail(int status, const std::string& s);
+int cuda_fail(cudaError_t e, const char* what);
+void count_launch(unsigned long long n = 1);
+} // namespace pc
+#endif

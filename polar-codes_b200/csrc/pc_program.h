@@ -8,6 +8,12 @@
 #include <stdint.h>
 #include <vector>
 
+#if defined(__CUDACC__)
+#define PC_PHD __host__ __device__ __forceinline__
+#else
+#define PC_PHD inline
+#endif
+
 namespace pc {
 
 // instruction word: op[5:0] | s[10:6] (log2 of the node length) | off[31:11] (element offset of the node)
@@ -30,16 +36,16 @@ enum Op : uint32_t {
     OP_COUNT
 };
 
-static inline uint32_t mk_instr(uint32_t op, uint32_t s, uint32_t off) { return op | (s << 6) | (off << 11); }
-static inline uint32_t instr_op(uint32_t i) { return i & 63u; }
-static inline uint32_t instr_s(uint32_t i) { return (i >> 6) & 31u; }
-static inline uint32_t instr_off(uint32_t i) { return i >> 11; }
+PC_PHD uint32_t mk_instr(uint32_t op, uint32_t s, uint32_t off) { return op | (s << 6) | (off << 11); }
+PC_PHD uint32_t instr_op(uint32_t i) { return i & 63u; }
+PC_PHD uint32_t instr_s(uint32_t i) { return (i >> 6) & 31u; }
+PC_PHD uint32_t instr_off(uint32_t i) { return i >> 11; }
 
 // One piece of the info-bit gather (CharContainer::getPackedInformationBits, bitcontainer.cpp:536-564):
 // take `len` consecutive hard decisions starting at bit `sshift` of 32-bit block `sword` and append
 // them at bit `dshift` of the current output word; `last` closes the output word.
 // packed: sword[10:0] | sshift[15:11] | (len-1)[20:16] | dshift[25:21] | last[26]
-static inline uint32_t mk_run(uint32_t sword, uint32_t sshift, uint32_t len, uint32_t dshift, uint32_t last)
+PC_PHD uint32_t mk_run(uint32_t sword, uint32_t sshift, uint32_t len, uint32_t dshift, uint32_t last)
 {
     return sword | (sshift << 11) | ((len - 1) << 16) | (dshift << 21) | (last << 26);
 }
