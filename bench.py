@@ -1,0 +1,281 @@
+#!/usr/bin/env python
+"""bench.py -- decoded information Gbit/s of the batched Fast-SSC int8 decoder (N=1024, K=512), B200.
+
+Contract (driver): `python bench.py --gpus N --steps K --warmup W` prints ONE JSON line on rank 0.
+  value        whole-job decoded info Gbit/s, LLR batches resident in HBM (CUDA events, max over ranks)
+  e2e          same metric through the host-buffer C-ABI call (pinned host LLRs -> H2D -> decode -> D2H)
+  roofline     algorithmic bytes (N + K/8 + 1 per frame) / kernel time vs measured HBM peak
+  cpu_baseline the reference's own AVX2 Fast-SSC char decoder (oracle/_ref) on the host cores, bounded sample
+`--impl reference` times that CPU path alone (all host threads) and prints the same line shape.
+A step = one decode launch over one batch of B frames per GPU; the batch (B x 1024 B = 1 GiB at 2^20) is far
+larger than the 126 MB L2, so no flush between steps is needed ("l2": "inputs larger than L2").
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+N_CODE, K_CODE, DSNR = 1024, 512, 0.0
+EBN0_DB, AMP = 2.0, 10.0
+METRIC = "decoded info Gbit/s, N=1024 K=512 Fast-SSC int8"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--frames", type=int, default=1 << 20, help="frames per GPU per step")
+    ap.add_argument("--e2e-frames", type=int, default=1 << 18)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """samples nvidia-smi clocks and throttle reasons DURING the timed region"""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows = []
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(index)], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+            except ValueError:
+                continue
+            for n, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def make_llr_host(rng, B):
+    """all-zero codeword over BPSK/AWGN at EBN0_DB, int8 LLR = sat(rint(AMP*y)) (pcsim defaults)"""
+    sigma = 1.0 / np.sqrt(2.0 * (K_CODE / N_CODE) * 10.0 ** (EBN0_DB / 10.0))
+    y = 1.0 + sigma * rng.standard_normal((B, N_CODE), dtype=np.float32)
+    return np.clip(np.rint(AMP * y), -128, 127).astype(np.int8)
+
+
+def cpu_reference_rate(frames, threads, repeat=1):
+    """info Gbit/s of the reference's own decode_vector loop (oracle/_ref), one decoder object per thread"""
+    import refshim
+    fz = refshim.frozen_bits(N_CODE, K_CODE, DSNR)
+    llr = make_llr_host(np.random.default_rng(7), frames)
+    _, _, secs = refshim.decode_batch(N_CODE, 1, fz, "char", llr, threads=threads, repeat=repeat, return_time=True)
+    return frames * repeat * K_CODE / secs / 1e9, secs
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation on the box's host cores (rank 0 only)"""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import refshim
+    cores = os.cpu_count() or 1
+    frames = 1 << 16
+    if not refshim.available():
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref not built on this box"}))
+        return
+    # size one step to ~1 s of all-core work
+    g, secs = cpu_reference_rate(frames, cores, 1)
+    repeat = max(1, int(1.0 / max(secs, 1e-3)))
+    for _ in range(args.warmup):
+        cpu_reference_rate(frames, cores, repeat)
+    t_tot, n_tot = 0.0, 0
+    for _ in range(args.steps):
+        g, secs = cpu_reference_rate(frames, cores, repeat)
+        t_tot += secs
+        n_tot += frames * repeat
+    val = n_tot * K_CODE / t_tot / 1e9
+    sample = f"{frames} frames x {repeat} repeats per step, {cores} threads, one decoder object per thread"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": "Gbit/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_tot / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8", "data": "synthetic",
+        "config": {"workload": "configs[1]: N=1024 K=512 Fast-SSC int8 'char', BPSK/AWGN 2 dB, amp 10"},
+        "cpu_baseline": {"value": val, "unit": "Gbit/s", "cores": cores, "kind": "reference", "sample": sample},
+        "e2e": {"value": val, "unit": "Gbit/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        return run_reference(args)
+    import torch
+    import torch.distributed as dist
+    import polar_b200_loader
+    pcb = polar_b200_loader.load()
+    capi = pcb.capi
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+    B = args.frames
+    kb = K_CODE // 8
+    fz = pcb.frozen_bits(N_CODE, K_CODE, DSNR)
+    dec = pcb.PolarDecoder(N_CODE, 1, fz, "char")
+    # synthetic batch, generated on the device for this rank's shard (global frame index seeds the generator)
+    g = torch.Generator(device=dev).manual_seed(0x5EED + rank)
+    sigma = 1.0 / np.sqrt(2.0 * (K_CODE / N_CODE) * 10.0 ** (EBN0_DB / 10.0))
+    llr = torch.empty((B, N_CODE), dtype=torch.int8, device=dev)
+    chunk = 1 << 16
+    for lo in range(0, B, chunk):
+        n = min(chunk, B - lo)
+        y = 1.0 + sigma * torch.randn((n, N_CODE), device=dev, generator=g)
+        llr[lo:lo + n] = torch.clamp(torch.round(AMP * y), -128, 127).to(torch.int8)
+    out = torch.empty((B, kb), dtype=torch.uint8, device=dev)
+    ok = torch.empty((B,), dtype=torch.uint8, device=dev)
+    stream = torch.cuda.current_stream(dev)
+    sp = __import__("ctypes").c_void_p(stream.cuda_stream)
+
+    def step():
+        capi.check(capi.lib().pc_decode_batch(dec._h, capi.ptr(llr), 0, capi.ptr(out), capi.ptr(ok), B, sp))
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    l0 = capi.lib().pc_launch_count()
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    evs[0].record(stream)
+    for i in range(args.steps):
+        step()
+        evs[i + 1].record(stream)
+    barrier()
+    launches = capi.lib().pc_launch_count() - l0
+    total_ms = evs[0].elapsed_time(evs[-1])
+    per_launch_ms = [evs[i].elapsed_time(evs[i + 1]) for i in range(args.steps)]
+    clocks = sampler.stop() if sampler else None
+    t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms_max = float(t.item())
+    value = world * B * args.steps * K_CODE / (total_ms_max * 1e-3) / 1e9
+    frac_zero = float((out == 0).all(dim=1).float().mean().item())
+
+    # ---- e2e: host buffers through the C-ABI (pinned LLRs, H2D + decode + D2H inside the timed region)
+    Be = min(args.e2e_frames, B)
+    h_llr = torch.empty((Be, N_CODE), dtype=torch.int8).pin_memory()
+    h_llr.copy_(llr[:Be].cpu())
+    h_out = torch.empty((Be, kb), dtype=torch.uint8).pin_memory()
+    h_ok = torch.empty((Be,), dtype=torch.uint8).pin_memory()
+
+    def e2e_step():
+        capi.check(capi.lib().pc_decode_batch_host(dec._h, capi.ptr(h_llr), 0, capi.ptr(h_out), capi.ptr(h_ok), Be))
+
+    for _ in range(2):
+        e2e_step()
+    barrier()
+    e2e_steps = max(3, min(args.steps, 10))
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_val = world * Be * e2e_steps * K_CODE / float(te.item()) / 1e9
+    e2e_match = bool(torch.equal(h_out, out[:Be].cpu()))
+
+    # ---- CPU baseline beside it (rank 0, N=1 only): the reference's AVX2 decoder on the host cores
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        try:
+            import refshim
+            if refshim.available():
+                cores = os.cpu_count() or 1
+                frames = 1 << 16
+                _, secs = cpu_reference_rate(frames, cores, 1)
+                repeat = max(1, int(6.0 / max(secs, 1e-3)))
+                val, secs = cpu_reference_rate(frames, cores, repeat)
+                one, _ = cpu_reference_rate(frames, 1, max(1, repeat // cores))
+                cpu = {"value": val, "unit": "Gbit/s", "cores": cores, "kind": "reference",
+                       "sample": f"{frames} frames x {repeat} repeats, {secs:.1f} s wall, one decoder per thread",
+                       "per_core": one}
+        except Exception as e:  # the baseline is a report, never a reason to lose the GPU line
+            cpu = {"value": None, "unit": "Gbit/s", "cores": 0, "kind": "reference", "sample": f"failed: {e}"}
+
+    if rank == 0:
+        peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+        if os.path.exists(peaks_path):
+            peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        else:
+            peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+        alg_bytes = B * (N_CODE + kb + 1)
+        avg_launch_s = float(np.mean(per_launch_ms)) * 1e-3
+        achieved = alg_bytes / avg_launch_s / 1e9
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tpath):
+            tj = json.load(open(tpath))
+            if tj.get("frames_per_launch"):
+                traffic = tj["dram_bytes_per_launch"] * (B / tj["frames_per_launch"])
+        line = {
+            "metric": METRIC, "value": value, "unit": "Gbit/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": total_ms_max / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "int8", "data": "synthetic",
+            "config": {"workload": "configs[1]: N=1024 K=512 Fast-SSC int8 'char', BB dSNR 0, CRC-8 detector, "
+                                   "BPSK/AWGN 2 dB, amp 10", "frames_per_gpu_per_step": B,
+                       "l2": "inputs larger than L2 (1 GiB LLR batch per step)", "parallelism": f"dp{world}"},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": traffic, "peak_source": peak_src, "kernel": "k_fastssc_i8",
+                         "alg_bytes_per_frame": N_CODE + kb + 1, "note": "integer-ALU/issue bound, see DESIGN.md"},
+            "cpu_baseline": cpu,
+            "e2e": {"value": e2e_val, "unit": "Gbit/s", "h2d_bytes_per_step": Be * N_CODE,
+                    "d2h_bytes_per_step": Be * (kb + 1), "frames_per_step": Be, "matches_device_path": e2e_match},
+            "gpu_launches": int(launches), "clocks": clocks,
+            "check": {"frac_frames_decoded_to_sent_word": frac_zero},
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
