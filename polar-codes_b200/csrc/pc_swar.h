@@ -26,7 +26,10 @@ static constexpr uint32_t k1 = 0x01010101u;
 PC_HD uint32_t sw_signfill(uint32_t x)
 {
 #ifdef __CUDA_ARCH__
-    return __byte_perm(x, 0, 0xba98);
+    // PRMT with the sign-replicate selector bit (the __byte_perm intrinsic masks it off, so inline PTX)
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %1, 0xba98;" : "=r"(r) : "r"(x));
+    return r;
 #else
     return ((x >> 7) & k1) * 0xFFu;
 #endif
