@@ -92,38 +92,55 @@ static int plan_fastssc(pc_code* c)
     P.nbw = (c->N + 31) / 32;
     const int top = g.staged_root ? g.S : g.S - 1;              // highest stage kept in the arena
     const int all_chunks = top >= 4 ? (1 << (top - 3)) - 1 : 0; // chunks 1 .. 2^(top-3)-1
-    const size_t budget = smem_max - 1024;                       // minus the CRC table
-    int want_threads = 192;
-    if (const char* e = getenv("PC_FASTSSC_THREADS")) want_threads = atoi(e);
-    if (want_threads < 32 || want_threads > 256 || (want_threads & 31)) want_threads = 192;
-    size_t per_thread = 16 + 16 * (size_t)all_chunks + 4 * (size_t)P.nbw;
-    P.gsplit = INT_MAX;
-    P.g_chunks = 0;
-    P.bits_in_smem = 1;
-    P.smem_chunks = all_chunks;
-    int T = (int)(budget / per_thread) & ~31;
-    if (T >= 128) {
-        if (T > want_threads) T = want_threads;
+    const size_t budget = smem_max;                              // per CTA, includes the 1 KiB CRC table
+    const size_t sm_smem = 233472 - 1024;                        // per SM (228 KiB minus the per-CTA reservation)
+    // Placement: stages >= sg live in the L2-resident HBM arena, stages < sg in shared memory. Each candidate
+    // split is scored by resident threads per SM; PC_FASTSSC_SPLIT / PC_FASTSSC_THREADS override (tuning).
+    int force_sg = -1, force_T = -1;
+    if (const char* e = getenv("PC_FASTSSC_SPLIT")) force_sg = atoi(e);
+    if (const char* e = getenv("PC_FASTSSC_THREADS")) force_T = atoi(e);
+    if (force_T != -1 && (force_T < 32 || force_T > 256 || (force_T & 31))) force_T = -1;
+    struct Cand { int sg, T, per_sm, bits_smem; size_t per_thread; };
+    Cand best{ -1, 0, 0, 1, 0 };
+    for (int sg = top + 1; sg >= 4; --sg) {
+        if (force_sg != -1 && sg != (force_sg > top + 1 ? top + 1 : force_sg) && !(force_sg < 4 && sg == 4)) continue;
+        const int sm_chunks = sg > top ? all_chunks : (1 << (sg - 4)) - 1;
+        for (int bits_smem = 1; bits_smem >= 0; --bits_smem) {
+            const size_t per_thread = 16 + 16 * (size_t)sm_chunks + (bits_smem ? 4 * (size_t)P.nbw : 0);
+            for (int T = 256; T >= 32; T -= 32) {
+                if (force_T != -1 && T != force_T) continue;
+                const size_t cta = 1024 + per_thread * T;
+                if (cta > budget) continue;
+                int per_sm = (int)(sm_smem / (cta + 1024));
+                if (per_sm < 1) per_sm = 1;
+                if (per_sm * T > 1024) per_sm = 1024 / T; // more threads than this never helped (register file, L2 arena size)
+                if (per_sm < 1) continue;
+                const int threads = per_sm * T;
+                // prefer: more resident threads up to 512; then everything in smem; then larger CTAs
+                const int score = (threads > 512 ? 512 : threads) * 8 + (sg > top ? 4 : 0) + bits_smem * 2 + (T >= 128);
+                const int bscore = best.sg < 0 ? -1
+                                               : ((best.T * best.per_sm > 512 ? 512 : best.T * best.per_sm) * 8 +
+                                                  (best.sg > top ? 4 : 0) + best.bits_smem * 2 + (best.T >= 128));
+                if (score > bscore) best = Cand{ sg, T, per_sm, bits_smem, per_thread };
+            }
+        }
+        if (force_sg == -1 && best.sg > top && best.T * best.per_sm >= 128) break; // whole tree fits on chip
+    }
+    if (best.sg < 0) return fail(PC_ERR_UNSUPPORTED, "fastssc_i8: no launch configuration fits shared memory");
+    P.bits_in_smem = best.bits_smem;
+    if (best.sg > top) {
+        P.gsplit = INT_MAX;
+        P.g_chunks = 0;
+        P.smem_chunks = all_chunks;
     } else {
-        // long code: keep the low stages in shared memory, the rest in the HBM arena
-        T = want_threads;
-        const size_t cap = budget / T;
-        P.bits_in_smem = (4 * (size_t)P.nbw <= cap / 4) ? 1 : 0;
-        size_t left = cap - 16 - (P.bits_in_smem ? 4 * (size_t)P.nbw : 0);
-        int sg = 4; // stages < sg in smem
-        while (sg <= top && 16 * (size_t)((1 << (sg - 3)) - 1) <= left) sg++;
-        // stages 4..sg-1 fit: chunks 1 .. 2^(sg-4+1-1)... expressed through the chunk index split
-        P.gsplit = 1 << (sg - 4);
+        P.gsplit = 1 << (best.sg - 4);
         P.smem_chunks = P.gsplit - 1;
         P.g_chunks = all_chunks + 1 - P.gsplit;
-        per_thread = 16 + 16 * (size_t)P.smem_chunks + (P.bits_in_smem ? 4 * (size_t)P.nbw : 0);
     }
+    const int T = best.T;
     P.threads = T;
-    P.smem_bytes = 1024 + per_thread * T;
-    int per_sm = (int)((smem_max + 1024) / (P.smem_bytes + 1024));
-    if (per_sm < 1) per_sm = 1;
-    if (per_sm * T > 2048) per_sm = 2048 / T;
-    P.grid = sms * per_sm;
+    P.smem_bytes = 1024 + best.per_thread * T;
+    P.grid = sms * best.per_sm;
     const size_t need = ((size_t)P.g_chunks * 16 + (P.bits_in_smem ? 0 : 4 * (size_t)P.nbw)) * (size_t)P.grid * T;
     if (need > c->arena_bytes) {
         if (c->arena) cudaFree(c->arena);

@@ -35,6 +35,40 @@ PC_HD uint32_t sw_signfill(uint32_t x)
 #endif
 }
 
+// per-byte |a - b|, bytes read as SIGNED (result 0..255) -- the one packed-byte ALU op sm_100a has natively
+// (SASS VABSDIFF4; vadd4/vmin4/vmax4 are all multi-instruction emulations, see DESIGN.md "SWAR cost table")
+PC_HD uint32_t sw_absdiff_s(uint32_t a, uint32_t b)
+{
+#ifdef __CUDA_ARCH__
+    uint32_t r;
+    asm("vabsdiff4.u32.s32.s32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(0u));
+    return r;
+#else
+    uint32_t r = 0;
+    for (int i = 0; i < 4; ++i) {
+        int x = (int8_t)(a >> (8 * i)), y = (int8_t)(b >> (8 * i));
+        r |= (uint32_t)(x > y ? x - y : y - x) << (8 * i);
+    }
+    return r;
+#endif
+}
+// per-byte |a - b|, bytes read as UNSIGNED
+PC_HD uint32_t sw_absdiff_u(uint32_t a, uint32_t b)
+{
+#ifdef __CUDA_ARCH__
+    uint32_t r;
+    asm("vabsdiff4.u32.u32.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(0u));
+    return r;
+#else
+    uint32_t r = 0;
+    for (int i = 0; i < 4; ++i) {
+        int x = (a >> (8 * i)) & 0xFF, y = (b >> (8 * i)) & 0xFF;
+        r |= (uint32_t)(x > y ? x - y : y - x) << (8 * i);
+    }
+    return r;
+#endif
+}
+
 // _mm256_adds_epi8 on four lanes
 PC_HD uint32_t sw_adds(uint32_t a, uint32_t b)
 {
@@ -114,18 +148,23 @@ PC_HD uint32_t sw_maxu(uint32_t a, uint32_t b)
 // a zero input counts as +1 (its sign bit is clear), the result is never 0 and never -128.
 PC_HD uint32_t sw_f(uint32_t a, uint32_t b)
 {
-    uint32_t m = sw_minu(sw_abs_sat(a), sw_abs_sat(b));
-    m = sw_maxu(m, k1);
-    uint32_t f = sw_signfill(a ^ b);
-    return sw_sub(m ^ f, f); // negate lanes whose sign product is negative (m in [1,127]: no overflow)
+    // 15 ALU instructions per 4 lanes, no inter-byte carries anywhere:
+    uint32_t x = sw_absdiff_s(a, 0u);         // |a| in [0,128]
+    x ^= sw_signfill(x);                      // 128 -> 127, so x + y <= 255 below
+    const uint32_t y = sw_absdiff_s(b, 0u);   // |b| in [0,128]; min(x, y) <= 127 without clamping y
+    const uint32_t m = (x + y - sw_absdiff_u(x, y)) >> 1;      // min(x, y) = (x + y - |x - y|) / 2
+    const uint32_t mag = (m + k1 + sw_absdiff_u(m, k1)) >> 1;  // max(m, 1) = (m + 1 + |m - 1|) / 2
+    const uint32_t fill = sw_signfill(a ^ b);
+    return (mag ^ fill) + (fill & k1);        // negate lanes whose sign product is negative: ~mag + 1 <= 0xFF
 }
 
 // G_function_calc (fip_char.h:67-73): bit ? sat(b - a) : sat(b + a). `fill` = 0xFF in lanes whose bit is 1.
 // sat(b - a) == ~sat(~b + a), so one saturating add serves both signs.
 PC_HD uint32_t sw_g(uint32_t a, uint32_t b, uint32_t fill) { return sw_adds(b ^ fill, a) ^ fill; }
 
-// 4-bit mask -> 0xFF/0x00 per byte (bit j -> byte j)
-PC_HD uint32_t sw_expand4(uint32_t nib) { return (((nib & 0xFu) * 0x00204081u) & k1) * 0xFFu; }
+// 4-bit mask -> 0xFF/0x00 per byte (bit j -> byte j): bit j times 2^(7j+7) lands on the MSB of byte j, the
+// sign-replicating PRMT turns MSBs into fills and ignores every other bit
+PC_HD uint32_t sw_expand4(uint32_t nib) { return sw_signfill((nib & 0xFu) * 0x10204080u); }
 
 // MSBs of the four bytes -> 4-bit mask (byte j -> bit j)
 PC_HD uint32_t sw_movemask(uint32_t w) { return (((w >> 7) & k1) * 0x01020408u) >> 24; }
