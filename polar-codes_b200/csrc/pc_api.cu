@@ -8,6 +8,7 @@
 
 #include "pc_construct.h"
 #include "pc_internal.h"
+#include "pc_fastssc_i8_core.h"
 
 namespace pc {
 
@@ -69,7 +70,12 @@ static int device_props(int* sms, size_t* smem_optin)
     return PC_OK;
 }
 
-// Chooses threads per CTA, what lives in shared memory and the grid for the Fast-SSC int8 kernel.
+// Launch planner of the Fast-SSC int8 kernel: threads per CTA, CTAs per SM and the memory every LLR stage and the
+// decision words live in (shared memory, tensor memory, L2-resident arena). One thread needs about N + N/8 bytes
+// of private storage; resident warps per SM (latency hiding for the integer pipes) are bounded by that.
+// Greedy placement per candidate geometry: stages ascending into shared memory while they fit, the rest into
+// tensor memory while it fits, the rest into the arena; decision words likewise.
+// Environment overrides (tuning only): PC_FASTSSC_THREADS, PC_FASTSSC_CTAS, PC_FASTSSC_NOTMEM=1.
 static int plan_fastssc(pc_code* c)
 {
     int sms = 0;
@@ -90,58 +96,91 @@ static int plan_fastssc(pc_code* c)
     P.g_runs = c->d_runs;
     P.g_crc_table = c->d_crc_table;
     P.nbw = (c->N + 31) / 32;
-    const int top = g.staged_root ? g.S : g.S - 1;              // highest stage kept in the arena
-    const int all_chunks = top >= 4 ? (1 << (top - 3)) - 1 : 0; // chunks 1 .. 2^(top-3)-1
-    const size_t budget = smem_max;                              // per CTA, includes the 1 KiB CRC table
-    const size_t sm_smem = 233472 - 1024;                        // per SM (228 KiB minus the per-CTA reservation)
-    // Placement: stages >= sg live in the L2-resident HBM arena, stages < sg in shared memory. Each candidate
-    // split is scored by resident threads per SM; PC_FASTSSC_SPLIT / PC_FASTSSC_THREADS override (tuning).
-    int force_sg = -1, force_T = -1;
-    if (const char* e = getenv("PC_FASTSSC_SPLIT")) force_sg = atoi(e);
+    const int top = g.staged_root ? g.S : g.S - 1; // highest stage stored by the kernel
+    int force_T = -1, force_ctas = -1, no_tmem = 0;
     if (const char* e = getenv("PC_FASTSSC_THREADS")) force_T = atoi(e);
-    if (force_T != -1 && (force_T < 32 || force_T > 256 || (force_T & 31))) force_T = -1;
-    struct Cand { int sg, T, per_sm, bits_smem; size_t per_thread; };
-    Cand best{ -1, 0, 0, 1, 0 };
-    for (int sg = top + 1; sg >= 4; --sg) {
-        if (force_sg != -1 && sg != (force_sg > top + 1 ? top + 1 : force_sg) && !(force_sg < 4 && sg == 4)) continue;
-        const int sm_chunks = sg > top ? all_chunks : (1 << (sg - 4)) - 1;
-        for (int bits_smem = 1; bits_smem >= 0; --bits_smem) {
-            const size_t per_thread = 16 + 16 * (size_t)sm_chunks + (bits_smem ? 4 * (size_t)P.nbw : 0);
-            for (int T = 256; T >= 32; T -= 32) {
-                if (force_T != -1 && T != force_T) continue;
-                const size_t cta = 1024 + per_thread * T;
-                if (cta > budget) continue;
-                int per_sm = (int)(sm_smem / (cta + 1024));
-                if (per_sm < 1) per_sm = 1;
-                if (per_sm * T > 1024) per_sm = 1024 / T; // more threads than this never helped (register file, L2 arena size)
-                if (per_sm < 1) continue;
-                const int threads = per_sm * T;
-                // prefer: more resident threads up to 512; then everything in smem; then larger CTAs
-                const int score = (threads > 512 ? 512 : threads) * 8 + (sg > top ? 4 : 0) + bits_smem * 2 + (T >= 128);
-                const int bscore = best.sg < 0 ? -1
-                                               : ((best.T * best.per_sm > 512 ? 512 : best.T * best.per_sm) * 8 +
-                                                  (best.sg > top ? 4 : 0) + best.bits_smem * 2 + (best.T >= 128));
-                if (score > bscore) best = Cand{ sg, T, per_sm, bits_smem, per_thread };
+    if (const char* e = getenv("PC_FASTSSC_CTAS")) force_ctas = atoi(e);
+    if (const char* e = getenv("PC_FASTSSC_NOTMEM")) no_tmem = atoi(e);
+    const size_t sm_smem = 233472; // 228 KiB per SM, 1 KiB of it reserved per resident CTA
+    struct Plan {
+        int T = 0, per_sm = 0, smem_chunks = 0, tm_alloc = 0, tm_cols = 0, arena_chunks = 0, bits_kind = 0, bits_base = 0;
+        uint32_t place[24] = { 0 };
+        size_t smem_bytes = 0;
+        long score = -1;
+    } best;
+    for (int per_sm = 1; per_sm <= 2; ++per_sm) {
+        if (force_ctas != -1 && per_sm != force_ctas) continue;
+        for (int T = 1024; T >= 32; T -= 32) {
+            if (force_T != -1 ? T != force_T : (T != 32 && T != 64 && (T % 128) != 0)) continue;
+            const size_t cta_budget = std::min(smem_max, sm_smem / per_sm - 1024);
+            if (cta_budget < 1024 + 64 * (size_t)T) continue;
+            const size_t per_thread_budget = (cta_budget - 1024) / T;
+            const int warps = T / 32, stack = (warps + 3) / 4;
+            int tm_alloc = no_tmem ? 0 : 512 / per_sm; // power of two
+            int tm_budget = tm_alloc / stack;           // columns per thread
+            Plan q;
+            q.T = T;
+            q.per_sm = per_sm;
+            size_t used = 16; // the four small words
+            int tm_used = 0, ar_used = 0, sm_chunks = 0;
+            bool smem_open = true;
+            for (int s = 4; s <= top && s < 24; ++s) {
+                const int nch = 1 << (s - 4);
+                if (smem_open && (s <= 5 || used + 16 * (size_t)nch <= per_thread_budget)) {
+                    q.place[s] = mk_place(PK_SMEM, (uint32_t)sm_chunks);
+                    sm_chunks += nch;
+                    used += 16 * (size_t)nch;
+                    continue;
+                }
+                smem_open = false; // keep the stage order monotone: small stages on chip, large ones further out
+                if (tm_used + 4 * nch <= tm_budget) {
+                    q.place[s] = mk_place(PK_TMEM, (uint32_t)tm_used);
+                    tm_used += 4 * nch;
+                } else {
+                    q.place[s] = mk_place(PK_ARENA, (uint32_t)ar_used);
+                    ar_used += nch;
+                }
             }
+            if (used > per_thread_budget) continue;
+            if (used + 4 * (size_t)P.nbw <= per_thread_budget) {
+                q.bits_kind = PK_SMEM;
+                used += 4 * (size_t)P.nbw;
+            } else if (tm_used + P.nbw <= tm_budget) {
+                q.bits_kind = PK_TMEM;
+                q.bits_base = tm_used;
+                tm_used += P.nbw;
+            } else {
+                q.bits_kind = PK_ARENA;
+            }
+            q.smem_chunks = sm_chunks;
+            q.arena_chunks = ar_used;
+            q.tm_cols = tm_budget;
+            q.tm_alloc = tm_used ? tm_alloc : 0;
+            q.smem_bytes = 1024 + 16 * (size_t)T + 16 * (size_t)sm_chunks * T + (q.bits_kind == PK_SMEM ? 4 * (size_t)P.nbw * T : 0);
+            const int resident = T * per_sm;
+            // Measured on B200 (N=1024, tools/sweep.sh): resident warps per SM matter more than where the large stages
+            // live -- 2 x 512 threads with stages 8, 9 in the L2 arena 194 Gbit/s, 1 x 1024 174, 1 x 512 170,
+            // 1 x 384 with everything in shared + tensor memory 146. So: maximise resident threads up to the
+            // register-file limit (64 regs x 1024), prefer two CTAs, and charge only a little for arena use.
+            q.score = (long)std::min(resident, 1024) * 100 - (ar_used ? 1000 + 4L * std::min(ar_used, 512) : 0) -
+                      (q.bits_kind == PK_ARENA ? 4000 : 0) + (per_sm - 1) * 2000 - (T > 512 ? 3000 : 0);
+            if (q.score > best.score) best = q;
         }
-        if (force_sg == -1 && best.sg > top && best.T * best.per_sm >= 128) break; // whole tree fits on chip
     }
-    if (best.sg < 0) return fail(PC_ERR_UNSUPPORTED, "fastssc_i8: no launch configuration fits shared memory");
-    P.bits_in_smem = best.bits_smem;
-    if (best.sg > top) {
-        P.gsplit = INT_MAX;
-        P.g_chunks = 0;
-        P.smem_chunks = all_chunks;
-    } else {
-        P.gsplit = 1 << (best.sg - 4);
-        P.smem_chunks = P.gsplit - 1;
-        P.g_chunks = all_chunks + 1 - P.gsplit;
-    }
-    const int T = best.T;
-    P.threads = T;
-    P.smem_bytes = 1024 + best.per_thread * T;
+    if (best.score < 0) return fail(PC_ERR_UNSUPPORTED, "fastssc_i8: no launch configuration fits the on-chip memories");
+    P.threads = best.T;
+    P.ctas_per_sm = best.per_sm;
     P.grid = sms * best.per_sm;
-    const size_t need = ((size_t)P.g_chunks * 16 + (P.bits_in_smem ? 0 : 4 * (size_t)P.nbw)) * (size_t)P.grid * T;
+    P.smem_bytes = best.smem_bytes;
+    for (int i = 0; i < 24; ++i) P.place[i] = best.place[i];
+    P.smem_chunks = best.smem_chunks;
+    P.tmem_alloc_cols = best.tm_alloc;
+    P.tmem_cols_thread = best.tm_cols;
+    P.arena_chunks = best.arena_chunks;
+    P.bits_kind = best.bits_kind;
+    P.bits_base = best.bits_base;
+    const int T = P.threads;
+    const size_t need = ((size_t)P.arena_chunks * 16 + (P.bits_kind == PK_ARENA ? 4 * (size_t)P.nbw : 0)) * (size_t)P.grid * T;
     if (need > c->arena_bytes) {
         if (c->arena) cudaFree(c->arena);
         c->arena = nullptr;

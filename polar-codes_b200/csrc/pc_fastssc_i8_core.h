@@ -1,16 +1,11 @@
 // Fast-SSC int8 decoder core: one THREAD decodes one codeword by interpreting the node program of
 // pc_program.h. Four int8 LLRs per 32-bit word (pc_swar.h); hard decisions are one bit per element.
 //
-// On-chip layout (shared memory on the device), T = threads per CTA, thread t:
-//   small words   word j (0..3) at small[j*T + t]: LLR stages n=2 (word 0), n=4 (word 1), n=8 (words 2,3)
-//   chunks        16-byte chunk c >= 1 at chunks[((c-1)*T + t)*4]: LLR stage s >= 4 (n = 2^s int8 values)
-//                 occupies chunks [2^(s-4), 2^(s-3)), up to s = S-1 (s = S too when the root is staged,
-//                 FastSscProgram::staged_root). A warp's access to one chunk index is one conflict-free
-//                 LDS.128/STS.128.
-//   bit words     hard decisions, 32 per word, element i -> word i/32 bit i%32, word w at bits[w*T + t]
-// Stages with s >= Sg (HYB variant, long codes) live in a global-memory arena with the same
-// thread-interleaved layout, so that every warp access is one coalesced 512-byte transaction.
-// The root LLRs (the channel row) are read straight from HBM by the top-level ops.
+// Storage per thread (see "where things live" below): LLR stage s (n = 2^s int8) is a run of 16-byte chunks in
+// shared memory, tensor memory or the L2-resident arena, chosen per stage by the host planner; stages 4 and 5 are
+// always shared-memory chunks 0 and 1..2; stages n = 2, 4, 8 are the four "small" words; hard decisions are
+// bit-packed words (element i -> word i/32, bit i%32). The channel row is read straight from HBM.
+// All threads of a warp execute the same node program with the same addresses (tcgen05.ld/st are warp-collective).
 //
 // Semantics follow reference src/polarcode/decoding/fastssc_fip_char.cpp (node decode functions
 // :202-492) and include/polarcode/decoding/fip_char.h; the hard decision of a node is the MSB of the
@@ -29,55 +24,144 @@ struct alignas(16) u4 {
     uint32_t x, y, z, w;
 };
 
-// per-thread view of the thread-interleaved arena
-struct TMem {
-    uint32_t* small;   // word 0 of this thread's small words
-    uint32_t* chunks;  // chunk 1 of this thread
-    uint32_t* bits;    // bit word 0 of this thread
-    int ws;            // word stride of the small words (threads per CTA)
-    int bws;           // word stride of the bit words
-    int cs;            // chunk stride in words (4 * ws)
-    uint32_t* gchunks; // chunk `gsplit` of this thread in the global arena (long codes), else null
-    int gcs;           // its chunk stride in words
-    int gsplit;        // first chunk index held in the global arena (INT_MAX when none)
-    PC_HD uint32_t* cptr(int chunk) const
-    {
-        return chunk >= gsplit ? gchunks + (size_t)(chunk - gsplit) * gcs : chunks + (chunk - 1) * cs;
+// ---- where things live -------------------------------------------------------------------------------
+// Every LLR stage s >= 4 (n = 2^s int8 values = 2^(s-4) chunks of 16 bytes) is placed by the host planner
+// (pc_api.cu plan_fastssc) in one of three memories, all private to the thread:
+//   PK_SMEM   shared memory, thread-interleaved chunks (one conflict-free LDS.128/STS.128 per warp access)
+//   PK_TMEM   tensor memory used as plain per-thread storage: lane = thread, 4 columns per chunk, moved with
+//             tcgen05.ld/st 32x32b.x4 (measured 459 B/clk/SM vs 128 B/clk/SM for shared memory, tools/tmem_bench.cu)
+//   PK_ARENA  L2-resident HBM arena, thread-interleaved like shared memory (long codes only)
+// The channel row itself is read straight from HBM. Stages s <= 3 and the hard-decision scratch word are in
+// the "small" shared-memory words.
+enum : uint32_t { PK_SMEM = 0, PK_TMEM = 1, PK_ARENA = 2 };
+PC_HD uint32_t mk_place(uint32_t kind, uint32_t base) { return kind | (base << 2); }
+
+#if defined(__CUDA_ARCH__)
+__device__ __forceinline__ void tm_st4(uint32_t taddr, const u4& v)
+{
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};" ::"r"(taddr), "r"(v.x), "r"(v.y),
+                 "r"(v.z), "r"(v.w)
+                 : "memory");
+}
+__device__ __forceinline__ void tm_ld4_nowait(uint32_t taddr, u4& v)
+{
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "r"(taddr)
+                 : "memory");
+}
+__device__ __forceinline__ void tm_st1(uint32_t taddr, uint32_t v)
+{
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x1.b32 [%0], {%1};" ::"r"(taddr), "r"(v) : "memory");
+}
+__device__ __forceinline__ void tm_ld1_nowait(uint32_t taddr, uint32_t& v)
+{
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(v) : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tm_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tm_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+#else
+// host emulation (tests/host_emul.cpp): "tensor memory" is a plain array of columns, the address its index
+extern thread_local uint32_t* g_tm_emul;
+inline void tm_st4(uint32_t taddr, const u4& v)
+{
+    g_tm_emul[taddr] = v.x; g_tm_emul[taddr + 1] = v.y; g_tm_emul[taddr + 2] = v.z; g_tm_emul[taddr + 3] = v.w;
+}
+inline void tm_ld4_nowait(uint32_t taddr, u4& v)
+{
+    v = u4{ g_tm_emul[taddr], g_tm_emul[taddr + 1], g_tm_emul[taddr + 2], g_tm_emul[taddr + 3] };
+}
+inline void tm_st1(uint32_t taddr, uint32_t v) { g_tm_emul[taddr] = v; }
+inline void tm_ld1_nowait(uint32_t taddr, uint32_t& v) { v = g_tm_emul[taddr]; }
+inline void tm_wait_ld() {}
+inline void tm_wait_st() {}
+#endif
+
+// One stage (or the channel row) as seen by one thread
+struct Mem {
+    uint32_t* p;   // generic address of chunk 0 (shared, arena or channel row); unused for tensor memory
+    int stride;    // words between consecutive chunks
+    uint32_t tcol; // tensor-memory address of chunk 0
+    bool tm;
+    PC_HD u4 ld4(int i) const
+    { // general accessor (leaves); the hot loops below use the templated forms
+        u4 v;
+        if (tm) {
+            tm_ld4_nowait(tcol + 4u * (uint32_t)i, v);
+            tm_wait_ld();
+        } else {
+            v = *reinterpret_cast<const u4*>(p + (size_t)i * stride);
+        }
+        return v;
     }
-    PC_HD u4 ld4(int chunk) const { return *reinterpret_cast<const u4*>(cptr(chunk)); }
-    PC_HD void st4(int chunk, const u4& v) const { *reinterpret_cast<u4*>(cptr(chunk)) = v; }
+    PC_HD void st4(int i, const u4& v) const
+    {
+        if (tm) {
+            tm_st4(tcol + 4u * (uint32_t)i, v);
+            tm_wait_st();
+        } else {
+            *reinterpret_cast<u4*>(p + (size_t)i * stride) = v;
+        }
+    }
+};
+
+// per-thread state
+struct Ctx {
+    int S;             // log2 N
+    uint32_t cur;      // hard decisions of the 32-element block being decoded (nodes with n <= 32)
+    const uint32_t* place; // place[s], s = 4 .. S (mk_place)
+    uint32_t* small;   // word j (0..3) at small[j * ws]: stages n = 2, 4, 8
+    int ws;
+    uint32_t* sm;      // this thread's slot of shared-memory chunk 0, chunk stride scs words
+    int scs;
+    uint32_t* ar;      // same for the arena
+    size_t acs;
+    uint32_t tm;       // tensor-memory address of this thread's column 0 (lane field of its warp + column base)
+    // hard-decision words, 32 per word, element i -> word i/32 bit i%32
+    uint32_t bits_kind;
+    uint32_t* bits;    // word 0 (shared or arena), stride bws
+    size_t bws;
+    uint32_t tbits;    // tensor-memory address of word 0
+
+    PC_HD Mem stage(int s) const
+    {
+        const uint32_t pl = place[s];
+        const uint32_t kind = pl & 3u, base = pl >> 2;
+        Mem m;
+        m.tm = kind == PK_TMEM;
+        m.tcol = tm + base;
+        if (kind == PK_ARENA) {
+            m.p = ar + (size_t)base * acs;
+            m.stride = (int)acs;
+        } else {
+            m.p = sm + (size_t)base * scs;
+            m.stride = scs;
+        }
+        return m;
+    }
     PC_HD uint32_t sld(int j) const { return small[j * ws]; }
     PC_HD void sst(int j, uint32_t v) const { small[j * ws] = v; }
-};
-
-// LLR source of a node with >= 32 elements: either the on-chip stage or the channel row in HBM
-struct SmemSrc {
-    TMem m;
-    int cb;
-    PC_HD u4 ld4(int i) const { return m.ld4(cb + i); }
-};
-struct GlobalSrc {
-    const u4* row;
-    PC_HD u4 ld4(int i) const
+    PC_HD uint32_t bld(int word) const
     {
-#ifdef __CUDA_ARCH__
-        uint4 v = __ldg(reinterpret_cast<const uint4*>(row) + i);
-        return u4{ v.x, v.y, v.z, v.w };
-#else
-        return row[i];
-#endif
+        if (bits_kind == PK_TMEM) {
+            uint32_t v;
+            tm_ld1_nowait(tbits + (uint32_t)word, v);
+            tm_wait_ld();
+            return v;
+        }
+        return bits[(size_t)word * bws];
+    }
+    PC_HD void bst(int word, uint32_t v) const
+    {
+        if (bits_kind == PK_TMEM) {
+            tm_st1(tbits + (uint32_t)word, v);
+            tm_wait_st();
+        } else {
+            bits[(size_t)word * bws] = v;
+        }
     }
 };
 
-struct Ctx {
-    TMem m;
-    int S;        // log2 N
-    uint32_t cur; // hard decisions of the 32-element block being decoded (nodes with n <= 32)
-    PC_HD uint32_t bld(int word) const { return m.bits[word * m.bws]; }
-    PC_HD void bst(int word, uint32_t v) const { m.bits[word * m.bws] = v; }
-};
-
-PC_HD int stage_chunk(int s) { return 1 << (s - 4); } // s >= 4
 PC_HD uint32_t lowmask(int nbits) { return nbits >= 32 ? 0xFFFFFFFFu : ((1u << nbits) - 1u); }
 
 PC_HD u4 f4(const u4& a, const u4& b) { return u4{ sw_f(a.x, b.x), sw_f(a.y, b.y), sw_f(a.z, b.z), sw_f(a.w, b.w) }; }
@@ -96,102 +180,141 @@ PC_HD uint32_t movemask16(const u4& v)
     return sw_movemask(v.x) | (sw_movemask(v.y) << 4) | (sw_movemask(v.z) << 8) | (sw_movemask(v.w) << 12);
 }
 
-// ------------------------------------------------------------------ internal nodes -----------------
+// stages 4 and 5 (always shared memory, chunks 0 and 1..2)
+PC_HD u4 ld_s4(const Ctx& c) { return *reinterpret_cast<const u4*>(c.sm); }
+PC_HD void st_s4(const Ctx& c, const u4& v) { *reinterpret_cast<u4*>(c.sm) = v; }
+PC_HD u4 ld_s5(const Ctx& c, int i) { return *reinterpret_cast<const u4*>(c.sm + (size_t)(1 + i) * c.scs); }
 
-// RateRNode / ShortRateRNode left step (fastssc_fip_char.cpp:401-404,414-417): child = f(lo, hi)
-template <class Src>
-PC_HD void op_f_big(const Ctx& c, const Src& src, int s)
+// ------------------------------------------------------------------ internal nodes -----------------
+// One step of a node with n = 2^s >= 64 elements: child = op(lo half, hi half) in batches of two 16-byte
+// chunks (32 child LLRs = one hard-decision word). All loads of a batch are issued before the arithmetic.
+//   BIG_F   child = f(lo, hi)                     RateRNode::decode   fastssc_fip_char.cpp:401-404
+//   BIG_G   child = g(lo, hi, left decisions)     :406-408
+//   BIG_G0  child = sat(lo + hi)                  ZeroRNode::decode   :476-483
+//   BIG_G1  right child rate-1: decisions = sign(g), combine fused    ROneNode :427-449
+enum { BIG_F = 0, BIG_G = 1, BIG_G0 = 2, BIG_G1 = 3 };
+
+template <int OP, bool ST, bool DT>
+PC_HD void big_loop(const Ctx& c, const Mem& src, const Mem& dst, int s, int off)
 {
-    const int half = 1 << (s - 5), dst = half; // stage s-1 starts at chunk 2^(s-5)
-#pragma unroll 2
-    for (int i = 0; i < half; ++i) c.m.st4(dst + i, f4(src.ld4(i), src.ld4(half + i)));
+    const int half = 1 << (s - 5), nb = half >> 1, wo = off >> 5;
+    for (int j = 0; j < nb; ++j) {
+        uint32_t bl = 0;
+        if (OP == BIG_G || OP == BIG_G1) bl = c.bld(wo + j);
+        u4 a0, a1, b0, b1;
+        if (ST) {
+            const uint32_t t = src.tcol + 8u * (uint32_t)j;
+            tm_ld4_nowait(t, a0);
+            tm_ld4_nowait(t + 4u, a1);
+            tm_ld4_nowait(t + 4u * (uint32_t)half, b0);
+            tm_ld4_nowait(t + 4u * (uint32_t)half + 4u, b1);
+            tm_wait_ld();
+        } else {
+            const uint32_t* p = src.p + (size_t)(2 * j) * src.stride;
+            a0 = *reinterpret_cast<const u4*>(p);
+            a1 = *reinterpret_cast<const u4*>(p + src.stride);
+            b0 = *reinterpret_cast<const u4*>(p + (size_t)half * src.stride);
+            b1 = *reinterpret_cast<const u4*>(p + (size_t)(half + 1) * src.stride);
+        }
+        u4 r0, r1;
+        if (OP == BIG_F) {
+            r0 = f4(a0, b0);
+            r1 = f4(a1, b1);
+        } else if (OP == BIG_G0) {
+            r0 = adds4(a0, b0);
+            r1 = adds4(a1, b1);
+        } else {
+            r0 = g4(a0, b0, bl & 0xFFFFu);
+            r1 = g4(a1, b1, bl >> 16);
+        }
+        if (OP == BIG_G1) {
+            const uint32_t r = movemask16(r0) | (movemask16(r1) << 16);
+            c.bst(wo + nb + j, r);
+            c.bst(wo + j, bl ^ r);
+        } else if (DT) {
+            const uint32_t t = dst.tcol + 8u * (uint32_t)j;
+            tm_st4(t, r0);
+            tm_st4(t + 4u, r1);
+        } else {
+            uint32_t* q = dst.p + (size_t)(2 * j) * dst.stride;
+            *reinterpret_cast<u4*>(q) = r0;
+            *reinterpret_cast<u4*>(q + dst.stride) = r1;
+        }
+    }
+    if (DT && OP != BIG_G1) tm_wait_st();
 }
-PC_HD void op_f_small(const Ctx& c, int s)
+
+template <int OP>
+PC_HD void big_op(Ctx& c, const Mem& src, int s, int off)
 {
-    if (s == 4) {
-        u4 v = c.m.ld4(1);
-        c.m.sst(2, sw_f(v.x, v.z));
-        c.m.sst(3, sw_f(v.y, v.w));
-    } else if (s == 3) {
-        c.m.sst(1, sw_f(c.m.sld(2), c.m.sld(3)));
-    } else { // s == 2
-        uint32_t w = c.m.sld(1);
-        c.m.sst(0, sw_f(w, w >> 16));
+    if (s == 5) { // one chunk per half; the left decisions are still in the block register
+        const u4 a = src.ld4(0), b = src.ld4(1);
+        const uint32_t left = c.cur & 0xFFFFu;
+        if (OP == BIG_F) {
+            st_s4(c, f4(a, b));
+        } else if (OP == BIG_G0) {
+            st_s4(c, adds4(a, b));
+        } else if (OP == BIG_G) {
+            st_s4(c, g4(a, b, left));
+        } else {
+            const uint32_t r = movemask16(g4(a, b, left));
+            c.cur = (left ^ r) | (r << 16);
+        }
+        return;
+    }
+    const Mem dst = c.stage(s - 1);
+    if (src.tm) {
+        if (OP != BIG_G1 && dst.tm)
+            big_loop<OP, true, true>(c, src, dst, s, off);
+        else
+            big_loop<OP, true, false>(c, src, dst, s, off);
+    } else {
+        if (OP != BIG_G1 && dst.tm)
+            big_loop<OP, false, true>(c, src, dst, s, off);
+        else
+            big_loop<OP, false, false>(c, src, dst, s, off);
     }
 }
 
-// ZeroRNode (fastssc_fip_char.cpp:476-483): left child is rate-0, child llr = sat(lo + hi)
-template <class Src>
-PC_HD void op_g0_big(const Ctx& c, const Src& src, int s)
+// the same steps for nodes with n <= 16 (sources: stage 4 chunk or the small words)
+PC_HD void op_f_small(const Ctx& c, int s)
 {
-    const int half = 1 << (s - 5), dst = half;
-#pragma unroll 2
-    for (int i = 0; i < half; ++i) c.m.st4(dst + i, adds4(src.ld4(i), src.ld4(half + i)));
+    if (s == 4) {
+        u4 v = ld_s4(c);
+        c.sst(2, sw_f(v.x, v.z));
+        c.sst(3, sw_f(v.y, v.w));
+    } else if (s == 3) {
+        c.sst(1, sw_f(c.sld(2), c.sld(3)));
+    } else { // s == 2
+        uint32_t w = c.sld(1);
+        c.sst(0, sw_f(w, w >> 16));
+    }
 }
 PC_HD void op_g0_small(const Ctx& c, int s)
 {
     if (s == 4) {
-        u4 v = c.m.ld4(1);
-        c.m.sst(2, sw_adds(v.x, v.z));
-        c.m.sst(3, sw_adds(v.y, v.w));
+        u4 v = ld_s4(c);
+        c.sst(2, sw_adds(v.x, v.z));
+        c.sst(3, sw_adds(v.y, v.w));
     } else if (s == 3) {
-        c.m.sst(1, sw_adds(c.m.sld(2), c.m.sld(3)));
+        c.sst(1, sw_adds(c.sld(2), c.sld(3)));
     } else {
-        uint32_t w = c.m.sld(1);
-        c.m.sst(0, sw_adds(w, w >> 16));
-    }
-}
-
-// right step (fastssc_fip_char.cpp:406-408): child = g(lo, hi, left hard decisions)
-template <class Src>
-PC_HD void op_g_big(const Ctx& c, const Src& src, int s, int off)
-{
-    const int half = 1 << (s - 5), dst = half;
-    if (s == 5) {
-        c.m.st4(dst, g4(src.ld4(0), src.ld4(1), c.cur & 0xFFFFu));
-        return;
-    }
-    const int wo = off >> 5;
-    for (int j = 0; j < (half >> 1); ++j) {
-        uint32_t bl = c.bld(wo + j);
-        c.m.st4(dst + 2 * j, g4(src.ld4(2 * j), src.ld4(half + 2 * j), bl & 0xFFFFu));
-        c.m.st4(dst + 2 * j + 1, g4(src.ld4(2 * j + 1), src.ld4(half + 2 * j + 1), bl >> 16));
+        uint32_t w = c.sld(1);
+        c.sst(0, sw_adds(w, w >> 16));
     }
 }
 PC_HD void op_g_small(const Ctx& c, int s, int off)
 {
     const uint32_t lb = c.cur >> (off & 31);
     if (s == 4) {
-        u4 v = c.m.ld4(1);
-        c.m.sst(2, sw_g(v.x, v.z, sw_expand4(lb)));
-        c.m.sst(3, sw_g(v.y, v.w, sw_expand4(lb >> 4)));
+        u4 v = ld_s4(c);
+        c.sst(2, sw_g(v.x, v.z, sw_expand4(lb)));
+        c.sst(3, sw_g(v.y, v.w, sw_expand4(lb >> 4)));
     } else if (s == 3) {
-        c.m.sst(1, sw_g(c.m.sld(2), c.m.sld(3), sw_expand4(lb)));
+        c.sst(1, sw_g(c.sld(2), c.sld(3), sw_expand4(lb)));
     } else {
-        uint32_t w = c.m.sld(1);
-        c.m.sst(0, sw_g(w, w >> 16, sw_expand4(lb & 3u)));
-    }
-}
-
-// ROneNode (fastssc_fip_char.cpp:427-474): the right child is rate-1, so its hard decision is the sign
-// of g and the combine is fused: bits = [left ^ right, right]
-template <class Src>
-PC_HD void op_g1_big(Ctx& c, const Src& src, int s, int off)
-{
-    const int half = 1 << (s - 5);
-    if (s == 5) {
-        uint32_t left = c.cur & 0xFFFFu;
-        uint32_t r = movemask16(g4(src.ld4(0), src.ld4(1), left));
-        c.cur = (left ^ r) | (r << 16);
-        return;
-    }
-    const int wo = off >> 5, hw = half >> 1;
-    for (int j = 0; j < hw; ++j) {
-        uint32_t bl = c.bld(wo + j);
-        uint32_t r = movemask16(g4(src.ld4(2 * j), src.ld4(half + 2 * j), bl & 0xFFFFu));
-        r |= movemask16(g4(src.ld4(2 * j + 1), src.ld4(half + 2 * j + 1), bl >> 16)) << 16;
-        c.bst(wo + hw + j, r);
-        c.bst(wo + j, bl ^ r);
+        uint32_t w = c.sld(1);
+        c.sst(0, sw_g(w, w >> 16, sw_expand4(lb & 3u)));
     }
 }
 PC_HD void op_g1_small(Ctx& c, int s, int off)
@@ -200,12 +323,12 @@ PC_HD void op_g1_small(Ctx& c, int s, int off)
     const uint32_t lb = c.cur >> pos;
     uint32_t r;
     if (s == 4) {
-        u4 v = c.m.ld4(1);
+        u4 v = ld_s4(c);
         r = sw_movemask(sw_g(v.x, v.z, sw_expand4(lb))) | (sw_movemask(sw_g(v.y, v.w, sw_expand4(lb >> 4))) << 4);
     } else if (s == 3) {
-        r = sw_movemask(sw_g(c.m.sld(2), c.m.sld(3), sw_expand4(lb)));
+        r = sw_movemask(sw_g(c.sld(2), c.sld(3), sw_expand4(lb)));
     } else {
-        uint32_t w = c.m.sld(1);
+        uint32_t w = c.sld(1);
         r = sw_movemask(sw_g(w, w >> 16, sw_expand4(lb & 3u))) & 3u;
     }
     c.cur ^= r << pos;       // left ^= right
@@ -235,19 +358,19 @@ template <int S>
 PC_HD void load_small(const Ctx& c, uint32_t (&x)[8])
 {
     if (S == 5) {
-        u4 a = c.m.ld4(2), b = c.m.ld4(3);
+        u4 a = ld_s5(c, 0), b = ld_s5(c, 1);
         x[0] = a.x; x[1] = a.y; x[2] = a.z; x[3] = a.w;
         x[4] = b.x; x[5] = b.y; x[6] = b.z; x[7] = b.w;
     } else if (S == 4) {
-        u4 a = c.m.ld4(1);
+        u4 a = ld_s4(c);
         x[0] = a.x; x[1] = a.y; x[2] = a.z; x[3] = a.w;
     } else if (S == 3) {
-        x[0] = c.m.sld(2);
-        x[1] = c.m.sld(3);
+        x[0] = c.sld(2);
+        x[1] = c.sld(3);
     } else if (S == 2) {
-        x[0] = c.m.sld(1);
+        x[0] = c.sld(1);
     } else {
-        x[0] = c.m.sld(0) & 0xFFFFu;
+        x[0] = c.sld(0) & 0xFFFFu;
     }
 }
 // x = sat(lo + hi) of a node with n = 2^S <= 32 elements: n/2 lanes in x[0 .. max(1, n/8))
@@ -255,16 +378,16 @@ template <int S>
 PC_HD void load_small_sum(const Ctx& c, uint32_t (&x)[8])
 {
     if (S == 5) {
-        u4 r = adds4(c.m.ld4(2), c.m.ld4(3));
+        u4 r = adds4(ld_s5(c, 0), ld_s5(c, 1));
         x[0] = r.x; x[1] = r.y; x[2] = r.z; x[3] = r.w;
     } else if (S == 4) {
-        u4 a = c.m.ld4(1);
+        u4 a = ld_s4(c);
         x[0] = sw_adds(a.x, a.z);
         x[1] = sw_adds(a.y, a.w);
     } else if (S == 3) {
-        x[0] = sw_adds(c.m.sld(2), c.m.sld(3));
+        x[0] = sw_adds(c.sld(2), c.sld(3));
     } else { // S == 2: two lanes
-        uint32_t w = c.m.sld(1);
+        uint32_t w = c.sld(1);
         x[0] = sw_adds(w, w >> 16) & 0xFFFFu;
     }
 }
@@ -291,13 +414,14 @@ PC_HD uint32_t reduce_words(uint32_t (&x)[8])
 // (RepetitionDecoder::decode fastssc_fip_char.cpp:225-236)
 PC_HD void accumulate_vectors(const Ctx& c, int s, uint32_t (&acc)[8])
 {
-    const int cb = stage_chunk(s), nv = 1 << (s - 5);
-    u4 a = c.m.ld4(cb), b = c.m.ld4(cb + 1);
+    const int nv = 1 << (s - 5);
+    const Mem m = c.stage(s);
+    u4 a = m.ld4(0), b = m.ld4(1);
     acc[0] = a.x; acc[1] = a.y; acc[2] = a.z; acc[3] = a.w;
     acc[4] = b.x; acc[5] = b.y; acc[6] = b.z; acc[7] = b.w; // sat(0 + x) == x
     for (int v = 1; v < nv; ++v) {
-        a = c.m.ld4(cb + 2 * v);
-        b = c.m.ld4(cb + 2 * v + 1);
+        a = m.ld4(2 * v);
+        b = m.ld4(2 * v + 1);
         acc[0] = sw_adds(acc[0], a.x); acc[1] = sw_adds(acc[1], a.y);
         acc[2] = sw_adds(acc[2], a.z); acc[3] = sw_adds(acc[3], a.w);
         acc[4] = sw_adds(acc[4], b.x); acc[5] = sw_adds(acc[5], b.y);
@@ -357,9 +481,9 @@ PC_HD void leaf_r1_small(Ctx& c, int off)
 }
 PC_HD void leaf_r1_big(Ctx& c, int s, int off)
 {
-    const int cb = stage_chunk(s), wo = off >> 5, nw = 1 << (s - 5);
-    for (int j = 0; j < nw; ++j)
-        c.bst(wo + j, movemask16(c.m.ld4(cb + 2 * j)) | (movemask16(c.m.ld4(cb + 2 * j + 1)) << 16));
+    const int wo = off >> 5, nw = 1 << (s - 5);
+    const Mem m = c.stage(s);
+    for (int j = 0; j < nw; ++j) c.bst(wo + j, movemask16(m.ld4(2 * j)) | (movemask16(m.ld4(2 * j + 1)) << 16));
 }
 
 // minpos_epu8 (src/polarcode/avxconvenience.cpp:13-56) restated on keys: value*32 + lane in 16-bit
@@ -450,20 +574,39 @@ struct SpcSearch {
     PC_HD bool flips() const { return (parity_of_msbs(par) & flipOk) != 0u; }
 };
 
+// Applies the SPC flip to the stored decisions (and to the copy `dup` words further on for ZeroSpc). With the
+// decision words in tensor memory every access must use a warp-uniform address, so all nv words are rewritten.
+PC_HD void spc_flip(const Ctx& c, const SpcSearch& q, int wo, int nv, int dup)
+{
+    const bool fl = q.flips();
+    if (c.bits_kind == PK_TMEM) {
+        const uint32_t mask = fl ? (1u << (q.minIdx & 31)) : 0u;
+        const int fw = q.minIdx >> 5;
+        for (int v = 0; v < nv; ++v) {
+            const uint32_t nb = c.bld(wo + v) ^ (v == fw ? mask : 0u);
+            c.bst(wo + v, nb);
+            if (dup) c.bst(wo + v + dup, nb);
+        }
+    } else if (fl) {
+        const int w = wo + (q.minIdx >> 5);
+        const uint32_t nb = c.bld(w) ^ (1u << (q.minIdx & 31));
+        c.bst(w, nb);
+        if (dup) c.bst(w + dup, nb);
+    }
+}
+
 PC_HD void leaf_spc_big(Ctx& c, int s, int off)
 {
-    const int cb = stage_chunk(s), wo = off >> 5, nv = 1 << (s - 5);
+    const int wo = off >> 5, nv = 1 << (s - 5);
+    const Mem m = c.stage(s);
     SpcSearch q;
     for (int v = 0; v < nv; ++v) {
-        u4 a = c.m.ld4(cb + 2 * v), b = c.m.ld4(cb + 2 * v + 1);
+        u4 a = m.ld4(2 * v), b = m.ld4(2 * v + 1);
         uint32_t x[8] = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w };
         c.bst(wo + v, movemask16(a) | (movemask16(b) << 16));
         q.vector(x, v);
     }
-    if (q.flips()) {
-        int w = wo + (q.minIdx >> 5);
-        c.bst(w, c.bld(w) ^ (1u << (q.minIdx & 31)));
-    }
+    spc_flip(c, q, wo, nv, 0);
 }
 
 // ShortZeroOneDecoder (fastssc_fip_char.cpp:390-399): x = sat(lo + hi), bits = [x, x]
@@ -506,12 +649,7 @@ PC_HD void leaf_0spc_big(Ctx& c, const Src& src, int s, int off)
         c.bst(wo + nv + v, bits);
         q.vector(x, v);
     }
-    if (q.flips()) {
-        int w = wo + (q.minIdx >> 5);
-        uint32_t nb = c.bld(w) ^ (1u << (q.minIdx & 31));
-        c.bst(w, nb);
-        c.bst(w + nv, nb);
-    }
+    spc_flip(c, q, wo, nv, nv);
 }
 
 // RateZeroDecoder (fastssc_fip_char.cpp:202-208): all hard decisions 0
@@ -522,23 +660,24 @@ PC_HD void leaf_r0(Ctx& c, int s, int off)
 
 // ------------------------------------------------------------------ interpreter --------------------
 
-// Copies the channel row into stage S of the arena (FastSscProgram::staged_root: the root is a leaf or
-// N < 32). Rows of N < 16 bytes are not 16-byte aligned in HBM, so those go byte by byte.
+// Copies the channel row into stage S (FastSscProgram::staged_root: the root is a leaf or N < 32). Rows of
+// N < 16 bytes are not 16-byte aligned in HBM, so those go byte by byte.
 PC_HD void stage_root(const Ctx& c, const int8_t* row)
 {
     const int S = c.S;
     if (S >= 4) {
-        const int cb = stage_chunk(S), nc = 1 << (S - 4);
-        GlobalSrc g{ reinterpret_cast<const u4*>(row) };
-        for (int i = 0; i < nc; ++i) c.m.st4(cb + i, g.ld4(i));
+        const int nc = 1 << (S - 4);
+        const Mem m = c.stage(S);
+        const u4* g = reinterpret_cast<const u4*>(row);
+        for (int i = 0; i < nc; ++i) m.st4(i, g[i]);
     } else {
         uint32_t w[2] = { 0u, 0u };
         for (int i = 0; i < (1 << S); ++i) w[i >> 2] |= (uint32_t)(uint8_t)row[i] << (8 * (i & 3));
         if (S == 3) {
-            c.m.sst(2, w[0]);
-            c.m.sst(3, w[1]);
+            c.sst(2, w[0]);
+            c.sst(3, w[1]);
         } else {
-            c.m.sst(S - 1, w[0]); // S == 2 -> word 1, S == 1 -> word 0
+            c.sst(S - 1, w[0]); // S == 2 -> word 1, S == 1 -> word 0
         }
     }
 }
@@ -568,61 +707,42 @@ PC_HD void fastssc_i8_run(Ctx& c, const uint32_t* code, const int8_t* row, bool 
     const int S = c.S;
     c.cur = 0u;
     if (staged_root) stage_root(c, row);
-    const GlobalSrc groot{ reinterpret_cast<const u4*>(row) };
+    Mem groot;
+    groot.p = reinterpret_cast<uint32_t*>(const_cast<int8_t*>(row));
+    groot.stride = 4;
+    groot.tcol = 0;
+    groot.tm = false;
     for (int pc = 0;; ++pc) {
         const uint32_t ins = code[pc];
         const uint32_t op = instr_op(ins);
         const int s = (int)instr_s(ins), off = (int)instr_off(ins);
         if (op == OP_END) break;
-        const bool from_hbm = (s == S) && !staged_root;
+        if (op <= OP_G1) { // internal steps
+            if (s >= 5) {
+                const Mem src = (s == S && !staged_root) ? groot : c.stage(s);
+                switch (op) {
+                case OP_F: big_op<BIG_F>(c, src, s, off); break;
+                case OP_G: big_op<BIG_G>(c, src, s, off); break;
+                case OP_G0: big_op<BIG_G0>(c, src, s, off); break;
+                default: big_op<BIG_G1>(c, src, s, off); break;
+                }
+            } else {
+                switch (op) {
+                case OP_F: op_f_small(c, s); break;
+                case OP_G: op_g_small(c, s, off); break;
+                case OP_G0: op_g0_small(c, s); break;
+                default: op_g1_small(c, s, off); break;
+                }
+            }
+            continue;
+        }
         switch (op) {
-        case OP_F:
-            if (from_hbm)
-                op_f_big(c, groot, s);
-            else if (s >= 5)
-                op_f_big(c, SmemSrc{ c.m, stage_chunk(s) }, s);
-            else
-                op_f_small(c, s);
-            break;
-        case OP_G:
-            if (from_hbm)
-                op_g_big(c, groot, s, off);
-            else if (s >= 5)
-                op_g_big(c, SmemSrc{ c.m, stage_chunk(s) }, s, off);
-            else
-                op_g_small(c, s, off);
-            break;
-        case OP_G0:
-            if (from_hbm)
-                op_g0_big(c, groot, s);
-            else if (s >= 5)
-                op_g0_big(c, SmemSrc{ c.m, stage_chunk(s) }, s);
-            else
-                op_g0_small(c, s);
-            break;
-        case OP_G1:
-            if (from_hbm)
-                op_g1_big(c, groot, s, off);
-            else if (s >= 5)
-                op_g1_big(c, SmemSrc{ c.m, stage_chunk(s) }, s, off);
-            else
-                op_g1_small(c, s, off);
-            break;
         case OP_COMB: op_comb(c, s, off, false); break;
         case OP_COMB0: op_comb(c, s, off, true); break;
         case OP_FLUSH:
             c.bst(off >> 5, c.cur);
             c.cur = 0u;
             break;
-        case OP_0SPC:
-            if (s >= 6) {
-                if (from_hbm)
-                    leaf_0spc_big(c, groot, s, off);
-                else
-                    leaf_0spc_big(c, SmemSrc{ c.m, stage_chunk(s) }, s, off);
-                break;
-            }
-            // fall through: short variant
         default: // leaves
             if (s >= 6 || (s == 5 && op == OP_DREP)) {
                 switch (op) {
@@ -631,6 +751,7 @@ PC_HD void fastssc_i8_run(Ctx& c, const uint32_t* code, const int8_t* row, bool 
                 case OP_REP: leaf_rep_big(c, s, off); break;
                 case OP_DREP: leaf_drep(c, s, off); break;
                 case OP_SPC: leaf_spc_big(c, s, off); break;
+                case OP_0SPC: leaf_0spc_big(c, (s == S && !staged_root) ? groot : c.stage(s), s, off); break;
                 default: break;
                 }
             } else {
@@ -687,7 +808,7 @@ PC_HD uint32_t msb_first_word(uint32_t w)
 // then Detector::check over the ceil(K/8) output bytes (fastssc_fip_char.cpp:627-629).
 // Returns the detector verdict. `crc_table` may live in shared memory.
 PC_HD bool extract_info(const Ctx& c, const uint32_t* runs, int nruns, int K, uint8_t* out_row, const CrcSpec& crc,
-                        const uint32_t* crc_table)
+                        const uint32_t* crc_table, bool store = true)
 {
     const int kb = (K + 7) >> 3;
     const bool word_stores = (kb & 3) == 0;
@@ -704,7 +825,8 @@ PC_HD bool extract_info(const Ctx& c, const uint32_t* runs, int nruns, int K, ui
         if (last) {
             const uint32_t w = msb_first_word(acc);
             const int nb = (kb - ob) < 4 ? (kb - ob) : 4;
-            if (word_stores) {
+            if (!store) {
+            } else if (word_stores) {
                 *reinterpret_cast<uint32_t*>(out_row + ob) = w;
             } else {
                 for (int j = 0; j < nb; ++j) out_row[ob + j] = (uint8_t)(w >> (8 * j));

@@ -21,21 +21,24 @@ struct FastSscLaunch {
     const uint32_t* g_runs;
     const uint32_t* g_crc_table;  // 256 words
     // geometry
-    int threads;        // per CTA
+    int threads;        // per CTA (multiple of 32)
     int grid;           // CTAs (grid-stride over frames)
-    int smem_chunks;    // 16-byte chunks per thread held in shared memory
-    int gsplit;         // first chunk index held in the HBM arena (INT_MAX: none)
-    int g_chunks;       // chunks per thread in the HBM arena
-    int bits_in_smem;   // hard-decision words in shared memory (else HBM arena)
-    int nbw;            // hard-decision words per frame
+    int ctas_per_sm;
     size_t smem_bytes;
-    uint32_t* arena;    // HBM arena: [g_chunks][grid*threads] chunks, then [nbw][grid*threads] words
+    // placement (pc_fastssc_i8_core.h "where things live")
+    uint32_t place[24];  // per stage s: mk_place(kind, base)
+    int smem_chunks;     // 16-byte chunk slots per thread in shared memory
+    int tmem_alloc_cols; // tcgen05.alloc size of the CTA (0: tensor memory unused)
+    int tmem_cols_thread; // columns owned by each thread (warps sharing a lane quarter are stacked along columns)
+    int arena_chunks;    // chunk slots per thread in the HBM arena
+    int bits_kind, bits_base; // decision words: PK_*; base = first column (tensor memory)
+    int nbw;             // decision words per frame
+    uint32_t* arena;     // [arena_chunks][grid*threads] chunks, then [nbw][grid*threads] words when bits_kind == PK_ARENA
 };
 
 cudaError_t const_pool_upload(int offset_words, const uint32_t* h_src, int nwords, cudaStream_t st);
 cudaError_t launch_fastssc_i8(const FastSscLaunch& L, const int8_t* d_llr, uint8_t* d_info, uint8_t* d_ok, size_t B,
                               cudaStream_t st);
-cudaError_t fastssc_i8_set_smem_limit(size_t bytes);
 
 } // namespace pc
 #endif

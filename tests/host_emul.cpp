@@ -12,11 +12,17 @@
 
 using namespace pc;
 
+namespace pc {
+thread_local uint32_t* g_tm_emul = nullptr;
+}
+
 extern "C" {
 
+// mode: 0 all stages in "shared memory", 1 top stage + decision words in emulated tensor memory,
+//       2 top stage + decision words in the "arena", 3 top stage in tensor memory and the next one in the arena
 // returns 0 on success; ok[i] = detector verdict
-int emul_fastssc_i8_decode(int N, const unsigned* frozen, int nf, int systematic, int crc_kind, const int8_t* llr,
-                           long B, uint8_t* out, uint8_t* ok)
+int emul_fastssc_i8_decode_mode(int N, const unsigned* frozen, int nf, int systematic, int crc_kind, const int8_t* llr,
+                                long B, uint8_t* out, uint8_t* ok, int mode)
 {
     FastSscProgram p;
     const char* msg = nullptr;
@@ -26,27 +32,40 @@ int emul_fastssc_i8_decode(int N, const unsigned* frozen, int nf, int systematic
     uint32_t table[256];
     crc_build_table(crc, table);
     const int S = p.S;
-    const int nchunks = (S >= 4 ? (1 << (S - 3)) : 1) + 1;
+    const int top = p.staged_root ? S : S - 1;
+    const int nchunks = (top >= 4 ? (1 << (top - 3)) : 1) + 1;
     const int nbw = (N + 31) / 32;
-    // 16-byte aligned row copy (rows of N < 16 bytes are unaligned in the batch)
     std::vector<u4> rowbuf((N + 15) / 16 + 1);
-    std::vector<u4> chunks(nchunks);
-    std::vector<uint32_t> small(4), bits(nbw);
+    std::vector<u4> smem(nchunks), arena(nchunks);
+    std::vector<uint32_t> tmem(4 * nchunks + nbw + 8), small(4), bits(nbw), place(32, 0u);
+    for (int s = 4; s <= top; ++s) {
+        uint32_t kind = PK_SMEM, base = (1u << (s - 4)) - 1u;
+        if (s >= 6) {
+            if ((mode == 1 || mode == 3) && s == top) { kind = PK_TMEM; base = 0; }
+            if (mode == 2 && s == top) { kind = PK_ARENA; base = 0; }
+            if (mode == 3 && s == top - 1) { kind = PK_ARENA; base = 0; }
+        }
+        place[s] = mk_place(kind, base);
+    }
     const int kb = (p.K + 7) / 8;
     std::vector<uint8_t> outrow(kb + 8);
+    g_tm_emul = tmem.data();
     for (long i = 0; i < B; ++i) {
         memcpy(rowbuf.data(), llr + i * N, N);
         Ctx c;
-        c.m.small = small.data();
-        c.m.chunks = reinterpret_cast<uint32_t*>(chunks.data());
-        c.m.bits = bits.data();
-        c.m.ws = 1;
-        c.m.bws = 1;
-        c.m.cs = 4;
-        c.m.gchunks = nullptr;
-        c.m.gcs = 0;
-        c.m.gsplit = INT_MAX;
         c.S = S;
+        c.place = place.data();
+        c.small = small.data();
+        c.ws = 1;
+        c.sm = reinterpret_cast<uint32_t*>(smem.data());
+        c.scs = 4;
+        c.ar = reinterpret_cast<uint32_t*>(arena.data());
+        c.acs = 4;
+        c.tm = 0;
+        c.bits_kind = mode == 1 ? PK_TMEM : PK_SMEM;
+        c.bits = bits.data();
+        c.bws = 1;
+        c.tbits = (uint32_t)(4 * nchunks);
         fastssc_i8_run(c, p.code.data(), reinterpret_cast<const int8_t*>(rowbuf.data()), p.staged_root);
         if (!systematic) transform_bits_inplace(c);
         bool res = extract_info(c, p.runs.data(), (int)p.runs.size(), p.K, outrow.data(), crc, table);
@@ -54,6 +73,12 @@ int emul_fastssc_i8_decode(int N, const unsigned* frozen, int nf, int systematic
         if (ok) ok[i] = res ? 1 : 0;
     }
     return 0;
+}
+
+int emul_fastssc_i8_decode(int N, const unsigned* frozen, int nf, int systematic, int crc_kind, const int8_t* llr,
+                           long B, uint8_t* out, uint8_t* ok)
+{
+    return emul_fastssc_i8_decode_mode(N, frozen, nf, systematic, crc_kind, llr, B, out, ok, 0);
 }
 
 int emul_program(int N, const unsigned* frozen, int nf, uint32_t* code, int cap)
