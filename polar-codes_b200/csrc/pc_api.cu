@@ -299,6 +299,7 @@ pc_code* pc_code_create(int N, const unsigned* frozen, int n_frozen, int kind, i
     if (st == PC_OK) st = upload(&c->d_lut, c->prog.lut);
     if (st == PC_OK) st = upload(&c->d_info_mask, c->prog.info_mask);
     if (st == PC_OK) st = upload_crc(c);
+    if (st == PC_OK) st = build_encoder_tables(c);
     if (st == PC_OK) {
         const int words = (int)(c->prog.code.size() + c->prog.runs.size());
         int off = pool_alloc(words);
@@ -329,6 +330,11 @@ void pc_code_destroy(pc_code* c)
     cudaFree(c->d_crc_table);
     cudaFree(c->d_lut);
     cudaFree(c->d_info_mask);
+    cudaFree(c->d_enc_runs);
+    cudaFree(c->d_enc_first);
+    cudaFree(c->d_enc_info);
+    cudaFree(c->d_chan_code);
+    cudaFree(c->d_quant);
     cudaFree(c->arena);
     cudaFree(c->d_stage_in);
     cudaFree(c->d_stage_out);

@@ -91,5 +91,58 @@ struct CrcStream {
     PC_HD bool ok(const CrcSpec& s) const { return s.width == 0 || tail_value(s) == stored; }
 };
 
+// Detector::calculate(data, bits): CRC::CalculateBits for the non-reflected parameter sets (reference
+// src/polarcode/errordetection/CRC.h:613-645, 870-988, 1059-1150) with the reference's register widths (8-bit register
+// for widths <= 8, 16-bit for <= 16, else 32) and its handling of a partial last byte: that byte is XORed in whole and
+// the register shifted `bits % 8` times. CRC-8 / CRC-16 round `bits` down to whole bytes (crc8.cpp:36-39,
+// crc16.cpp:20-23); CRC-32C takes bits/8 as the number of little-endian WORDS (crc32.cpp:28-31).
+PC_HD uint32_t crc_calculate_bits(const CrcSpec& s, const uint8_t* data, size_t bits)
+{
+    if (s.width == 0) return 0u;
+    if (s.reflected) {
+        uint32_t crc = 0;
+        for (size_t i = 0; i < (bits / 8) * 4; ++i) {
+            crc ^= data[i];
+            for (int k = 0; k < 8; ++k) crc = (crc & 1u) ? ((crc >> 1) ^ s.poly) : (crc >> 1);
+        }
+        return crc;
+    }
+    if (s.kind == 8 || s.kind == 16) bits = (bits / 8) * 8;
+    const int regbits = s.width <= 8 ? 8 : (s.width <= 16 ? 16 : 32);
+    const uint32_t regmask = regbits == 32 ? 0xFFFFFFFFu : ((1u << regbits) - 1u);
+    uint32_t rem = s.init;
+    const size_t whole = bits / 8, tail = bits % 8;
+    if (s.width >= 8) {
+        const int sh = s.width - 8;
+        const uint32_t top = 1u << (s.width - 1);
+        for (size_t i = 0; i < whole; ++i) {
+            rem = (rem ^ ((uint32_t)data[i] << sh)) & regmask;
+            for (int k = 0; k < 8; ++k) rem = ((rem & top) ? ((rem << 1) ^ s.poly) : (rem << 1)) & regmask;
+        }
+        if (tail) {
+            rem = (rem ^ ((uint32_t)data[whole] << sh)) & regmask;
+            for (size_t k = 0; k < tail; ++k) rem = ((rem & top) ? ((rem << 1) ^ s.poly) : (rem << 1)) & regmask;
+        }
+    } else {
+        const int sh = 8 - s.width;
+        const uint32_t poly = (s.poly << sh) & regmask;
+        if (whole) {
+            rem = (rem << sh) & regmask;
+            for (size_t i = 0; i < whole; ++i) {
+                rem = (rem ^ data[i]) & regmask;
+                for (int k = 0; k < 8; ++k) rem = ((rem & 0x80u) ? ((rem << 1) ^ poly) : (rem << 1)) & regmask;
+            }
+            rem = (rem >> sh) & regmask;
+        }
+        if (tail) {
+            rem = ((rem << sh) ^ data[whole]) & regmask;
+            for (size_t k = 0; k < tail; ++k) rem = ((rem & 0x80u) ? ((rem << 1) ^ poly) : (rem << 1)) & regmask;
+            rem = (rem >> sh) & regmask;
+        }
+    }
+    const uint32_t wmask = s.width == 32 ? 0xFFFFFFFFu : ((1u << s.width) - 1u);
+    return rem & wmask;
+}
+
 } // namespace pc
 #endif

@@ -25,6 +25,15 @@ struct pc_code {
     uint32_t* d_crc_table = nullptr;
     uint32_t* d_lut = nullptr;        // K info positions
     uint32_t* d_info_mask = nullptr;  // N/32 words
+    // encoder tables: info-bit scatter runs grouped by code word (pc_encode.cu)
+    uint2* d_enc_runs = nullptr;      // (mk_run word, info word index)
+    uint32_t* d_enc_first = nullptr;  // first run of each code word, N/32 + 1 entries
+    uint8_t* d_enc_info = nullptr;    // scratch copy of the info blocks when the detector writes check bytes
+    size_t enc_info_bytes = 0;
+    void* d_quant = nullptr;          // int8 LLRs quantised from a float batch
+    size_t quant_bytes = 0;
+    void* d_chan_code = nullptr;      // code words of the channel generator (pc_channel.cu)
+    size_t chan_code_bytes = 0;
     int const_code = -1, const_runs = -1, const_words = 0;
     // Fast-SSC launch plan
     pc::FastSscLaunch plan;
@@ -44,5 +53,12 @@ void set_error(const std::string& s);
 int fail(int status, const std::string& s);
 int cuda_fail(cudaError_t e, const char* what);
 void count_launch(unsigned long long n = 1);
+int ensure_bytes(void** d, size_t* have, size_t need);
+int crc_generate_rows(int crc_kind, uint8_t* d_data, int bytes, size_t B, cudaStream_t st);
+const uint32_t* crc_table_device(int kind);
+int quantize_device(int N, const float* d_in, int8_t* d_out, size_t B, cudaStream_t st);
+int encode_device(pc_code* c, const uint8_t* d_info, uint8_t* d_code, uint8_t* d_info_crc, size_t B, cudaStream_t st);
+int build_encoder_tables(pc_code* c);
+int encode_device_raw(pc_code* c, const uint8_t* d_info, uint8_t* d_code, size_t B, cudaStream_t st);
 } // namespace pc
 #endif
