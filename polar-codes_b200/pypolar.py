@@ -112,6 +112,7 @@ class PolarDecoder(_Code):
     def __init__(self, blockLength, listSize, frozenBitPositions, decoderType):
         kind = _kind_from_string(decoderType, int(listSize))
         self._L = int(listSize)
+        self._kind = kind
         # makeDecoder installs CRC-8 (decoder.cpp:85)
         super().__init__(blockLength, frozenBitPositions, kind, listSize, 8)
 
