@@ -37,6 +37,11 @@ uint64_t pco_crc_calculate(int kind, const uint8_t* data, size_t bits);
 void pco_crc_generate(int kind, uint8_t* data, int bytes);
 int pco_crc_check(int kind, const uint8_t* data, int bytes);
 
+/* int8 CRC-aided SCL decoder SclFipChar (src/polarcode/decoding/scl_fip_char.cpp), pc_oracle_scl.c.
+ * Returns the detector verdict; info_out gets ceil(K/8) bytes. */
+int pco_scl_i8_decode(int N, const unsigned* frozen, int nf, int L, int crc_kind, int systematic, const int8_t* llr,
+                      uint8_t* info_out);
+
 #ifdef __cplusplus
 }
 #endif

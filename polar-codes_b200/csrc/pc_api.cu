@@ -300,6 +300,14 @@ pc_code* pc_code_create(int N, const unsigned* frozen, int n_frozen, int kind, i
     if (st == PC_OK) st = upload(&c->d_info_mask, c->prog.info_mask);
     if (st == PC_OK) st = upload_crc(c);
     if (st == PC_OK) st = build_encoder_tables(c);
+    if (st == PC_OK && (kind == PC_DEC_SCL_I8)) {
+        if (!compile_scl(N, frozen, n_frozen, c->scl_prog, &msg)) {
+            set_error(msg);
+            st = PC_ERR_ARG;
+        } else {
+            st = upload(&c->d_scl_code, c->scl_prog.code);
+        }
+    }
     if (st == PC_OK) {
         const int words = (int)(c->prog.code.size() + c->prog.runs.size());
         int off = pool_alloc(words);
@@ -335,6 +343,7 @@ void pc_code_destroy(pc_code* c)
     cudaFree(c->d_enc_info);
     cudaFree(c->d_chan_code);
     cudaFree(c->d_quant);
+    cudaFree(c->d_scl_code);
     cudaFree(c->arena);
     cudaFree(c->d_stage_in);
     cudaFree(c->d_stage_out);
@@ -351,6 +360,7 @@ int pc_code_set_crc(pc_code* c, int crc_kind)
     if (!crc_spec(crc_kind, s)) return fail(PC_ERR_ARG, "CRC INVALID SIZE!");
     c->crc_kind = crc_kind;
     c->plan_valid = false;
+    c->scl_plan_valid = false;
     return upload_crc(c);
 }
 
@@ -359,6 +369,7 @@ int pc_code_set_systematic(pc_code* c, int systematic)
     if (!c) return fail(PC_ERR_ARG, "null code");
     c->systematic = systematic ? 1 : 0;
     c->plan_valid = false;
+    c->scl_plan_valid = false;
     return PC_OK;
 }
 

@@ -807,8 +807,9 @@ PC_HD uint32_t msb_first_word(uint32_t w)
 // CharContainer::getPackedInformationBits (src/polarcode/bitcontainer.cpp:536-564) through the run list,
 // then Detector::check over the ceil(K/8) output bytes (fastssc_fip_char.cpp:627-629).
 // Returns the detector verdict. `crc_table` may live in shared memory.
-PC_HD bool extract_info(const Ctx& c, const uint32_t* runs, int nruns, int K, uint8_t* out_row, const CrcSpec& crc,
-                        const uint32_t* crc_table, bool store = true)
+template <class Rd>
+PC_HD bool extract_info_rd(const Rd& rd, const uint32_t* runs, int nruns, int K, uint8_t* out_row, const CrcSpec& crc,
+                           const uint32_t* crc_table, bool store)
 {
     const int kb = (K + 7) >> 3;
     const bool word_stores = (kb & 3) == 0;
@@ -821,7 +822,7 @@ PC_HD bool extract_info(const Ctx& c, const uint32_t* runs, int nruns, int K, ui
         const uint32_t run = runs[r];
         const uint32_t sword = run & 0x7FFu, sshift = (run >> 11) & 31u, len = ((run >> 16) & 31u) + 1u,
                        dshift = (run >> 21) & 31u, last = (run >> 26) & 1u;
-        acc |= ((c.bld((int)sword) >> sshift) & lowmask((int)len)) << dshift;
+        acc |= ((rd((int)sword) >> sshift) & lowmask((int)len)) << dshift;
         if (last) {
             const uint32_t w = msb_first_word(acc);
             const int nb = (kb - ob) < 4 ? (kb - ob) : 4;
@@ -846,6 +847,16 @@ PC_HD bool extract_info(const Ctx& c, const uint32_t* runs, int nruns, int K, ui
         }
     }
     return cs.ok(crc);
+}
+
+struct CtxBitsReader {
+    const Ctx& c;
+    PC_HD uint32_t operator()(int word) const { return c.bld(word); }
+};
+PC_HD bool extract_info(const Ctx& c, const uint32_t* runs, int nruns, int K, uint8_t* out_row, const CrcSpec& crc,
+                        const uint32_t* crc_table, bool store = true)
+{
+    return extract_info_rd(CtxBitsReader{ c }, runs, nruns, K, out_row, crc, crc_table, store);
 }
 
 } // namespace pc

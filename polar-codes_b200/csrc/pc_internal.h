@@ -35,6 +35,11 @@ struct pc_code {
     void* d_chan_code = nullptr;      // code words of the channel generator (pc_channel.cu)
     size_t chan_code_bytes = 0;
     int const_code = -1, const_runs = -1, const_words = 0;
+    // SCL int8 (kind PC_DEC_SCL_I8)
+    pc::SclProgram scl_prog;
+    uint32_t* d_scl_code = nullptr;
+    pc::SclLaunch scl_plan;
+    bool scl_plan_valid = false;
     // Fast-SSC launch plan
     pc::FastSscLaunch plan;
     bool plan_valid = false;

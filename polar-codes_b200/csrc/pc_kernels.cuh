@@ -36,6 +36,32 @@ struct FastSscLaunch {
     uint32_t* arena;     // [arena_chunks][grid*threads] chunks, then [nbw][grid*threads] words when bits_kind == PK_ARENA
 };
 
+// ---- SCL int8 (pc_scl_i8.cu) ----
+struct SclParams {
+    const int8_t* llr;
+    uint8_t* info;
+    uint8_t* ok;
+    unsigned long long B;
+    int S, K, L, G, nruns, systematic, root_leaf;
+    CrcSpec crc;
+    const uint32_t* code;
+    const uint32_t* runs;
+    const uint32_t* crc_table;
+    int llr_off[20];  // word offset of LLR stage s in a lane's space (s = 0 .. S)
+    int bitL_off[20]; // word offset of the left / right decision buffer of stage s
+    int bitR_off[20];
+    int words;        // words per lane
+};
+
+struct SclLaunch {
+    SclParams p;
+    int threads, grid;
+    size_t smem_bytes;
+};
+
+cudaError_t launch_scl_i8(const SclLaunch& L, const int8_t* d_llr, uint8_t* d_info, uint8_t* d_ok, size_t B, cudaStream_t st);
+int plan_scl_i8(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, SclLaunch& out, const char** msg);
+
 cudaError_t const_pool_upload(int offset_words, const uint32_t* h_src, int nwords, cudaStream_t st);
 cudaError_t launch_fastssc_i8(const FastSscLaunch& L, const int8_t* d_llr, uint8_t* d_info, uint8_t* d_ok, size_t B,
                               cudaStream_t st);

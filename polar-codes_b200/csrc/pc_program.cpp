@@ -136,4 +136,60 @@ bool compile_fastssc_i8(int N, const unsigned* frozen, int nf, FastSscProgram& o
     return true;
 }
 
+
+namespace {
+void scl_node(SclProgram& p, int s, uint32_t side, const std::vector<unsigned>& fz)
+{
+    const unsigned n = 1u << s, h = n >> 1;
+    const size_t nf = fz.size();
+    uint32_t leaf = 0xFFu;
+    if (nf == n)
+        leaf = SCL_R0;
+    else if (nf == 0)
+        leaf = SCL_R1;
+    else if (nf == n - 1)
+        leaf = SCL_REP;
+    else if (nf == 1)
+        leaf = SCL_SPC;
+    if (leaf != 0xFFu) {
+        p.code.push_back(scl_instr(leaf, (uint32_t)s, side));
+        p.census[leaf]++;
+        return;
+    }
+    std::vector<unsigned> lf, rf;
+    for (unsigned v : fz) {
+        if (v < h)
+            lf.push_back(v);
+        else
+            rf.push_back(v - h);
+    }
+    p.code.push_back(scl_instr(SCL_F, (uint32_t)s, side));
+    scl_node(p, s - 1, 0, lf);
+    p.code.push_back(scl_instr(SCL_G, (uint32_t)s, side));
+    scl_node(p, s - 1, 1, rf);
+    p.code.push_back(scl_instr(SCL_COMB, (uint32_t)s, side));
+    p.census[SCL_F]++;
+}
+} // namespace
+
+bool compile_scl(int N, const unsigned* frozen, int nf, SclProgram& out, const char** msg)
+{
+    int S = 0;
+    while ((1 << S) < N) S++;
+    if (N < 2 || (1 << S) != N || N > 65536) {
+        if (msg) *msg = "block length must be a power of two in [2, 65536]";
+        return false;
+    }
+    std::vector<unsigned> fz(frozen, frozen + nf);
+    std::sort(fz.begin(), fz.end());
+    out = SclProgram();
+    out.N = N;
+    out.K = N - nf;
+    out.S = S;
+    scl_node(out, S, 1, fz);
+    out.root_leaf = instr_op(out.code[0]) != SCL_F;
+    out.code.push_back(scl_instr(SCL_END, 0, 0));
+    return true;
+}
+
 } // namespace pc

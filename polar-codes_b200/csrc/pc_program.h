@@ -61,6 +61,19 @@ struct FastSscProgram {
     int census[OP_COUNT] = { 0 };
 };
 
+// SCL node program (reference SclFip::createDecoder, src/polarcode/decoding/scl_fip_char.cpp:729-755): leaves are
+// R0 / R1 / REP / SPC only, in that match order; every other node splits. Instruction word:
+// op[5:0] | s[10:6] | side[11] (1: this node's decisions go to the "right" buffer of its stage, 0: "left")
+enum SclOp : uint32_t { SCL_F = 0, SCL_G = 1, SCL_COMB = 2, SCL_R0 = 3, SCL_R1 = 4, SCL_REP = 5, SCL_SPC = 6, SCL_END = 7 };
+PC_PHD uint32_t scl_instr(uint32_t op, uint32_t s, uint32_t side) { return op | (s << 6) | (side << 11); }
+struct SclProgram {
+    int N = 0, K = 0, S = 0;
+    bool root_leaf = false;       // the root itself is a leaf: the channel row is staged into stage S
+    std::vector<uint32_t> code;
+    int census[8] = { 0 };
+};
+bool compile_scl(int N, const unsigned* frozen, int nf, SclProgram& out, const char** msg);
+
 // returns false (and leaves msg) on invalid input
 bool compile_fastssc_i8(int N, const unsigned* frozen, int nf, FastSscProgram& out, const char** msg);
 

@@ -1,0 +1,606 @@
+// CRC-aided SCL int8 batch decoder for sm_100a: a group of G = 2^ceil(log2 L) lanes owns one codeword, ONE LANE PER
+// LIST PATH. Replaces SclFipChar::decode of the reference (src/polarcode/decoding/scl_fip_char.cpp:801-855).
+//
+// * Per-path work (f, g, combine, candidate metrics of a leaf) runs in the path's lane with the same SWAR int8
+//   arithmetic as the Fast-SSC kernel (pc_swar.h); all groups of a CTA execute the same node program in lockstep,
+//   so the live path count P is uniform.
+// * Lazy list copy: the reference's ref-counted block tree (PathList / DataPool, scl_fip_char.cpp:21-163,
+//   datapool.txx:100-130) becomes three small owner tables per lane (LLR, left-decisions, right-decisions: which
+//   lane's buffer holds stage s of my path), packed 5 bits per stage in registers. A fork is 9 warp shuffles; a
+//   path always writes into its own lane's buffers, and a stage is only ever rewritten by all lanes at the same
+//   program point, when its old contents are dead, so no copy-on-write is needed.
+// * Path selection: the reference's swap-based selection sort (simplePartialSortDescending, arrayfuncs.h:161-183) is
+//   emulated pass by pass with warp-shuffle arg-max (ties -> lowest position, then the swap), because the survivor
+//   ORDER and tie handling are part of the bit-exact semantics. findWeakLlrs (arrayfuncs.h:209-231) likewise.
+// * Hard decisions are one bit per element (only the MSB of the reference's bit bytes is ever consumed).
+// * extractBestPath: every lane gathers its path's info bits and runs the detector; the first passing lane (ballot)
+//   stores its block, else lane 0.
+// Storage: shared memory only, word-granular, thread-interleaved (word w of a lane at smem[w * T + tid]); other
+// lanes' buffers are read at their tid.
+#include "pc_fastssc_i8_core.h"
+#include "pc_kernels.cuh"
+
+namespace pc {
+
+struct Tbl { // 5-bit owner lane per stage
+    uint32_t w[3];
+    __device__ __forceinline__ uint32_t get(int s) const
+    {
+        const uint32_t v = s < 6 ? w[0] : (s < 12 ? w[1] : w[2]);
+        return (v >> (5 * (s % 6))) & 31u;
+    }
+    __device__ __forceinline__ void set(int s, uint32_t lane)
+    {
+        const uint32_t sh = 5u * (uint32_t)(s % 6), m = ~(31u << sh), b = lane << sh;
+        if (s < 6)
+            w[0] = (w[0] & m) | b;
+        else if (s < 12)
+            w[1] = (w[1] & m) | b;
+        else
+            w[2] = (w[2] & m) | b;
+    }
+    __device__ __forceinline__ void copy_from(const Tbl& o, int src, int width)
+    {
+        w[0] = __shfl_sync(0xFFFFFFFFu, o.w[0], src, width);
+        w[1] = __shfl_sync(0xFFFFFFFFu, o.w[1], src, width);
+        w[2] = __shfl_sync(0xFFFFFFFFu, o.w[2], src, width);
+    }
+};
+
+struct Lane {
+    uint32_t* sm;   // smem base + tid (word w at sm[w * T])
+    int T, G, l;    // threads per CTA, lanes per group, lane index inside the group
+    int P;          // live paths (uniform)
+    int metric;     // path metric (the reference uses long; |metric| <= 128 N fits easily)
+    Tbl own_llr, own_L, own_R;
+    __device__ __forceinline__ uint32_t ld(int word, uint32_t owner) const { return sm[(size_t)word * T + ((int)owner - l)]; }
+    __device__ __forceinline__ void st(int word, uint32_t v) const { sm[(size_t)word * T] = v; }
+};
+
+__device__ __forceinline__ int stage_words(int s) { return s >= 2 ? (1 << (s - 2)) : 1; }   // LLR words
+__device__ __forceinline__ int stage_bwords(int s) { return s >= 5 ? (1 << (s - 5)) : 1; }  // decision words
+__device__ __forceinline__ uint32_t bytemask(int nbytes) { return nbytes >= 4 ? 0xFFFFFFFFu : ((1u << (8 * nbytes)) - 1u); }
+
+// f / g step of a node of size 2^s: parent LLRs (stage s, through the owner table or the channel row) -> child
+// LLRs (stage s-1, own buffer). RateRNode::decode scl_fip_char.cpp:315-349.
+template <bool IS_G>
+__device__ __forceinline__ void scl_fg(Lane& c, const SclParams& p, int s, const int8_t* row)
+{
+    const bool active = c.l < c.P;
+    const int h = 1 << (s - 1);
+    const uint32_t* grow = reinterpret_cast<const uint32_t*>(row);
+    const bool from_row = (s == p.S) && !p.root_leaf;
+    const uint32_t o = c.own_llr.get(s), ol = c.own_L.get(s - 1);
+    const int src = p.llr_off[s], dst = p.llr_off[s - 1], lb = p.bitL_off[s - 1];
+    if (active) {
+        if (h >= 4) {
+            const int hw = h >> 2;
+            for (int j = 0; j < hw; ++j) {
+                const uint32_t a = from_row ? __ldg(grow + j) : c.ld(src + j, o);
+                const uint32_t b = from_row ? __ldg(grow + hw + j) : c.ld(src + hw + j, o);
+                uint32_t r;
+                if (IS_G) {
+                    const uint32_t bw = c.ld(lb + (j >> 3), ol);
+                    r = sw_g(a, b, sw_expand4(bw >> (4 * (j & 7))));
+                } else {
+                    r = sw_f(a, b);
+                }
+                c.st(dst + j, r);
+            }
+        } else {
+            const uint32_t w = from_row ? __ldg(grow) : c.ld(src, o);
+            const uint32_t hi = w >> (8 * h);
+            uint32_t r;
+            if (IS_G)
+                r = sw_g(w, hi, sw_expand4(c.ld(lb, ol)));
+            else
+                r = sw_f(w, hi);
+            c.st(dst, r & bytemask(h));
+        }
+    }
+    c.own_llr.set(s - 1, (uint32_t)c.l);
+}
+
+// CombineBits (fip_char.h:173-207): decisions(s, side) = [left ^ right, right] of stage s-1
+__device__ __forceinline__ void scl_comb(Lane& c, const SclParams& p, int s, int side)
+{
+    const bool active = c.l < c.P;
+    const int h = 1 << (s - 1);
+    const uint32_t ol = c.own_L.get(s - 1), orr = c.own_R.get(s - 1);
+    const int lo = p.bitL_off[s - 1], ro = p.bitR_off[s - 1], dst = side ? p.bitR_off[s] : p.bitL_off[s];
+    if (active) {
+        if (h >= 32) {
+            const int hw = h >> 5;
+            for (int j = 0; j < hw; ++j) {
+                const uint32_t a = c.ld(lo + j, ol), b = c.ld(ro + j, orr);
+                c.st(dst + j, a ^ b);
+                c.st(dst + hw + j, b);
+            }
+        } else {
+            const uint32_t m = (1u << h) - 1u;
+            const uint32_t a = c.ld(lo, ol) & m, b = c.ld(ro, orr) & m;
+            c.st(dst, (a ^ b) | (b << h));
+        }
+    }
+    if (side)
+        c.own_R.set(s, (uint32_t)c.l);
+    else
+        c.own_L.set(s, (uint32_t)c.l);
+}
+
+// sums of the negative / positive LLRs of the own stage-s buffer (exact integer sums, dp4a)
+__device__ __forceinline__ void llr_sums(const Lane& c, const SclParams& p, int s, int& neg, int& pos)
+{
+    const int n = 1 << s, nw = stage_words(s), off = p.llr_off[s];
+    neg = 0;
+    pos = 0;
+    for (int j = 0; j < nw; ++j) {
+        uint32_t w = c.ld(off + j, (uint32_t)c.l);
+        if (n < 4) w &= bytemask(n);
+        const uint32_t f = sw_signfill(w);
+        neg = __dp4a((int)(w & f), 0x01010101, neg);
+        pos = __dp4a((int)(w & ~f), 0x01010101, pos);
+    }
+}
+
+__device__ __forceinline__ void set_side(Lane& c, int s, int side)
+{
+    if (side)
+        c.own_R.set(s, (uint32_t)c.l);
+    else
+        c.own_L.set(s, (uint32_t)c.l);
+}
+
+// RateZeroDecoder::decode scl_fip_char.cpp:387-421: metric += sum(min(llr, 0)), decisions 0, no fork, no re-sort
+__device__ __forceinline__ void scl_r0(Lane& c, const SclParams& p, int s, int side)
+{
+    if (c.l < c.P) {
+        int neg, pos;
+        llr_sums(c, p, s, neg, pos);
+        c.metric += neg;
+        const int dst = side ? p.bitR_off[s] : p.bitL_off[s], nb = stage_bwords(s);
+        for (int j = 0; j < nb; ++j) c.st(dst + j, 0u);
+    }
+    set_side(c, s, side);
+}
+
+// ---- register-array helpers (dynamic index -> predicated selects) ---------------------------------
+template <int C>
+__device__ __forceinline__ int sel(const int (&v)[C], int k)
+{
+    int r = v[0];
+#pragma unroll
+    for (int i = 1; i < C; ++i) r = (k == i) ? v[i] : r;
+    return r;
+}
+template <int C>
+__device__ __forceinline__ void put(int (&v)[C], int k, int x)
+{
+#pragma unroll
+    for (int i = 0; i < C; ++i) v[i] = (k == i) ? x : v[i];
+}
+
+// simplePartialSortDescending (reference include/polarcode/arrayfuncs.h:161-183) over the C * P candidate metrics
+// held C per lane (position = lane * C + k), emulated pass by pass: pass i takes the FIRST maximum of positions
+// [i, size) (strict '>'), then swaps values and indices of positions i and max. Returns Values[j] / Indices[j] for
+// the caller's new path j = lane.
+template <int C>
+__device__ __forceinline__ void scl_sort(const Lane& c, int (&v)[C], int newP, int& out_val, int& out_idx)
+{
+    const int size = C * c.P, G = c.G;
+    int idx[C];
+#pragma unroll
+    for (int k = 0; k < C; ++k) idx[k] = c.l * C + k;
+    const int lim = size - 1 < newP ? size - 1 : newP;
+    for (int i = 0; i < lim; ++i) {
+        int bv = INT_MIN, bp = INT_MAX;
+#pragma unroll
+        for (int k = 0; k < C; ++k) {
+            const int pos = c.l * C + k;
+            if (pos >= i && pos < size && (bp == INT_MAX || v[k] > bv)) {
+                bv = v[k];
+                bp = pos;
+            }
+        }
+        for (int off = G >> 1; off; off >>= 1) {
+            const int ov = __shfl_xor_sync(0xFFFFFFFFu, bv, off), op = __shfl_xor_sync(0xFFFFFFFFu, bp, off);
+            if (op != INT_MAX && (bp == INT_MAX || ov > bv || (ov == bv && op < bp))) {
+                bv = ov;
+                bp = op;
+            }
+        }
+        const int li = i / C, ki = i % C, lm = bp / C, km = bp % C;
+        const int vi = __shfl_sync(0xFFFFFFFFu, sel(v, ki), li, G), ii = __shfl_sync(0xFFFFFFFFu, sel(idx, ki), li, G);
+        const int im = __shfl_sync(0xFFFFFFFFu, sel(idx, km), lm, G);
+        if (c.l == lm) {
+            put(v, km, vi);
+            put(idx, km, ii);
+        }
+        if (c.l == li) {
+            put(v, ki, bv);
+            put(idx, ki, im);
+        }
+    }
+    const int lj = (c.l / C) & (G - 1), kj = c.l % C;
+    out_val = 0;
+    out_idx = 0;
+#pragma unroll
+    for (int k = 0; k < C; ++k) {
+        const int tv = __shfl_sync(0xFFFFFFFFu, v[k], lj, G), ti = __shfl_sync(0xFFFFFFFFu, idx[k], lj, G);
+        if (kj == k) {
+            out_val = tv;
+            out_idx = ti;
+        }
+    }
+}
+
+// findWeakLlrs (arrayfuncs.h:209-231) on the |LLR| bytes stored in place in the own stage buffer: `want` passes of
+// a selection sort that takes the FIRST minimum (strict '<') of positions [i, n) and swaps it to position i. The
+// swaps mutate the array, which decides later ties, so they are performed for real. The Indices array of the
+// reference is tracked as its first four entries plus a patch list for positions >= 4.
+__device__ __forceinline__ void scl_find_weak(const Lane& c, int off, int n, int want, int (&widx)[4], int (&wval)[4])
+{
+    int I[4] = { 0, 1, 2, 3 }, ppos[4] = { -1, -1, -1, -1 }, pidx[4] = { 0, 0, 0, 0 };
+    int np = 0;
+    const int lim = n - 1 < want ? n - 1 : want;
+    const int nw = (n + 3) >> 2;
+    for (int i = 0; i < lim; ++i) {
+        int bv = 256, bp = i;
+        for (int w = i >> 2; w < nw; ++w) {
+            const uint32_t x = c.ld(off + w, (uint32_t)c.l);
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                const int pos = 4 * w + b, val = (int)((x >> (8 * b)) & 0xFFu);
+                if (pos >= i && pos < n && val < bv) {
+                    bv = val;
+                    bp = pos;
+                }
+            }
+        }
+        // swap bytes i <-> bp
+        const uint32_t wi = c.ld(off + (i >> 2), (uint32_t)c.l);
+        const int vi = (int)((wi >> (8 * (i & 3))) & 0xFFu);
+        if (bp != i) {
+            c.st(off + (i >> 2), (wi & ~(0xFFu << (8 * (i & 3)))) | ((uint32_t)bv << (8 * (i & 3))));
+            const uint32_t wm = c.ld(off + (bp >> 2), (uint32_t)c.l);
+            c.st(off + (bp >> 2), (wm & ~(0xFFu << (8 * (bp & 3)))) | ((uint32_t)vi << (8 * (bp & 3))));
+        }
+        // Indices[i] <-> Indices[bp]
+        int im = bp;
+        if (bp < 4) {
+            im = sel(I, bp);
+        } else {
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+                if (q < np && ppos[q] == bp) im = pidx[q]; // later patches override earlier ones
+        }
+        const int ii = sel(I, i); // i < 4 always (want <= 4)
+        put(I, i, im);
+        if (bp < 4) {
+            if (bp != i) put(I, bp, ii);
+        } else {
+            put(ppos, np, bp);
+            put(pidx, np, ii);
+            np++;
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        widx[k] = I[k];
+        const uint32_t x = c.ld(off + (k >> 2), (uint32_t)c.l);
+        wval[k] = (k < n) ? (int)((x >> (8 * (k & 3))) & 0xFFu) : 0;
+    }
+}
+
+// first phase of RateOne / SPC leaves: decisions = signs into the own side buffer, |max(llr, -127)| in place,
+// returns the XOR of all LLR words (its byte MSBs give the parity)
+__device__ __forceinline__ uint32_t scl_signs_and_abs(const Lane& c, const SclParams& p, int s, int side)
+{
+    const int n = 1 << s, nw = stage_words(s), off = p.llr_off[s], dst = side ? p.bitR_off[s] : p.bitL_off[s];
+    uint32_t par = 0, acc = 0;
+    for (int j = 0; j < nw; ++j) {
+        uint32_t w = c.ld(off + j, (uint32_t)c.l);
+        if (n < 4) w &= bytemask(n);
+        par ^= w;
+        acc |= sw_movemask(w) << (4 * (j & 7));
+        c.st(off + j, sw_abs_sat(w));
+        if ((j & 7) == 7 || j == nw - 1) {
+            c.st(dst + (j >> 3), acc);
+            acc = 0;
+        }
+    }
+    return par;
+}
+
+// second phase: the new path in this lane takes the decisions of old path `sp` (stored in lane sp's side buffer)
+// with the bytes listed in fmask (bit q -> index fi[q]) flipped (`~` in the reference, i.e. the sign always flips)
+__device__ __forceinline__ void scl_take_bits(const Lane& c, const SclParams& p, int s, int side, int sp, bool live,
+                                              int fmask, const int (&fi)[4])
+{
+    const int nb = stage_bwords(s), dst = side ? p.bitR_off[s] : p.bitL_off[s];
+    for (int w = 0; w < nb; ++w) {
+        uint32_t t = c.ld(dst + w, (uint32_t)sp);
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+            if (((fmask >> q) & 1) && (fi[q] >> 5) == w) t ^= 1u << (fi[q] & 31);
+        __syncwarp();
+        if (live) c.st(dst + w, t);
+    }
+    __syncwarp();
+}
+
+// duplicatePath + switchToNext (scl_fip_char.cpp:55-63,91-98): 9 shuffles instead of ref-count updates
+__device__ __forceinline__ void scl_fork(Lane& c, int sp, int val, int newP)
+{
+    Tbl a = c.own_llr, b = c.own_L, d = c.own_R;
+    c.own_llr.copy_from(a, sp, c.G);
+    c.own_L.copy_from(b, sp, c.G);
+    c.own_R.copy_from(d, sp, c.G);
+    c.metric = val;
+    c.P = newP;
+}
+
+// RepetitionDecoder::decode scl_fip_char.cpp:508-581
+__device__ __forceinline__ void scl_rep(Lane& c, const SclParams& p, int s, int side)
+{
+    int v[2] = { INT_MIN, INT_MIN };
+    if (c.l < c.P) {
+        int neg, pos;
+        llr_sums(c, p, s, neg, pos);
+        v[0] = c.metric + neg;
+        v[1] = c.metric - pos;
+    }
+    const int newP = 2 * c.P < p.L ? 2 * c.P : p.L;
+    int val, idx;
+    scl_sort<2>(c, v, newP, val, idx);
+    const bool live = c.l < newP;
+    const int sp = live ? idx >> 1 : 0;
+    scl_fork(c, sp, val, newP);
+    if (live) {
+        const int dst = side ? p.bitR_off[s] : p.bitL_off[s], nb = stage_bwords(s);
+        const uint32_t fill = (idx & 1) ? 0xFFFFFFFFu : 0u;
+        for (int j = 0; j < nb; ++j) c.st(dst + j, fill);
+    }
+    set_side(c, s, side);
+}
+
+// RateOneDecoder::decode scl_fip_char.cpp:423-505
+__device__ __forceinline__ void scl_r1(Lane& c, const SclParams& p, int s, int side)
+{
+    int v[4] = { INT_MIN, INT_MIN, INT_MIN, INT_MIN };
+    int wi[4] = { 0, 0, 0, 0 }, wv[4];
+    if (c.l < c.P) {
+        scl_signs_and_abs(c, p, s, side);
+        scl_find_weak(c, p.llr_off[s], 1 << s, 2, wi, wv);
+        v[0] = c.metric;
+        v[1] = c.metric - wv[0];
+        v[2] = c.metric - wv[1];
+        v[3] = c.metric - wv[0] - wv[1];
+    }
+    __syncwarp();
+    const int newP = 4 * c.P < p.L ? 4 * c.P : p.L;
+    int val, idx;
+    scl_sort<4>(c, v, newP, val, idx);
+    const bool live = c.l < newP;
+    const int sp = live ? idx >> 2 : 0;
+    int fi[4];
+    fi[0] = __shfl_sync(0xFFFFFFFFu, wi[0], sp, c.G);
+    fi[1] = __shfl_sync(0xFFFFFFFFu, wi[1], sp, c.G);
+    fi[2] = 0;
+    fi[3] = 0;
+    scl_fork(c, sp, val, newP);
+    scl_take_bits(c, p, s, side, sp, live, idx & 3, fi);
+    set_side(c, s, side);
+}
+
+// SpcDecoder::decode scl_fip_char.cpp:583-726
+__device__ __forceinline__ void scl_spc(Lane& c, const SclParams& p, int s, int side)
+{
+    int v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = INT_MIN;
+    int wi[4] = { 0, 0, 0, 0 }, wv[4];
+    int parity = 0;
+    if (c.l < c.P) {
+        const uint32_t par = scl_signs_and_abs(c, p, s, side);
+        parity = (int)parity_of_msbs(par);
+        scl_find_weak(c, p.llr_off[s], 1 << s, 4, wi, wv);
+        int m = c.metric, weakest = 0;
+        if (parity)
+            m -= wv[0];
+        else
+            weakest = wv[0];
+        v[0] = m;
+        v[1] = m - weakest - wv[1];
+        v[2] = m - weakest - wv[2];
+        v[3] = m - weakest - wv[3];
+        v[4] = m - wv[1] - wv[2];
+        v[5] = m - wv[1] - wv[3];
+        v[6] = m - wv[2] - wv[3];
+        v[7] = m - weakest - wv[1] - wv[2] - wv[3];
+    }
+    __syncwarp();
+    const int newP = 8 * c.P < p.L ? 8 * c.P : p.L;
+    int val, idx;
+    scl_sort<8>(c, v, newP, val, idx);
+    const bool live = c.l < newP;
+    const int sp = live ? idx >> 3 : 0;
+    int fi[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) fi[q] = __shfl_sync(0xFFFFFFFFu, wi[q], sp, c.G);
+    const int spar = __shfl_sync(0xFFFFFFFFu, parity, sp, c.G);
+    // flip sets per candidate as 4-bit masks over (idx0..idx3), scl_fip_char.cpp:641-692
+    const uint32_t tab = spar ? 0xEDB78421u : 0xFCA69530u;
+    scl_fork(c, sp, val, newP);
+    scl_take_bits(c, p, s, side, sp, live, (int)((tab >> (4 * (idx & 7))) & 15u), fi);
+    set_side(c, s, side);
+}
+
+struct SclBitsReader {
+    const Lane& c;
+    int off;
+    uint32_t owner;
+    __device__ __forceinline__ uint32_t operator()(int word) const { return c.ld(off + word, owner); }
+};
+
+__global__ void __launch_bounds__(256) k_scl_i8(const __grid_constant__ SclParams p)
+{
+    extern __shared__ __align__(16) uint32_t smem[];
+    const int T = blockDim.x, t = threadIdx.x;
+    uint32_t* crc_table = smem; // 256 words
+    if (p.crc.width)
+        for (int i = t; i < 256; i += T) crc_table[i] = p.crc_table[i];
+    __syncthreads();
+    Lane c;
+    c.sm = smem + 256 + t;
+    c.T = T;
+    c.G = p.G;
+    c.l = t & (p.G - 1);
+    const int gpc = T / p.G; // codewords per CTA
+    const int N = 1 << p.S, kb = (p.K + 7) >> 3;
+    const unsigned gmask = (p.G == 32 ? 0xFFFFFFFFu : ((1u << p.G) - 1u)) << ((t & 31) & ~(p.G - 1));
+    const unsigned long long nbatch = (p.B + gpc - 1) / gpc;
+    for (unsigned long long bi = blockIdx.x; bi < nbatch; bi += gridDim.x) {
+        const unsigned long long fl = bi * gpc + (unsigned long long)(t / p.G);
+        const bool live_frame = fl < p.B;
+        const unsigned long long f = live_frame ? fl : p.B - 1;
+        const int8_t* row = p.llr + f * N;
+        c.P = 1;
+        c.metric = 0;
+        c.own_llr = Tbl{ { 0u, 0u, 0u } };
+        c.own_L = c.own_llr;
+        c.own_R = c.own_llr;
+        if (p.root_leaf && c.l == 0) { // stage the channel row (the root is a leaf)
+            const int nw = stage_words(p.S);
+            if (N >= 4) {
+                for (int j = 0; j < nw; ++j) c.st(p.llr_off[p.S] + j, reinterpret_cast<const uint32_t*>(row)[j]);
+            } else {
+                c.st(p.llr_off[p.S], (uint32_t)(uint8_t)row[0] | ((uint32_t)(uint8_t)row[1] << 8));
+            }
+        }
+        __syncwarp();
+        for (int pc = 0;; ++pc) {
+            const uint32_t ins = __ldg(p.code + pc);
+            const uint32_t op = ins & 63u;
+            const int s = (int)((ins >> 6) & 31u), side = (int)((ins >> 11) & 1u);
+            if (op == SCL_END) break;
+            switch (op) {
+            case SCL_F: scl_fg<false>(c, p, s, row); break;
+            case SCL_G: scl_fg<true>(c, p, s, row); break;
+            case SCL_COMB: scl_comb(c, p, s, side); break;
+            case SCL_R0: scl_r0(c, p, s, side); break;
+            case SCL_R1: scl_r1(c, p, s, side); break;
+            case SCL_REP: scl_rep(c, p, s, side); break;
+            default: scl_spc(c, p, s, side); break;
+            }
+            __syncwarp(); // other lanes' buffers are read by the next step
+        }
+        // extractBestPath (scl_fip_char.cpp:816-855)
+        const bool active = c.l < c.P;
+        const int top = p.bitR_off[p.S], nbw = stage_bwords(p.S);
+        uint32_t owner = c.own_R.get(p.S);
+        int off = top;
+        if (!p.systematic) {
+            // u = x F^(x)n on a private copy (the left buffer of the top stage is free at this point)
+            const int scr = p.bitL_off[p.S];
+            if (active) {
+                const uint32_t lim = lowmask(1 << (p.S < 5 ? p.S : 5));
+                for (int w = 0; w < nbw; ++w) {
+                    uint32_t x = c.ld(top + w, owner);
+                    x ^= (x >> 1) & 0x55555555u & lim;
+                    if (p.S > 1) x ^= (x >> 2) & 0x33333333u & lim;
+                    if (p.S > 2) x ^= (x >> 4) & 0x0F0F0F0Fu & lim;
+                    if (p.S > 3) x ^= (x >> 8) & 0x00FF00FFu & lim;
+                    if (p.S > 4) x ^= (x >> 16) & 0x0000FFFFu;
+                    c.st(scr + w, x);
+                }
+                for (int d = 1; d < nbw; d <<= 1)
+                    for (int g = 0; g < nbw; g += 2 * d)
+                        for (int i = g; i < g + d; ++i)
+                            c.st(scr + i, c.ld(scr + i, (uint32_t)c.l) ^ c.ld(scr + i + d, (uint32_t)c.l));
+            }
+            owner = (uint32_t)c.l;
+            off = scr;
+        }
+        bool okp = false;
+        uint8_t* out_row = p.info + f * kb;
+        const SclBitsReader rd{ c, off, owner };
+        if (active) okp = extract_info_rd(rd, p.runs, p.nruns, p.K, out_row, p.crc, crc_table, false);
+        const unsigned bal = __ballot_sync(0xFFFFFFFFu, active && okp) & gmask;
+        const int first_lane = bal ? (__ffs(bal) - 1) : (__ffs(gmask) - 1); // absolute lane in the warp
+        if ((t & 31) == first_lane && live_frame) {
+            extract_info_rd(rd, p.runs, p.nruns, p.K, out_row, p.crc, crc_table, true);
+            if (p.ok) p.ok[f] = bal ? 1 : 0;
+        }
+        __syncwarp();
+    }
+}
+
+cudaError_t launch_scl_i8(const SclLaunch& L, const int8_t* d_llr, uint8_t* d_info, uint8_t* d_ok, size_t B, cudaStream_t st)
+{
+    SclParams p = L.p;
+    p.llr = d_llr;
+    p.info = d_info;
+    p.ok = d_ok;
+    p.B = B;
+    cudaError_t e = cudaFuncSetAttribute(k_scl_i8, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes);
+    if (e != cudaSuccess) return e;
+    const int gpc = L.threads / p.G;
+    size_t nb = (B + gpc - 1) / gpc;
+    const int grid = (int)(nb < (size_t)L.grid ? nb : (size_t)L.grid);
+    k_scl_i8<<<grid, L.threads, L.smem_bytes, st>>>(p);
+    return cudaGetLastError();
+}
+
+// host planner: per-lane word layout and CTA size
+int plan_scl_i8(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, SclLaunch& out, const char** msg)
+{
+    if (L < 1 || L > 32) {
+        *msg = "list size must be in [1, 32]";
+        return 1;
+    }
+    if (S > 17) {
+        *msg = "block length too large for the SCL kernel";
+        return 1;
+    }
+    int G = 1;
+    while (G < L) G <<= 1;
+    SclParams& p = out.p;
+    p.S = S;
+    p.K = K;
+    p.L = L;
+    p.G = G;
+    p.root_leaf = root_leaf ? 1 : 0;
+    int w = 0;
+    const int top_llr = root_leaf ? S : S - 1;
+    for (int s = 0; s < 20; ++s) p.llr_off[s] = p.bitL_off[s] = p.bitR_off[s] = 0;
+    for (int s = 0; s <= top_llr; ++s) {
+        p.llr_off[s] = w;
+        w += s >= 2 ? (1 << (s - 2)) : 1;
+    }
+    for (int s = 0; s <= S; ++s) {
+        const int bw = s >= 5 ? (1 << (s - 5)) : 1;
+        p.bitL_off[s] = w;
+        w += bw;
+        p.bitR_off[s] = w;
+        w += bw;
+    }
+    p.words = w;
+    const size_t per_lane = 4 * (size_t)w;
+    int T = 256;
+    while (T >= 32 && (1024 + per_lane * T > smem_max || T < G)) T -= 32;
+    if (T < 32 || T < G || 1024 + per_lane * T > smem_max) {
+        *msg = "SCL path state does not fit shared memory (block length too large for this list size)";
+        return 1;
+    }
+    T = (T / G) * G;
+    out.threads = T;
+    out.smem_bytes = 1024 + per_lane * T;
+    int per_sm = (int)((233472) / (out.smem_bytes + 1024));
+    if (per_sm < 1) per_sm = 1;
+    if (per_sm * T > 1024) per_sm = 1024 / T > 0 ? 1024 / T : 1;
+    out.grid = sms * per_sm;
+    return 0;
+}
+
+} // namespace pc

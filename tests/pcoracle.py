@@ -27,7 +27,8 @@ def lib():
     global _LIB
     if _LIB is None:
         so = os.path.join(ORACLE_DIR, "libpc_oracle.so")
-        if not os.path.exists(so):
+        srcs = [os.path.join(ORACLE_DIR, f) for f in ("pc_oracle.c", "pc_oracle_scl.c", "pc_oracle.h")]
+        if not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(f) for f in srcs):
             subprocess.check_call(["make", "-C", ORACLE_DIR, "restatement"])
         L = ctypes.CDLL(so)
         vp, ci, cf = ctypes.c_void_p, ctypes.c_int, ctypes.c_float
@@ -46,6 +47,8 @@ def lib():
         L.pco_crc_generate.argtypes = [ci, vp, ci]
         L.pco_crc_check.restype = ci
         L.pco_crc_check.argtypes = [ci, vp, ci]
+        L.pco_scl_i8_decode.restype = ci
+        L.pco_scl_i8_decode.argtypes = [ci, vp, ci, ci, ci, ci, vp, vp]
         _LIB = L
     return _LIB
 
@@ -137,3 +140,15 @@ def crc_check(kind, data):
     data2 = data.reshape(-1, data.shape[-1])
     return np.array([lib().pco_crc_check(kind, _p(data2[i]), data2.shape[1]) for i in range(data2.shape[0])],
                     dtype=np.uint8)
+
+
+def scl_i8_decode(N, frozen, L, llr, crc=8, systematic=True):
+    frozen = np.ascontiguousarray(frozen, dtype=np.uint32)
+    llr = np.ascontiguousarray(llr, dtype=np.int8).reshape(-1, N)
+    K = N - len(frozen)
+    out = np.zeros((llr.shape[0], (K + 7) // 8), dtype=np.uint8)
+    ok = np.zeros(llr.shape[0], dtype=np.uint8)
+    lb = lib()
+    for i in range(llr.shape[0]):
+        ok[i] = lb.pco_scl_i8_decode(N, _p(frozen), len(frozen), L, crc, int(systematic), _p(llr[i]), _p(out[i]))
+    return out, ok
