@@ -300,6 +300,14 @@ pc_code* pc_code_create(int N, const unsigned* frozen, int n_frozen, int kind, i
     if (st == PC_OK) st = upload(&c->d_info_mask, c->prog.info_mask);
     if (st == PC_OK) st = upload_crc(c);
     if (st == PC_OK) st = build_encoder_tables(c);
+    if (st == PC_OK && (kind == PC_DEC_FASTSSC_F32 || kind == PC_DEC_ADAPTIVE_F32)) {
+        if (!compile_fastssc_f32(N, frozen, n_frozen, c->f32_prog, &msg)) {
+            set_error(msg);
+            st = PC_ERR_ARG;
+        } else {
+            st = upload(&c->d_f32_code, c->f32_prog.code);
+        }
+    }
     if (st == PC_OK && (kind == PC_DEC_SCL_I8)) {
         if (!compile_scl(N, frozen, n_frozen, c->scl_prog, &msg)) {
             set_error(msg);
@@ -344,6 +352,9 @@ void pc_code_destroy(pc_code* c)
     cudaFree(c->d_chan_code);
     cudaFree(c->d_quant);
     cudaFree(c->d_scl_code);
+    cudaFree(c->d_f32_code);
+    cudaFree(c->f32_arena);
+    cudaFree(c->d_f32_in);
     cudaFree(c->arena);
     cudaFree(c->d_stage_in);
     cudaFree(c->d_stage_out);
@@ -361,6 +372,7 @@ int pc_code_set_crc(pc_code* c, int crc_kind)
     c->crc_kind = crc_kind;
     c->plan_valid = false;
     c->scl_plan_valid = false;
+    c->f32_plan_valid = false;
     return upload_crc(c);
 }
 
@@ -370,6 +382,7 @@ int pc_code_set_systematic(pc_code* c, int systematic)
     c->systematic = systematic ? 1 : 0;
     c->plan_valid = false;
     c->scl_plan_valid = false;
+    c->f32_plan_valid = false;
     return PC_OK;
 }
 

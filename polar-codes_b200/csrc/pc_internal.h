@@ -40,6 +40,15 @@ struct pc_code {
     uint32_t* d_scl_code = nullptr;
     pc::SclLaunch scl_plan;
     bool scl_plan_valid = false;
+    // fp32 Fast-SSC (kind PC_DEC_FASTSSC_F32, first pass of PC_DEC_ADAPTIVE_F32)
+    pc::FloatProgram f32_prog;
+    uint32_t* d_f32_code = nullptr;
+    pc::F32Launch f32_plan;
+    bool f32_plan_valid = false;
+    float* f32_arena = nullptr;
+    size_t f32_arena_bytes = 0;
+    void* d_f32_in = nullptr;         // float LLRs converted from an int8 batch
+    size_t f32_in_bytes = 0;
     // Fast-SSC launch plan
     pc::FastSscLaunch plan;
     bool plan_valid = false;

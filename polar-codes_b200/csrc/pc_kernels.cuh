@@ -62,6 +62,32 @@ struct SclLaunch {
 cudaError_t launch_scl_i8(const SclLaunch& L, const int8_t* d_llr, uint8_t* d_info, uint8_t* d_ok, size_t B, cudaStream_t st);
 int plan_scl_i8(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, SclLaunch& out, const char** msg);
 
+// ---- fp32 Fast-SSC (pc_fastssc_f32.cu) ----
+struct F32Params {
+    const float* llr;
+    uint8_t* info;
+    uint8_t* ok;
+    unsigned long long B;
+    int S, K, nruns, staged_root, systematic;
+    CrcSpec crc;
+    const uint32_t* code;
+    const uint32_t* runs;
+    const uint32_t* crc_table;
+    int llr_off[20];
+    int elems;     // floats per thread in the arena
+    int nbw;       // decision words per frame
+    size_t arena_stride; // threads the arena rows are laid out for
+    float* arena;  // [elems][arena_stride]
+    uint32_t* bits_arena; // [nbw][grid*threads]
+};
+
+struct F32Launch {
+    F32Params p;
+    int threads, grid;
+};
+cudaError_t launch_fastssc_f32(const F32Launch& L, const float* d_llr, uint8_t* d_info, uint8_t* d_ok, size_t B, cudaStream_t st);
+cudaError_t launch_i8_to_f32(const int8_t* d_in, float* d_out, size_t n, cudaStream_t st);
+
 cudaError_t const_pool_upload(int offset_words, const uint32_t* h_src, int nwords, cudaStream_t st);
 cudaError_t launch_fastssc_i8(const FastSscLaunch& L, const int8_t* d_llr, uint8_t* d_info, uint8_t* d_ok, size_t B,
                               cudaStream_t st);

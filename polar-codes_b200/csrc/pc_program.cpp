@@ -192,4 +192,98 @@ bool compile_scl(int N, const unsigned* frozen, int nf, SclProgram& out, const c
     return true;
 }
 
+namespace {
+// opcode values of pc_fastssc_f32_core.h (FOp)
+enum { F_F = 0, F_G = 1, F_G0 = 2, F_G1 = 3, F_COMB = 4, F_COMB0 = 5, F_R0 = 6, F_R1 = 7, F_REP = 8, F_SPC = 9, F_DREP = 10,
+       F_DSPC = 11, F_DSPC8 = 12, F_ZSPC = 13, F_ZSPC8 = 14, F_TREP = 15, F_T5 = 16, F_REPONE8 = 17, F_END = 18 };
+
+struct FBuilder {
+    FloatProgram& p;
+    bool bad = false;
+    void emit(uint32_t op, int s, unsigned off)
+    {
+        p.code.push_back(mk_instr(op, (uint32_t)s, off));
+        p.census[op]++;
+    }
+    static bool is_prefix(const std::vector<unsigned>& fz)
+    {
+        for (size_t i = 0; i < fz.size(); ++i)
+            if (fz[i] != i) return false;
+        return true;
+    }
+    void node(int s, unsigned off, const std::vector<unsigned>& fz)
+    {
+        const unsigned n = 1u << s, h = n >> 1;
+        const size_t nf = fz.size();
+        if (nf == n) return emit(F_R0, s, off);
+        if (nf == 0) return emit(F_R1, s, off);
+        if (nf == n - 1) return emit(F_REP, s, off);
+        if (nf == 1) return emit(F_SPC, s, off);
+        if (nf == n - 2) {
+            if (!is_prefix(fz)) bad = true;
+            return emit(F_DREP, s, off);
+        }
+        if (nf == 2 && fz[0] == 0 && fz[1] == 1) return emit(n == 8 ? F_DSPC8 : F_DSPC, s, off);
+        if (nf == n - 3 && n > 8 && fz[nf - 1] == n - 4) {
+            if (!is_prefix(fz)) bad = true;
+            return emit(F_TREP, s, off);
+        }
+        if (nf == n - 4 && fz[nf - 1] == n - 4 && fz[nf - 2] == n - 6) return emit(F_T5, s, off);
+        if (n == 8 && nf == 3 && fz[0] == 0 && fz[1] == 1 && fz[2] == 2) return emit(F_REPONE8, s, off);
+        if (n == 8 && nf == 5 && fz[nf - 1] == n - 4 && fz[nf - 2] == n - 5) return emit(F_ZSPC8, s, off);
+        std::vector<unsigned> lf, rf;
+        for (unsigned v : fz) {
+            if (v < h)
+                lf.push_back(v);
+            else
+                rf.push_back(v - h);
+        }
+        if (n > 8) {
+            if (lf.size() == h && rf.size() == 1) return emit(F_ZSPC, s, off);
+            if (rf.empty()) {
+                emit(F_F, s, off);
+                node(s - 1, off, lf);
+                return emit(F_G1, s, off);
+            }
+            if (lf.size() == h) {
+                emit(F_G0, s, off);
+                node(s - 1, off + h, rf);
+                return emit(F_COMB0, s, off);
+            }
+        }
+        emit(F_F, s, off);
+        node(s - 1, off, lf);
+        emit(F_G, s, off);
+        node(s - 1, off + h, rf);
+        emit(F_COMB, s, off);
+    }
+};
+} // namespace
+
+bool compile_fastssc_f32(int N, const unsigned* frozen, int nf, FloatProgram& out, const char** msg)
+{
+    int S = 0;
+    while ((1 << S) < N) S++;
+    if (N < 2 || (1 << S) != N || N > 65536) {
+        if (msg) *msg = "block length must be a power of two in [2, 65536]";
+        return false;
+    }
+    std::vector<unsigned> fz(frozen, frozen + nf);
+    std::sort(fz.begin(), fz.end());
+    out = FloatProgram();
+    out.N = N;
+    out.K = N - nf;
+    out.S = S;
+    FBuilder b{ out };
+    b.node(S, 0, fz);
+    b.emit(F_END, 0, 0);
+    if (b.bad) {
+        if (msg) *msg = "frozen pattern rejected by the float decoder (DoubleRepetition / TripleRepetition need a frozen prefix)";
+        return false;
+    }
+    const uint32_t rootop = instr_op(out.code[0]);
+    out.staged_root = !(rootop == F_F || rootop == F_G0);
+    return true;
+}
+
 } // namespace pc

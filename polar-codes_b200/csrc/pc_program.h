@@ -74,6 +74,17 @@ struct SclProgram {
 };
 bool compile_scl(int N, const unsigned* frozen, int nf, SclProgram& out, const char** msg);
 
+// fp32 Fast-SSC node program (FastSscAvx::createDecoder, src/polarcode/decoding/fastssc_avx_float.cpp:797-896);
+// opcodes FOp in pc_fastssc_f32_core.h. Fails like the reference (std::invalid_argument) on the frozen patterns its
+// DoubleRepetition / TripleRepetition checks reject.
+struct FloatProgram {
+    int N = 0, K = 0, S = 0;
+    bool staged_root = false;
+    std::vector<uint32_t> code;
+    int census[32] = { 0 };
+};
+bool compile_fastssc_f32(int N, const unsigned* frozen, int nf, FloatProgram& out, const char** msg);
+
 // returns false (and leaves msg) on invalid input
 bool compile_fastssc_i8(int N, const unsigned* frozen, int nf, FastSscProgram& out, const char** msg);
 

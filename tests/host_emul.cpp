@@ -7,6 +7,7 @@
 #include <cstring>
 #include <vector>
 
+#include "../polar-codes_b200/csrc/pc_fastssc_f32_core.h"
 #include "../polar-codes_b200/csrc/pc_fastssc_i8_core.h"
 #include "../polar-codes_b200/csrc/pc_program.h"
 
@@ -79,6 +80,53 @@ int emul_fastssc_i8_decode(int N, const unsigned* frozen, int nf, int systematic
                            long B, uint8_t* out, uint8_t* ok)
 {
     return emul_fastssc_i8_decode_mode(N, frozen, nf, systematic, crc_kind, llr, B, out, ok, 0);
+}
+
+// fp32 Fast-SSC core on the host (one emulated thread); returns 0 on success, 3 when the frozen pattern is rejected
+int emul_fastssc_f32_decode(int N, const unsigned* frozen, int nf, int systematic, int crc_kind, const float* llr, long B,
+                            uint8_t* out, uint8_t* ok)
+{
+    FloatProgram fp;
+    FastSscProgram ip; // gather runs
+    const char* msg = nullptr;
+    if (!compile_fastssc_f32(N, frozen, nf, fp, &msg)) return 3;
+    if (!compile_fastssc_i8(N, frozen, nf, ip, &msg)) return 1;
+    CrcSpec crc;
+    if (!crc_spec(crc_kind, crc)) return 2;
+    uint32_t table[256];
+    crc_build_table(crc, table);
+    const int S = fp.S;
+    std::vector<int> off(S + 2, 0);
+    int w = 0;
+    for (int s = 0; s <= S; ++s) {
+        off[s] = w;
+        w += 1 << s;
+    }
+    std::vector<float> llrs(w + 8);
+    std::vector<uint32_t> bits((N + 31) / 32 + 1);
+    const int kb = (fp.K + 7) / 8;
+    std::vector<uint8_t> outrow(kb + 8);
+    for (long i = 0; i < B; ++i) {
+        FCtx c;
+        c.S = S;
+        c.llr_off = off.data();
+        c.llr = llrs.data();
+        c.ls = 1;
+        c.bits = bits.data();
+        c.bs = 1;
+        std::fill(bits.begin(), bits.end(), 0u);
+        fastssc_f32_run(c, fp.code.data(), llr + i * N, fp.staged_root);
+        Ctx ic; // reuse the int8 core's bit transform / gather on the same decision words
+        ic.S = S;
+        ic.bits_kind = PK_SMEM;
+        ic.bits = bits.data();
+        ic.bws = 1;
+        if (!systematic) transform_bits_inplace(ic);
+        bool res = extract_info(ic, ip.runs.data(), (int)ip.runs.size(), ip.K, outrow.data(), crc, table);
+        memcpy(out + i * kb, outrow.data(), kb);
+        if (ok) ok[i] = res ? 1 : 0;
+    }
+    return 0;
 }
 
 int emul_program(int N, const unsigned* frozen, int nf, uint32_t* code, int cap)
