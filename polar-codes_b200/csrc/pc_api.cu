@@ -316,6 +316,14 @@ pc_code* pc_code_create(int N, const unsigned* frozen, int n_frozen, int kind, i
             st = upload(&c->d_scl_code, c->scl_prog.code);
         }
     }
+    if (st == PC_OK && (kind == PC_DEC_SCL_F32 || (kind == PC_DEC_ADAPTIVE_F32 && L > 1))) {
+        if (!compile_scl(N, frozen, n_frozen, c->sclf_prog, &msg, true)) {
+            set_error(msg);
+            st = PC_ERR_ARG;
+        } else {
+            st = upload(&c->d_sclf_code, c->sclf_prog.code);
+        }
+    }
     if (st == PC_OK) {
         const int words = (int)(c->prog.code.size() + c->prog.runs.size());
         int off = pool_alloc(words);
@@ -353,6 +361,11 @@ void pc_code_destroy(pc_code* c)
     cudaFree(c->d_quant);
     cudaFree(c->d_scl_code);
     cudaFree(c->d_f32_code);
+    cudaFree(c->d_sclf_code);
+    cudaFree(c->sclf_arena);
+    cudaFree(c->d_fail_idx);
+    cudaFree(c->d_fail_count);
+    cudaFree(c->d_ok_tmp);
     cudaFree(c->f32_arena);
     cudaFree(c->d_f32_in);
     cudaFree(c->arena);
@@ -373,6 +386,7 @@ int pc_code_set_crc(pc_code* c, int crc_kind)
     c->plan_valid = false;
     c->scl_plan_valid = false;
     c->f32_plan_valid = false;
+    c->sclf_plan_valid = false;
     return upload_crc(c);
 }
 
@@ -383,6 +397,7 @@ int pc_code_set_systematic(pc_code* c, int systematic)
     c->plan_valid = false;
     c->scl_plan_valid = false;
     c->f32_plan_valid = false;
+    c->sclf_plan_valid = false;
     return PC_OK;
 }
 

@@ -40,6 +40,19 @@ struct pc_code {
     uint32_t* d_scl_code = nullptr;
     pc::SclLaunch scl_plan;
     bool scl_plan_valid = false;
+    // SCL fp32 (kind PC_DEC_SCL_F32, second pass of PC_DEC_ADAPTIVE_F32)
+    pc::SclProgram sclf_prog;
+    uint32_t* d_sclf_code = nullptr;
+    pc::SclFLaunch sclf_plan;
+    bool sclf_plan_valid = false;
+    float* sclf_arena = nullptr;
+    size_t sclf_arena_bytes = 0;
+    // adaptive: frames whose first pass failed (index list + count on the device)
+    void* d_fail_idx = nullptr;
+    size_t fail_idx_bytes = 0;
+    unsigned long long* d_fail_count = nullptr;
+    void* d_ok_tmp = nullptr;
+    size_t ok_tmp_bytes = 0;
     // fp32 Fast-SSC (kind PC_DEC_FASTSSC_F32, first pass of PC_DEC_ADAPTIVE_F32)
     pc::FloatProgram f32_prog;
     uint32_t* d_f32_code = nullptr;

@@ -62,6 +62,38 @@ struct SclLaunch {
 cudaError_t launch_scl_i8(const SclLaunch& L, const int8_t* d_llr, uint8_t* d_info, uint8_t* d_ok, size_t B, cudaStream_t st);
 int plan_scl_i8(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, SclLaunch& out, const char** msg);
 
+// ---- SCL fp32 (pc_scl_f32.cu) ----
+struct SclFParams {
+    const float* llr;
+    uint8_t* info;
+    uint8_t* ok;
+    unsigned long long B;
+    const unsigned* frame_idx;         // optional indirection (adaptive second pass): frame = frame_idx[i]
+    const unsigned long long* count;   // optional device-side frame count (overrides B when non-null)
+    int S, K, L, G, nruns, systematic, root_leaf;
+    CrcSpec crc;
+    const uint32_t* code;
+    const uint32_t* runs;
+    const uint32_t* crc_table;
+    int smem_top;     // LLR stages s <= smem_top live in shared memory, larger ones in the arena
+    int llr_off[20];  // word offset (shared memory) or element offset (arena) of LLR stage s in a lane's space
+    int bitL_off[20]; // word offset of the left / right decision buffer of stage s (shared memory)
+    int bitR_off[20];
+    int words;        // shared-memory words per lane
+    int arena_elems;  // arena floats per lane
+    size_t arena_stride; // lanes the arena rows are laid out for (grid * threads)
+    float* arena;     // [arena_elems][arena_stride]
+};
+struct SclFLaunch {
+    SclFParams p;
+    int threads, grid;
+    size_t smem_bytes;
+};
+cudaError_t launch_scl_f32(const SclFLaunch& L, const float* d_llr, uint8_t* d_info, uint8_t* d_ok, size_t B,
+                           const unsigned* d_frame_idx, const unsigned long long* d_count, cudaStream_t st);
+cudaError_t launch_compact_failed(const uint8_t* d_ok, size_t B, unsigned* d_idx, unsigned long long* d_count, cudaStream_t st);
+int plan_scl_f32(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, SclFLaunch& out, const char** msg);
+
 // ---- fp32 Fast-SSC (pc_fastssc_f32.cu) ----
 struct F32Params {
     const float* llr;

@@ -138,7 +138,7 @@ bool compile_fastssc_i8(int N, const unsigned* frozen, int nf, FastSscProgram& o
 
 
 namespace {
-void scl_node(SclProgram& p, int s, uint32_t side, const std::vector<unsigned>& fz)
+void scl_node(SclProgram& p, int s, uint32_t side, const std::vector<unsigned>& fz, bool float_rules)
 {
     const unsigned n = 1u << s, h = n >> 1;
     const size_t nf = fz.size();
@@ -147,7 +147,7 @@ void scl_node(SclProgram& p, int s, uint32_t side, const std::vector<unsigned>& 
         leaf = SCL_R0;
     else if (nf == 0)
         leaf = SCL_R1;
-    else if (nf == n - 1)
+    else if (nf == n - 1 && (!float_rules || n < 8)) // SclAvx builds REP leaves only below one vector (scl_avx_float.cpp:637-639)
         leaf = SCL_REP;
     else if (nf == 1)
         leaf = SCL_SPC;
@@ -164,15 +164,15 @@ void scl_node(SclProgram& p, int s, uint32_t side, const std::vector<unsigned>& 
             rf.push_back(v - h);
     }
     p.code.push_back(scl_instr(SCL_F, (uint32_t)s, side));
-    scl_node(p, s - 1, 0, lf);
+    scl_node(p, s - 1, 0, lf, float_rules);
     p.code.push_back(scl_instr(SCL_G, (uint32_t)s, side));
-    scl_node(p, s - 1, 1, rf);
+    scl_node(p, s - 1, 1, rf, float_rules);
     p.code.push_back(scl_instr(SCL_COMB, (uint32_t)s, side));
     p.census[SCL_F]++;
 }
 } // namespace
 
-bool compile_scl(int N, const unsigned* frozen, int nf, SclProgram& out, const char** msg)
+bool compile_scl(int N, const unsigned* frozen, int nf, SclProgram& out, const char** msg, bool float_rules)
 {
     int S = 0;
     while ((1 << S) < N) S++;
@@ -186,7 +186,7 @@ bool compile_scl(int N, const unsigned* frozen, int nf, SclProgram& out, const c
     out.N = N;
     out.K = N - nf;
     out.S = S;
-    scl_node(out, S, 1, fz);
+    scl_node(out, S, 1, fz, float_rules);
     out.root_leaf = instr_op(out.code[0]) != SCL_F;
     out.code.push_back(scl_instr(SCL_END, 0, 0));
     return true;

@@ -72,7 +72,8 @@ struct SclProgram {
     std::vector<uint32_t> code;
     int census[8] = { 0 };
 };
-bool compile_scl(int N, const unsigned* frozen, int nf, SclProgram& out, const char** msg);
+// float_rules: the leaf set of SclAvx::createDecoder (scl_avx_float.cpp:624-651): REP leaves only for n < 8
+bool compile_scl(int N, const unsigned* frozen, int nf, SclProgram& out, const char** msg, bool float_rules = false);
 
 // fp32 Fast-SSC node program (FastSscAvx::createDecoder, src/polarcode/decoding/fastssc_avx_float.cpp:797-896);
 // opcodes FOp in pc_fastssc_f32_core.h. Fails like the reference (std::invalid_argument) on the frozen patterns its

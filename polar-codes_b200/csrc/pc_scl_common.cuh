@@ -1,0 +1,225 @@
+// Pieces shared by the two SCL kernels (pc_scl_i8.cu: SclFipChar, pc_scl_f32.cu: SclAvxFloat): the per-lane owner
+// tables that replace the reference's ref-counted block tree, the emulated selection sort over candidate metrics,
+// and the decision-bit steps (combine, take-with-flips, fork), which are identical for both LLR types because hard
+// decisions are one bit per element in both kernels.
+//
+// A "lane type" LN provides: sm/T/G/l/P, metric, own_llr/own_L/own_R, ld(word, owner) and st(word, value) on the
+// lane's shared-memory words. A "params type" PR provides bitL_off[] / bitR_off[] / L.
+#ifndef PC_SCL_COMMON_CUH
+#define PC_SCL_COMMON_CUH
+#include <limits.h>
+#include <stdint.h>
+
+namespace pc {
+
+struct Tbl { // 5-bit owner lane per stage
+    uint32_t w[3];
+    __device__ __forceinline__ uint32_t get(int s) const
+    {
+        const uint32_t v = s < 6 ? w[0] : (s < 12 ? w[1] : w[2]);
+        return (v >> (5 * (s % 6))) & 31u;
+    }
+    __device__ __forceinline__ void set(int s, uint32_t lane)
+    {
+        const uint32_t sh = 5u * (uint32_t)(s % 6), m = ~(31u << sh), b = lane << sh;
+        if (s < 6)
+            w[0] = (w[0] & m) | b;
+        else if (s < 12)
+            w[1] = (w[1] & m) | b;
+        else
+            w[2] = (w[2] & m) | b;
+    }
+    __device__ __forceinline__ void copy_from(const Tbl& o, int src, int width)
+    {
+        w[0] = __shfl_sync(0xFFFFFFFFu, o.w[0], src, width);
+        w[1] = __shfl_sync(0xFFFFFFFFu, o.w[1], src, width);
+        w[2] = __shfl_sync(0xFFFFFFFFu, o.w[2], src, width);
+    }
+};
+
+__device__ __forceinline__ int stage_bwords(int s) { return s >= 5 ? (1 << (s - 5)) : 1; } // decision words
+
+// ---- register-array helpers (dynamic index -> predicated selects) ---------------------------------
+template <class V, int C>
+__device__ __forceinline__ V sel(const V (&v)[C], int k)
+{
+    V r = v[0];
+#pragma unroll
+    for (int i = 1; i < C; ++i) r = (k == i) ? v[i] : r;
+    return r;
+}
+template <class V, int C>
+__device__ __forceinline__ void put(V (&v)[C], int k, V x)
+{
+#pragma unroll
+    for (int i = 0; i < C; ++i) v[i] = (k == i) ? x : v[i];
+}
+
+// simplePartialSortDescending (reference include/polarcode/arrayfuncs.h:161-183) over the C * P candidate metrics
+// held C per lane (position = lane * C + k), emulated pass by pass: pass i takes the FIRST maximum of positions
+// [i, size) (strict '>'), then swaps values and indices of positions i and max. Returns Values[j] / Indices[j] for
+// the caller's new path j = lane. V is int (SclFipChar's long metrics fit easily) or float (SclAvxFloat).
+template <int C, class V, class LN>
+__device__ __forceinline__ void scl_sort(const LN& c, V (&v)[C], int newP, V& out_val, int& out_idx)
+{
+    const int size = C * c.P, G = c.G;
+    int idx[C];
+#pragma unroll
+    for (int k = 0; k < C; ++k) idx[k] = c.l * C + k;
+    const int lim = size - 1 < newP ? size - 1 : newP;
+    for (int i = 0; i < lim; ++i) {
+        V bv = v[0];
+        int bp = INT_MAX;
+#pragma unroll
+        for (int k = 0; k < C; ++k) {
+            const int pos = c.l * C + k;
+            if (pos >= i && pos < size && (bp == INT_MAX || v[k] > bv)) {
+                bv = v[k];
+                bp = pos;
+            }
+        }
+        for (int off = G >> 1; off; off >>= 1) {
+            const V ov = __shfl_xor_sync(0xFFFFFFFFu, bv, off);
+            const int op = __shfl_xor_sync(0xFFFFFFFFu, bp, off);
+            if (op != INT_MAX && (bp == INT_MAX || ov > bv || (ov == bv && op < bp))) {
+                bv = ov;
+                bp = op;
+            }
+        }
+        const int li = i / C, ki = i % C, lm = bp / C, km = bp % C;
+        const V vi = __shfl_sync(0xFFFFFFFFu, sel(v, ki), li, G);
+        const int ii = __shfl_sync(0xFFFFFFFFu, sel(idx, ki), li, G);
+        const int im = __shfl_sync(0xFFFFFFFFu, sel(idx, km), lm, G);
+        if (c.l == lm) {
+            put(v, km, vi);
+            put(idx, km, ii);
+        }
+        if (c.l == li) {
+            put(v, ki, bv);
+            put(idx, ki, im);
+        }
+    }
+    const int lj = (c.l / C) & (G - 1), kj = c.l % C;
+    out_val = v[0];
+    out_idx = 0;
+#pragma unroll
+    for (int k = 0; k < C; ++k) {
+        const V tv = __shfl_sync(0xFFFFFFFFu, v[k], lj, G);
+        const int ti = __shfl_sync(0xFFFFFFFFu, idx[k], lj, G);
+        if (kj == k) {
+            out_val = tv;
+            out_idx = ti;
+        }
+    }
+}
+
+// Indices[] bookkeeping of findWeakLlrs (arrayfuncs.h:209-231): the first four entries plus a patch list for
+// positions >= 4 (at most four swaps happen). swap(i, bp) is called once per pass with i < 4.
+struct WeakIdx {
+    int I[4], ppos[4], pidx[4], np;
+    __device__ __forceinline__ void init()
+    {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            I[k] = k;
+            ppos[k] = -1;
+            pidx[k] = 0;
+        }
+        np = 0;
+    }
+    __device__ __forceinline__ void swap(int i, int bp)
+    {
+        int im = bp;
+        if (bp < 4) {
+            im = sel(I, bp);
+        } else {
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+                if (q < np && ppos[q] == bp) im = pidx[q]; // later patches override earlier ones
+        }
+        const int ii = sel(I, i);
+        put(I, i, im);
+        if (bp < 4) {
+            if (bp != i) put(I, bp, ii);
+        } else {
+            put(ppos, np, bp);
+            put(pidx, np, ii);
+            np++;
+        }
+    }
+};
+
+template <class LN>
+__device__ __forceinline__ void set_side(LN& c, int s, int side)
+{
+    if (side)
+        c.own_R.set(s, (uint32_t)c.l);
+    else
+        c.own_L.set(s, (uint32_t)c.l);
+}
+
+// CombineBits (fip_char.h:173-207, avx_float.h:203-236): decisions(s, side) = [left ^ right, right] of stage s-1
+template <class LN, class PR>
+__device__ __forceinline__ void scl_comb(LN& c, const PR& p, int s, int side)
+{
+    const bool active = c.l < c.P;
+    const int h = 1 << (s - 1);
+    const uint32_t ol = c.own_L.get(s - 1), orr = c.own_R.get(s - 1);
+    const int lo = p.bitL_off[s - 1], ro = p.bitR_off[s - 1], dst = side ? p.bitR_off[s] : p.bitL_off[s];
+    if (active) {
+        if (h >= 32) {
+            const int hw = h >> 5;
+            for (int j = 0; j < hw; ++j) {
+                const uint32_t a = c.ld(lo + j, ol), b = c.ld(ro + j, orr);
+                c.st(dst + j, a ^ b);
+                c.st(dst + hw + j, b);
+            }
+        } else {
+            const uint32_t m = (1u << h) - 1u;
+            const uint32_t a = c.ld(lo, ol) & m, b = c.ld(ro, orr) & m;
+            c.st(dst, (a ^ b) | (b << h));
+        }
+    }
+    set_side(c, s, side);
+}
+
+// the new path in this lane takes the decisions of old path `sp` (stored in lane sp's side buffer) with the
+// elements listed in fmask (bit q -> index fi[q]) flipped
+template <class LN, class PR>
+__device__ __forceinline__ void scl_take_bits(const LN& c, const PR& p, int s, int side, int sp, bool live, int fmask,
+                                              const int (&fi)[4])
+{
+    const int nb = stage_bwords(s), dst = side ? p.bitR_off[s] : p.bitL_off[s];
+    for (int w = 0; w < nb; ++w) {
+        uint32_t t = c.ld(dst + w, (uint32_t)sp);
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+            if (((fmask >> q) & 1) && (fi[q] >> 5) == w) t ^= 1u << (fi[q] & 31);
+        __syncwarp();
+        if (live) c.st(dst + w, t);
+    }
+    __syncwarp();
+}
+
+// duplicatePath + switchToNext (scl_fip_char.cpp:55-63,91-98): 9 shuffles instead of ref-count updates
+template <class LN, class V>
+__device__ __forceinline__ void scl_fork(LN& c, int sp, V val, int newP)
+{
+    Tbl a = c.own_llr, b = c.own_L, d = c.own_R;
+    c.own_llr.copy_from(a, sp, c.G);
+    c.own_L.copy_from(b, sp, c.G);
+    c.own_R.copy_from(d, sp, c.G);
+    c.metric = val;
+    c.P = newP;
+}
+
+template <class LN>
+struct SclBitsReader {
+    const LN& c;
+    int off;
+    uint32_t owner;
+    __device__ __forceinline__ uint32_t operator()(int word) const { return c.ld(off + word, owner); }
+};
+
+} // namespace pc
+#endif

@@ -19,33 +19,9 @@
 // lanes' buffers are read at their tid.
 #include "pc_fastssc_i8_core.h"
 #include "pc_kernels.cuh"
+#include "pc_scl_common.cuh"
 
 namespace pc {
-
-struct Tbl { // 5-bit owner lane per stage
-    uint32_t w[3];
-    __device__ __forceinline__ uint32_t get(int s) const
-    {
-        const uint32_t v = s < 6 ? w[0] : (s < 12 ? w[1] : w[2]);
-        return (v >> (5 * (s % 6))) & 31u;
-    }
-    __device__ __forceinline__ void set(int s, uint32_t lane)
-    {
-        const uint32_t sh = 5u * (uint32_t)(s % 6), m = ~(31u << sh), b = lane << sh;
-        if (s < 6)
-            w[0] = (w[0] & m) | b;
-        else if (s < 12)
-            w[1] = (w[1] & m) | b;
-        else
-            w[2] = (w[2] & m) | b;
-    }
-    __device__ __forceinline__ void copy_from(const Tbl& o, int src, int width)
-    {
-        w[0] = __shfl_sync(0xFFFFFFFFu, o.w[0], src, width);
-        w[1] = __shfl_sync(0xFFFFFFFFu, o.w[1], src, width);
-        w[2] = __shfl_sync(0xFFFFFFFFu, o.w[2], src, width);
-    }
-};
 
 struct Lane {
     uint32_t* sm;   // smem base + tid (word w at sm[w * T])
@@ -58,7 +34,6 @@ struct Lane {
 };
 
 __device__ __forceinline__ int stage_words(int s) { return s >= 2 ? (1 << (s - 2)) : 1; }   // LLR words
-__device__ __forceinline__ int stage_bwords(int s) { return s >= 5 ? (1 << (s - 5)) : 1; }  // decision words
 __device__ __forceinline__ uint32_t bytemask(int nbytes) { return nbytes >= 4 ? 0xFFFFFFFFu : ((1u << (8 * nbytes)) - 1u); }
 
 // f / g step of a node of size 2^s: parent LLRs (stage s, through the owner table or the channel row) -> child
@@ -101,33 +76,6 @@ __device__ __forceinline__ void scl_fg(Lane& c, const SclParams& p, int s, const
     c.own_llr.set(s - 1, (uint32_t)c.l);
 }
 
-// CombineBits (fip_char.h:173-207): decisions(s, side) = [left ^ right, right] of stage s-1
-__device__ __forceinline__ void scl_comb(Lane& c, const SclParams& p, int s, int side)
-{
-    const bool active = c.l < c.P;
-    const int h = 1 << (s - 1);
-    const uint32_t ol = c.own_L.get(s - 1), orr = c.own_R.get(s - 1);
-    const int lo = p.bitL_off[s - 1], ro = p.bitR_off[s - 1], dst = side ? p.bitR_off[s] : p.bitL_off[s];
-    if (active) {
-        if (h >= 32) {
-            const int hw = h >> 5;
-            for (int j = 0; j < hw; ++j) {
-                const uint32_t a = c.ld(lo + j, ol), b = c.ld(ro + j, orr);
-                c.st(dst + j, a ^ b);
-                c.st(dst + hw + j, b);
-            }
-        } else {
-            const uint32_t m = (1u << h) - 1u;
-            const uint32_t a = c.ld(lo, ol) & m, b = c.ld(ro, orr) & m;
-            c.st(dst, (a ^ b) | (b << h));
-        }
-    }
-    if (side)
-        c.own_R.set(s, (uint32_t)c.l);
-    else
-        c.own_L.set(s, (uint32_t)c.l);
-}
-
 // sums of the negative / positive LLRs of the own stage-s buffer (exact integer sums, dp4a)
 __device__ __forceinline__ void llr_sums(const Lane& c, const SclParams& p, int s, int& neg, int& pos)
 {
@@ -143,14 +91,6 @@ __device__ __forceinline__ void llr_sums(const Lane& c, const SclParams& p, int 
     }
 }
 
-__device__ __forceinline__ void set_side(Lane& c, int s, int side)
-{
-    if (side)
-        c.own_R.set(s, (uint32_t)c.l);
-    else
-        c.own_L.set(s, (uint32_t)c.l);
-}
-
 // RateZeroDecoder::decode scl_fip_char.cpp:387-421: metric += sum(min(llr, 0)), decisions 0, no fork, no re-sort
 __device__ __forceinline__ void scl_r0(Lane& c, const SclParams& p, int s, int side)
 {
@@ -162,76 +102,6 @@ __device__ __forceinline__ void scl_r0(Lane& c, const SclParams& p, int s, int s
         for (int j = 0; j < nb; ++j) c.st(dst + j, 0u);
     }
     set_side(c, s, side);
-}
-
-// ---- register-array helpers (dynamic index -> predicated selects) ---------------------------------
-template <int C>
-__device__ __forceinline__ int sel(const int (&v)[C], int k)
-{
-    int r = v[0];
-#pragma unroll
-    for (int i = 1; i < C; ++i) r = (k == i) ? v[i] : r;
-    return r;
-}
-template <int C>
-__device__ __forceinline__ void put(int (&v)[C], int k, int x)
-{
-#pragma unroll
-    for (int i = 0; i < C; ++i) v[i] = (k == i) ? x : v[i];
-}
-
-// simplePartialSortDescending (reference include/polarcode/arrayfuncs.h:161-183) over the C * P candidate metrics
-// held C per lane (position = lane * C + k), emulated pass by pass: pass i takes the FIRST maximum of positions
-// [i, size) (strict '>'), then swaps values and indices of positions i and max. Returns Values[j] / Indices[j] for
-// the caller's new path j = lane.
-template <int C>
-__device__ __forceinline__ void scl_sort(const Lane& c, int (&v)[C], int newP, int& out_val, int& out_idx)
-{
-    const int size = C * c.P, G = c.G;
-    int idx[C];
-#pragma unroll
-    for (int k = 0; k < C; ++k) idx[k] = c.l * C + k;
-    const int lim = size - 1 < newP ? size - 1 : newP;
-    for (int i = 0; i < lim; ++i) {
-        int bv = INT_MIN, bp = INT_MAX;
-#pragma unroll
-        for (int k = 0; k < C; ++k) {
-            const int pos = c.l * C + k;
-            if (pos >= i && pos < size && (bp == INT_MAX || v[k] > bv)) {
-                bv = v[k];
-                bp = pos;
-            }
-        }
-        for (int off = G >> 1; off; off >>= 1) {
-            const int ov = __shfl_xor_sync(0xFFFFFFFFu, bv, off), op = __shfl_xor_sync(0xFFFFFFFFu, bp, off);
-            if (op != INT_MAX && (bp == INT_MAX || ov > bv || (ov == bv && op < bp))) {
-                bv = ov;
-                bp = op;
-            }
-        }
-        const int li = i / C, ki = i % C, lm = bp / C, km = bp % C;
-        const int vi = __shfl_sync(0xFFFFFFFFu, sel(v, ki), li, G), ii = __shfl_sync(0xFFFFFFFFu, sel(idx, ki), li, G);
-        const int im = __shfl_sync(0xFFFFFFFFu, sel(idx, km), lm, G);
-        if (c.l == lm) {
-            put(v, km, vi);
-            put(idx, km, ii);
-        }
-        if (c.l == li) {
-            put(v, ki, bv);
-            put(idx, ki, im);
-        }
-    }
-    const int lj = (c.l / C) & (G - 1), kj = c.l % C;
-    out_val = 0;
-    out_idx = 0;
-#pragma unroll
-    for (int k = 0; k < C; ++k) {
-        const int tv = __shfl_sync(0xFFFFFFFFu, v[k], lj, G), ti = __shfl_sync(0xFFFFFFFFu, idx[k], lj, G);
-        if (kj == k) {
-            out_val = tv;
-            out_idx = ti;
-        }
-    }
 }
 
 // findWeakLlrs (arrayfuncs.h:209-231) on the |LLR| bytes stored in place in the own stage buffer: `want` passes of
@@ -310,34 +180,6 @@ __device__ __forceinline__ uint32_t scl_signs_and_abs(const Lane& c, const SclPa
         }
     }
     return par;
-}
-
-// second phase: the new path in this lane takes the decisions of old path `sp` (stored in lane sp's side buffer)
-// with the bytes listed in fmask (bit q -> index fi[q]) flipped (`~` in the reference, i.e. the sign always flips)
-__device__ __forceinline__ void scl_take_bits(const Lane& c, const SclParams& p, int s, int side, int sp, bool live,
-                                              int fmask, const int (&fi)[4])
-{
-    const int nb = stage_bwords(s), dst = side ? p.bitR_off[s] : p.bitL_off[s];
-    for (int w = 0; w < nb; ++w) {
-        uint32_t t = c.ld(dst + w, (uint32_t)sp);
-#pragma unroll
-        for (int q = 0; q < 4; ++q)
-            if (((fmask >> q) & 1) && (fi[q] >> 5) == w) t ^= 1u << (fi[q] & 31);
-        __syncwarp();
-        if (live) c.st(dst + w, t);
-    }
-    __syncwarp();
-}
-
-// duplicatePath + switchToNext (scl_fip_char.cpp:55-63,91-98): 9 shuffles instead of ref-count updates
-__device__ __forceinline__ void scl_fork(Lane& c, int sp, int val, int newP)
-{
-    Tbl a = c.own_llr, b = c.own_L, d = c.own_R;
-    c.own_llr.copy_from(a, sp, c.G);
-    c.own_L.copy_from(b, sp, c.G);
-    c.own_R.copy_from(d, sp, c.G);
-    c.metric = val;
-    c.P = newP;
 }
 
 // RepetitionDecoder::decode scl_fip_char.cpp:508-581
@@ -436,13 +278,6 @@ __device__ __forceinline__ void scl_spc(Lane& c, const SclParams& p, int s, int 
     set_side(c, s, side);
 }
 
-struct SclBitsReader {
-    const Lane& c;
-    int off;
-    uint32_t owner;
-    __device__ __forceinline__ uint32_t operator()(int word) const { return c.ld(off + word, owner); }
-};
-
 __global__ void __launch_bounds__(256) k_scl_i8(const __grid_constant__ SclParams p)
 {
     extern __shared__ __align__(16) uint32_t smem[];
@@ -524,7 +359,7 @@ __global__ void __launch_bounds__(256) k_scl_i8(const __grid_constant__ SclParam
         }
         bool okp = false;
         uint8_t* out_row = p.info + f * kb;
-        const SclBitsReader rd{ c, off, owner };
+        const SclBitsReader<Lane> rd{ c, off, owner };
         if (active) okp = extract_info_rd(rd, p.runs, p.nruns, p.K, out_row, p.crc, crc_table, false);
         const unsigned bal = __ballot_sync(0xFFFFFFFFu, active && okp) & gmask;
         const int first_lane = bal ? (__ffs(bal) - 1) : (__ffs(gmask) - 1); // absolute lane in the warp

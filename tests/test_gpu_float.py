@@ -59,3 +59,77 @@ def test_float_kat_n8(pcb):
     dec = pcb.PolarDecoder(8, 1, [0, 1, 2, 4], "float")
     out = dec.decode_vector(np.array([-5, -6, -4, 1, -4, -5, -7, 2], dtype=np.float32))
     assert (out[0] & 0xF0) == 0xF0
+
+
+# ---- SCL fp32 (SclAvxFloat) and the adaptive 'mixed' decoder (AdaptiveFloat) -------------------------------------------
+def _tx_float_llrs(ref, rng, N, K, fz, crc_bits, crc_type, B):
+    """transmitted codewords (so that the detector passes on some list path) at three noise levels, as float LLRs in
+    pcsim's scaling, integer-valued (exact metric ties) and very coarse (zeros and ties everywhere)"""
+    info = rng.integers(0, 256, (B, (K + 7) // 8), dtype=np.uint8)
+    if K % 8:
+        info[:, -1] &= (0xFF00 >> (K % 8)) & 0xFF
+    code, _ = ref.encode_batch(N, fz, info, crc_bits=crc_bits, crc_type=crc_type)
+    x = 1.0 - 2.0 * np.unpackbits(code, axis=1, bitorder="big")[:, :N].astype(np.float32)
+    out = []
+    for sigma, scale, rint in ((0.7, 4.0, False), (0.9, 10.0, True), (1.0, 2.0, True), (0.5, 3.0, False)):
+        y = (x + sigma * rng.standard_normal((B, N))).astype(np.float32) * np.float32(scale)
+        out.append(np.rint(y).astype(np.float32) if rint else y.astype(np.float32))
+    return np.concatenate(out)
+
+
+SCLF = [(64, 40, 4, 8, "crc"), (512, 128, 8, 24, "crc"), (1024, 512, 8, 16, "crc"), (8, 4, 4, 8, "crc"),
+        (1024, 512, 32, 16, "crc"), (256, 128, 2, 0, "crc"), (128, 64, 16, 8, "crc"), (32, 16, 8, 6, "crc"),
+        (2048, 1024, 4, 16, "crcnr"), (256, 200, 3, 8, "crc"), (16, 8, 32, 8, "crc"), (1024, 768, 8, 32, "crc"),
+        (4096, 2048, 2, 11, "crc")]
+
+
+@pytest.mark.parametrize("N,K,L,crc_bits,crc_type", SCLF)
+def test_scl_float_parity(pcb, ref, N, K, L, crc_bits, crc_type):
+    rng = np.random.default_rng(7 * N + K + L)
+    fz = ref.frozen_bits(N, K, 0.0)
+    B = 128 if L <= 8 and N <= 1024 else 32
+    llr = _tx_float_llrs(ref, rng, N, K, fz, crc_bits, crc_type, B)
+    dec = pcb.PolarDecoder(N, L, list(fz), "float")
+    dec.setErrorDetection(crc_bits, crc_type)
+    got, ok = dec.decode_batch(llr, return_ok=True)
+    exp, eok = ref.decode_batch(N, L, fz, "float", llr, crc_bits=crc_bits, crc_type=crc_type)
+    assert _agree(got, exp) >= MIN_FRAME_AGREEMENT
+    bad = (got != exp).any(axis=1)
+    assert not bad.any(), f"{bad.sum()} of {len(bad)} frames differ (first {np.flatnonzero(bad)[:5]})"
+    assert np.array_equal(ok, eok)
+
+
+@pytest.mark.parametrize("N,K,L,dsnr", [(64, 40, 4, 1.0), (1024, 512, 8, 0.0), (512, 128, 8, 0.0), (256, 128, 1, 0.0)])
+def test_adaptive_mixed_parity(pcb, ref, N, K, L, dsnr):
+    """configs[0]: README pypolar case N=64 K=40 (BB, 1.0 dB), L=4 'mixed'; AdaptiveFloat adaptive_float.cpp:33-45"""
+    rng = np.random.default_rng(N + K + L)
+    fz = ref.frozen_bits(N, K, dsnr)
+    llr = _tx_float_llrs(ref, rng, N, K, fz, 8, "crc", 256)
+    dec = pcb.PolarDecoder(N, L, list(fz), "mixed")
+    got, ok = dec.decode_batch(llr, return_ok=True)
+    exp, eok = ref.decode_batch(N, L, fz, "mixed", llr)
+    assert N not in (64, 1024) or 0 < ok.mean() < 1  # both passes are exercised
+    assert np.array_equal(got, exp) and np.array_equal(ok, eok)
+    # ragged batch sizes and the non-systematic flavour
+    for B in (1, 33):
+        got, ok = dec.decode_batch(llr[:B], return_ok=True)
+        assert np.array_equal(got, exp[:B]) and np.array_equal(ok, eok[:B])
+    if N >= 256:
+        dec.setSystematic(False)
+        got, ok = dec.decode_batch(llr, return_ok=True)
+        exp, eok = ref.decode_batch(N, L, fz, "mixed", llr, systematic=False)
+        assert np.array_equal(got, exp) and np.array_equal(ok, eok)
+
+
+def test_scl_float_kat_n8_and_int8_input(pcb, ref):
+    """reference test/polarcode/decodingtest.cpp:1137-1181 (testListDecoder, float flavour)"""
+    dec = pcb.PolarDecoder(8, 4, [0, 1, 2, 4], "float")
+    out = dec.decode_vector(np.array([-5, -6, -4, 1, -4, -5, -7, 2], dtype=np.float32))
+    assert (out[0] & 0xF0) == 0xF0
+    N, K, L = 512, 256, 4
+    rng = np.random.default_rng(5)
+    fz = ref.frozen_bits(N, K, 0.0)
+    llr8 = np.clip(np.rint(10 * (1 + 0.8 * rng.standard_normal((200, N)))), -128, 127).astype(np.int8)
+    got, ok = pcb.PolarDecoder(N, L, list(fz), "float").decode_batch(llr8, return_ok=True)
+    exp, eok = ref.decode_batch(N, L, fz, "float", llr8)
+    assert np.array_equal(got, exp) and np.array_equal(ok, eok)
