@@ -32,12 +32,13 @@ METRIC = "decoded info Gbit/s, N=1024 K=512 Fast-SSC int8"
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--frames", type=int, default=1 << 20, help="frames per GPU per step")
     ap.add_argument("--e2e-frames", type=int, default=1 << 18)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true")
     return ap.parse_args()
 
 
@@ -51,7 +52,7 @@ class ClockSampler:
         self.proc = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(index)], stdout=subprocess.PIPE, text=True)
+                                          "-lms", "20", "-i", str(index)], stdout=subprocess.PIPE, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
         except Exception:
@@ -153,15 +154,14 @@ def main():
     kb = K_CODE // 8
     fz = pcb.frozen_bits(N_CODE, K_CODE, DSNR)
     dec = pcb.PolarDecoder(N_CODE, 1, fz, "char")
-    # synthetic batch, generated on the device for this rank's shard (global frame index seeds the generator)
-    g = torch.Generator(device=dev).manual_seed(0x5EED + rank)
-    sigma = 1.0 / np.sqrt(2.0 * (K_CODE / N_CODE) * 10.0 ** (EBN0_DB / 10.0))
+    # synthetic batch from the library's own device-side channel generator (random info -> CRC-8 -> systematic
+    # encode -> BPSK -> AWGN -> int8 LLR, Philox counter = global frame index, so a rank's shard is its frame range)
+    import ctypes
     llr = torch.empty((B, N_CODE), dtype=torch.int8, device=dev)
-    chunk = 1 << 16
-    for lo in range(0, B, chunk):
-        n = min(chunk, B - lo)
-        y = 1.0 + sigma * torch.randn((n, N_CODE), device=dev, generator=g)
-        llr[lo:lo + n] = torch.clamp(torch.round(AMP * y), -128, 127).to(torch.int8)
+    sent = torch.empty((B, kb), dtype=torch.uint8, device=dev)
+    capi.check(capi.lib().pc_awgn_generate(dec._h, ctypes.c_uint64(0x5EED), ctypes.c_uint64(rank * B), ctypes.c_float(EBN0_DB),
+                                           ctypes.c_float(AMP), 0, capi.ptr(llr), capi.ptr(sent), B, None))
+    torch.cuda.synchronize(dev)
     out = torch.empty((B, kb), dtype=torch.uint8, device=dev)
     ok = torch.empty((B,), dtype=torch.uint8, device=dev)
     stream = torch.cuda.current_stream(dev)
@@ -196,7 +196,48 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     total_ms_max = float(t.item())
     value = world * B * args.steps * K_CODE / (total_ms_max * 1e-3) / 1e9
-    frac_zero = float((out == 0).all(dim=1).float().mean().item())
+    bler = float((out != sent).any(dim=1).float().mean().item())
+    verdict_false = float((ok == 0).float().mean().item())
+
+    # ---- secondary: the metric's other half, CRC-aided SCL L=8 (N=1024 K=512, CRC-16), int8 and fp32 kernels,
+    # LLRs resident in HBM, whole-job info Gbit/s (max over ranks); plus the fp32 Fast-SSC and the adaptive decoder
+    def timed_kind(kind, L, crc_bits, frames, is_float, reps):
+        d = pcb.PolarDecoder(N_CODE, L, fz, kind)
+        d.setErrorDetection(crc_bits, "crc")
+        x = torch.empty((frames, N_CODE), dtype=torch.float32 if is_float else torch.int8, device=dev)
+        tx = torch.empty((frames, kb), dtype=torch.uint8, device=dev)
+        o = torch.empty((frames, kb), dtype=torch.uint8, device=dev)
+        v = torch.empty((frames,), dtype=torch.uint8, device=dev)
+        amp = 4.0 * 10.0 ** (EBN0_DB / 10.0) if is_float else AMP
+        capi.check(capi.lib().pc_awgn_generate(d._h, ctypes.c_uint64(0x5EED), ctypes.c_uint64(rank * frames),
+                                               ctypes.c_float(EBN0_DB), ctypes.c_float(amp), int(is_float), capi.ptr(x),
+                                               capi.ptr(tx), frames, None))
+
+        def one():
+            capi.check(capi.lib().pc_decode_batch(d._h, capi.ptr(x), int(is_float), capi.ptr(o), capi.ptr(v), frames, sp))
+        for _ in range(2):
+            one()
+        barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        for _ in range(reps):
+            one()
+        b.record(stream)
+        barrier()
+        tt = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        return {"value": world * frames * reps * K_CODE / (float(tt.item()) * 1e-3) / 1e9, "unit": "Gbit/s",
+                "frames_per_gpu_per_step": frames, "steps": reps, "bler": float((o != tx).any(dim=1).float().mean().item())}
+
+    secondary = None
+    if not args.no_secondary:
+        secondary = {
+            "scl_l8_int8_crc16": timed_kind("char", 8, 16, 1 << 16, False, 5),
+            "scl_l8_fp32_crc16": timed_kind("float", 8, 16, 1 << 15, True, 5),
+            "adaptive_l8_fp32_crc16": timed_kind("mixed", 8, 16, 1 << 17, True, 5),
+            "fastssc_fp32_crc8": timed_kind("float", 1, 8, 1 << 17, True, 5),
+        }
 
     # ---- e2e: host buffers through the C-ABI (pinned LLRs, H2D + decode + D2H inside the timed region)
     Be = min(args.e2e_frames, B)
@@ -270,7 +311,8 @@ def main():
             "e2e": {"value": e2e_val, "unit": "Gbit/s", "h2d_bytes_per_step": Be * N_CODE,
                     "d2h_bytes_per_step": Be * (kb + 1), "frames_per_step": Be, "matches_device_path": e2e_match},
             "gpu_launches": int(launches), "clocks": clocks,
-            "check": {"frac_frames_decoded_to_sent_word": frac_zero},
+            "check": {"bler": bler, "detector_false_rate": verdict_false, "ebn0_db": EBN0_DB},
+            "secondary": secondary,
         }
         print(json.dumps(line))
     if world > 1:

@@ -158,12 +158,13 @@ static int plan_fastssc(pc_code* c)
             q.tm_alloc = tm_used ? tm_alloc : 0;
             q.smem_bytes = 1024 + 16 * (size_t)T + 16 * (size_t)sm_chunks * T + (q.bits_kind == PK_SMEM ? 4 * (size_t)P.nbw * T : 0);
             const int resident = T * per_sm;
-            // Measured on B200 (N=1024, tools/sweep.sh): resident warps per SM matter more than where the large stages
-            // live -- 2 x 512 threads with stages 8, 9 in the L2 arena 194 Gbit/s, 1 x 1024 174, 1 x 512 170,
-            // 1 x 384 with everything in shared + tensor memory 146. So: maximise resident threads up to the
-            // register-file limit (64 regs x 1024), prefer two CTAs, and charge only a little for arena use.
+            // Measured on B200 (N=1024, tools/sweep.sh, whole rounds of ~1M frames, 10 steps, gpurun_out/sweep5.log):
+            // 1 x 1024 threads 200.9 Gbit/s, 1 x 640 192.5, 1 x 960 176.2, 2 x 512 175.8, 1 x 512 167.5, 1 x 768 155.6,
+            // 1 x 896 136.4 (the 1 x 1024 and 2 x 512 plans place every stage identically). So: maximise resident
+            // threads up to the register-file limit (64 regs x 1024), prefer ONE CTA per SM, and charge only a little
+            // for arena use.
             q.score = (long)std::min(resident, 1024) * 100 - (ar_used ? 1000 + 4L * std::min(ar_used, 512) : 0) -
-                      (q.bits_kind == PK_ARENA ? 4000 : 0) + (per_sm - 1) * 2000 - (T > 512 ? 3000 : 0);
+                      (q.bits_kind == PK_ARENA ? 4000 : 0) - (per_sm - 1) * 2000;
             if (q.score > best.score) best = q;
         }
     }

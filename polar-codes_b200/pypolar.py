@@ -52,7 +52,8 @@ def _kind_from_string(decoderType, listSize):
     return {1: capi.PC_DEC_SCL_F32, 2: capi.PC_DEC_ADAPTIVE_F32}.get(impl, capi.PC_DEC_SCL_I8)
 
 
-_CRC_NAMES = {0: "Dummy-0", 6: "CRC-6", 8: "CRC-8", 11: "CRC-11", 16: "CRC-16", 17: "CRC-16", 24: "CRC-24", 32: "CRC-32"}
+# Detector::getType() + "-" + getCheckBitCount() (reference include/polarcode/errordetection/*.h, dummy.cpp:20-22)
+_CRC_NAMES = {0: "DUMMY-0", 6: "CRCNR-6", 8: "CRC-8", 11: "CRCNR-11", 16: "CRC-16", 17: "CRCNR-16", 24: "CRCNR-24", 32: "CRC-32"}
 
 
 class _Code:
@@ -210,7 +211,7 @@ class Detector:
             raise ValueError(capi.last_error())
         self._kind = k
         self._bits = int(size)
-        self._type = "Dummy" if k == 0 else "CRC"
+        self._type = _CRC_NAMES[k].split("-")[0]  # Detector::getType(): "CRC", "CRCNR" or "DUMMY"
 
     def getCheckBitCount(self):
         return self._bits

@@ -1,0 +1,119 @@
+"""The C++ class mirror include/polarcode_b200.hpp (PolarCode::Encoding::ButterflyFipPacked, Decoding::create /
+Decoder, ErrorDetection::create / Detector, Construction::frozen_bits) driven through tests/cxx_api.cpp the way a
+caller of the reference's classes would, and compared with the unmodified reference (oracle/_ref)."""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+VP = ctypes.c_void_p
+
+
+@pytest.fixture(scope="module")
+def cxx(pcb):
+    pcb.capi.lib()
+    build = os.path.join(ROOT, "tests", "_build")
+    os.makedirs(build, exist_ok=True)
+    so = os.path.join(build, "libcxx_api.so")
+    deps = [os.path.join(ROOT, "tests", "cxx_api.cpp"), os.path.join(ROOT, "include", "polarcode_b200.hpp"),
+            os.path.join(ROOT, "include", "polar_b200.h")]
+    if not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(d) for d in deps):
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-fPIC", "-shared", "-Wall", "-o", so, deps[0],
+                               "-L" + os.path.join(ROOT, "polar-codes_b200"), "-lpolar_b200",
+                               "-Wl,-rpath,$ORIGIN/../../polar-codes_b200"])
+    return ctypes.CDLL(so)
+
+
+def _p(a):
+    return a.ctypes.data_as(VP)
+
+
+def test_cxx_frozen_bits_and_errors(cxx, ref):
+    out = np.zeros(4096, np.uint32)
+    n = ctypes.c_int(0)
+    for N, K, d, t in ((1024, 512, 0.0, "BB"), (64, 40, 1.0, "BB"), (512, 128, 0.0, "BE")):
+        assert cxx.cxx_frozen_bits(N, K, ctypes.c_float(d), t.encode(), _p(out), ctypes.byref(n)) == 0
+        assert out[:n.value].tolist() == list(ref.frozen_bits(N, K, d, t))
+    # constructor.cpp:25-31: std::invalid_argument for a block length that is not a power of two
+    assert cxx.cxx_frozen_bits(100, 50, ctypes.c_float(0.0), b"BB", _p(out), ctypes.byref(n)) == 1
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("size,typ", [(0, "crc"), (6, "crc"), (8, "crc"), (11, "crc"), (16, "crc"), (16, "crcnr"),
+                                      (24, "crc"), (32, "crc")])
+def test_cxx_detector_matches_reference(cxx, ref, size, typ):
+    rng = np.random.default_rng(size)
+    for nbytes in (8, 16, 64):
+        data = rng.integers(0, 256, nbytes + 8, dtype=np.uint8)
+        buf = data.copy()
+        okf, bad, calc, bits = ctypes.c_int(0), ctypes.c_int(0), ctypes.c_ulonglong(0), ctypes.c_int(0)
+        mode = ctypes.create_string_buffer(32)
+        assert cxx.cxx_detector(size, typ.encode(), _p(buf), nbytes, ctypes.byref(okf), ctypes.byref(bad),
+                                ctypes.byref(calc), mode, ctypes.byref(bits)) == 0
+        cb = (size + 7) // 8
+        exp = ref.crc_generate(size, typ, data[None, :nbytes + cb].copy())[0]
+        assert np.array_equal(buf[:nbytes + cb], exp)
+        assert okf.value == 1 and (bad.value == 0 or size == 0)
+        assert bits.value == size
+    # errordetector.cpp:41: std::logic_error("CRC INVALID SIZE!")
+    assert cxx.cxx_detector(7, b"crc", _p(buf), 8, ctypes.byref(okf), ctypes.byref(bad), ctypes.byref(calc), mode,
+                            ctypes.byref(bits)) == 2
+
+
+def test_cxx_no_gpu_is_an_error(cxx):
+    """no CPU fallback: constructing a decoder without a usable device throws std::runtime_error"""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    fz = np.array([0, 1, 2, 4], np.uint32)
+    out, ok = np.zeros(8, np.uint8), np.zeros(1, np.uint8)
+    mode, ls = ctypes.create_string_buffer(32), ctypes.c_int(0)
+    llr = np.zeros(8, np.int8)
+    assert cxx.cxx_decode(8, 1, _p(fz), 4, b"char", -1, b"crc", 1, 0, _p(llr), ctypes.c_long(1), _p(out), _p(ok), 0, mode,
+                          ctypes.byref(ls)) == 3
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("N,K,crc,typ,syst", [(1024, 512, 0, "crc", 1), (1024, 512, 16, "crcnr", 1), (64, 40, 8, "crc", 1),
+                                              (256, 128, 24, "crc", 0), (2048, 1024, 32, "crc", 1)])
+def test_cxx_encoder_matches_reference(cxx, ref, N, K, crc, typ, syst):
+    rng = np.random.default_rng(N + K + crc)
+    fz = np.ascontiguousarray(ref.frozen_bits(N, K, 0.0), dtype=np.uint32)
+    B = 40
+    info = rng.integers(0, 256, (B, K // 8), dtype=np.uint8)
+    exp_code, exp_info = ref.encode_batch(N, fz, info, crc_bits=crc, crc_type=typ, systematic=bool(syst))
+    for batch in (0, 1):
+        mine, code = info.copy(), np.zeros((B, N // 8), np.uint8)
+        mode = ctypes.create_string_buffer(32)
+        assert cxx.cxx_encode(N, _p(fz), len(fz), crc, typ.encode(), syst, _p(mine), _p(code), ctypes.c_long(B), batch, mode) == 0
+        assert np.array_equal(code, exp_code) and np.array_equal(mine, exp_info)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("N,K,L,kind,crc,typ", [(1024, 512, 1, "char", -1, "crc"), (1024, 512, 1, "float", 8, "crc"),
+                                                (64, 40, 4, "mixed", -1, "crc"), (512, 128, 8, "float", 24, "crc"),
+                                                (256, 128, 4, "CHAR", 16, "crc")])
+def test_cxx_decoder_matches_reference(cxx, ref, N, K, L, kind, crc, typ):
+    from conftest import awgn_llr_i8
+    rng = np.random.default_rng(N + K + L)
+    fz = np.ascontiguousarray(ref.frozen_bits(N, K, 0.0), dtype=np.uint32)
+    B = 48
+    llr8 = awgn_llr_i8(rng, B, N, 1.5, K / N)
+    is_float = "char" not in kind.lower()
+    llr = llr8.astype(np.float32) * np.float32(0.37) if is_float else llr8
+    exp, eok = ref.decode_batch(N, L, fz, kind, llr, crc_bits=crc, crc_type=typ)
+    for batch in (0, 1):
+        out, ok = np.zeros((B, K // 8), np.uint8), np.zeros(B, np.uint8)
+        mode, ls = ctypes.create_string_buffer(32), ctypes.c_int(0)
+        assert cxx.cxx_decode(N, L, _p(fz), len(fz), kind.encode(), crc, typ.encode(), 1, int(is_float), _p(llr),
+                              ctypes.c_long(B), _p(out), _p(ok), batch, mode, ctypes.byref(ls)) == 0
+        assert np.array_equal(out, exp) and np.array_equal(ok, eok)
+        assert ls.value == L
+        # makeDecoder installs CRC-8 (decoder.cpp:85)
+        assert mode.value.decode() == ("CRC-8" if crc < 0 else {8: "CRC-8", 24: "CRCNR-24", 16: "CRC-16"}[crc])
+    # decoder.cpp:45: std::logic_error("Unknown PolarDecoder type!")
+    assert cxx.cxx_decode(N, L, _p(fz), len(fz), b"bogus", crc, typ.encode(), 1, 0, _p(llr8), ctypes.c_long(1), _p(out),
+                          _p(ok), 0, mode, ctypes.byref(ls)) == 2

@@ -49,7 +49,12 @@ def test_detector_factory_rules(pcb):
     assert L.pc_crc_kind(7, b"crc") < 0
     assert [L.pc_crc_bytes(k) for k in (0, 6, 8, 11, 16, 17, 24, 32)] == [0, 1, 1, 2, 2, 2, 3, 4]
     d = pcb.Detector(11, "crc")
-    assert d.getCheckBitCount() == 11 and d.getType() == "CRC"
+    assert d.getCheckBitCount() == 11 and d.getType() == "CRCNR"  # crc11nr.h:36
+    # getType() / getCheckBitCount() of every detector the factory builds (values printed by the reference's pybind module)
+    for size, typ, name in ((0, "crc", "DUMMY"), (6, "crc", "CRCNR"), (8, "crc", "CRC"), (16, "crc", "CRC"),
+                            (16, "crcnr", "CRCNR"), (24, "crc", "CRCNR"), (32, "crc", "CRC")):
+        d = pcb.Detector(size, typ)
+        assert (d.getType(), d.getCheckBitCount()) == (name, size)
 
 
 def test_decoder_kind_mapping(pcb):
