@@ -194,9 +194,14 @@ PC_HD u4 ld_s5(const Ctx& c, int i) { return *reinterpret_cast<const u4*>(c.sm +
 //   BIG_G1  right child rate-1: decisions = sign(g), combine fused    ROneNode :427-449
 enum { BIG_F = 0, BIG_G = 1, BIG_G0 = 2, BIG_G1 = 3 };
 
-template <int OP, bool ST, bool DT>
+// ST / DT (source / destination in tensor memory) are warp-uniform RUN-TIME flags on purpose: one copy of the
+// arithmetic per OP keeps the hot code small. With the 16 specialised bodies (60-70 KB of hot SASS) the kernel's top
+// stall was instruction fetch (profiles/r01_fastssc_i8_full_v3.txt); this alone took N=1024 from 201 to 233 Gbit/s.
+// (Making OP a run-time value as well shrinks the code further but measured no faster: 230.)
+template <int OP>
 PC_HD void big_loop(const Ctx& c, const Mem& src, const Mem& dst, int s, int off)
 {
+    const bool ST = src.tm, DT = (OP != BIG_G1) && dst.tm;
     const int half = 1 << (s - 5), nb = half >> 1, wo = off >> 5;
     for (int j = 0; j < nb; ++j) {
         uint32_t bl = 0;
@@ -263,17 +268,7 @@ PC_HD void big_op(Ctx& c, const Mem& src, int s, int off)
         return;
     }
     const Mem dst = c.stage(s - 1);
-    if (src.tm) {
-        if (OP != BIG_G1 && dst.tm)
-            big_loop<OP, true, true>(c, src, dst, s, off);
-        else
-            big_loop<OP, true, false>(c, src, dst, s, off);
-    } else {
-        if (OP != BIG_G1 && dst.tm)
-            big_loop<OP, false, true>(c, src, dst, s, off);
-        else
-            big_loop<OP, false, false>(c, src, dst, s, off);
-    }
+    big_loop<OP>(c, src, dst, s, off);
 }
 
 // the same steps for nodes with n <= 16 (sources: stage 4 chunk or the small words)
