@@ -162,9 +162,10 @@ static int plan_fastssc(pc_code* c)
             // 1 x 1024 threads 200.9 Gbit/s, 1 x 640 192.5, 1 x 960 176.2, 2 x 512 175.8, 1 x 512 167.5, 1 x 768 155.6,
             // 1 x 896 136.4 (the 1 x 1024 and 2 x 512 plans place every stage identically). So: maximise resident
             // threads up to the register-file limit (64 regs x 1024), prefer ONE CTA per SM, and charge only a little
-            // for arena use.
+            // for arena use. Long codes, whose stages live mostly in the arena, measured the other way round
+            // (N=16384: 2 x 512 82 Gbit/s, 1 x 1024 76), hence the sign flip on the CTA term.
             q.score = (long)std::min(resident, 1024) * 100 - (ar_used ? 1000 + 4L * std::min(ar_used, 512) : 0) -
-                      (q.bits_kind == PK_ARENA ? 4000 : 0) - (per_sm - 1) * 2000;
+                      (q.bits_kind == PK_ARENA ? 4000 : 0) - (per_sm - 1) * (ar_used >= 128 ? -2000 : 2000);
             if (q.score > best.score) best = q;
         }
     }
@@ -361,6 +362,7 @@ void pc_code_destroy(pc_code* c)
     cudaFree(c->d_chan_code);
     cudaFree(c->d_quant);
     cudaFree(c->d_scl_code);
+    cudaFree(c->scl_arena);
     cudaFree(c->d_f32_code);
     cudaFree(c->d_sclf_code);
     cudaFree(c->sclf_arena);

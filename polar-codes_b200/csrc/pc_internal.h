@@ -40,6 +40,8 @@ struct pc_code {
     uint32_t* d_scl_code = nullptr;
     pc::SclLaunch scl_plan;
     bool scl_plan_valid = false;
+    uint32_t* scl_arena = nullptr;
+    size_t scl_arena_bytes = 0;
     // SCL fp32 (kind PC_DEC_SCL_F32, second pass of PC_DEC_ADAPTIVE_F32)
     pc::SclProgram sclf_prog;
     uint32_t* d_sclf_code = nullptr;

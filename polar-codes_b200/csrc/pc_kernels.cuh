@@ -50,7 +50,10 @@ struct SclParams {
     int llr_off[20];  // word offset of LLR stage s in a lane's space (s = 0 .. S)
     int bitL_off[20]; // word offset of the left / right decision buffer of stage s
     int bitR_off[20];
-    int words;        // words per lane
+    int words;        // shared-memory words per lane
+    int arena_words;  // arena words per lane (LLR stages whose llr_off carries the arena flag)
+    size_t arena_stride; // lanes the arena rows are laid out for (grid * threads)
+    uint32_t* arena;
 };
 
 struct SclLaunch {

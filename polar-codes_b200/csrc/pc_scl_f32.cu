@@ -12,6 +12,8 @@
 //   ([element][lane], the lanes of a group are adjacent, so a step of all lanes is one coalesced transaction).
 // * Optional indirection (frame_idx / count) lets the adaptive decoder run this kernel over the frames whose first
 //   pass failed, without a host round trip (AdaptiveFloat::decode adaptive_float.cpp:33-45).
+#include <cstdlib>
+
 #include "pc_fastssc_f32_core.h"
 #include "pc_kernels.cuh"
 #include "pc_scl_common.cuh"
@@ -29,6 +31,19 @@ struct FLane {
     Tbl own_llr, own_L, own_R;
     __device__ __forceinline__ uint32_t ld(int word, uint32_t owner) const { return sm[(size_t)word * T + ((int)owner - l)]; }
     __device__ __forceinline__ void st(int word, uint32_t v) const { sm[(size_t)word * T] = v; }
+    // LLR stage s (off = p.llr_off[s]) in lane `owner`'s space, resolved once per node step
+    struct View {
+        float* p;
+        size_t stride;
+        __device__ __forceinline__ float operator[](int i) const { return p[(size_t)i * stride]; }
+        __device__ __forceinline__ void set(int i, float v) const { p[(size_t)i * stride] = v; }
+    };
+    __device__ __forceinline__ View view(int s, int off, uint32_t owner) const
+    {
+        const ptrdiff_t d = (int)owner - l;
+        if (s <= smem_top) return View{ reinterpret_cast<float*>(sm) + (size_t)off * T + d, (size_t)T };
+        return View{ ar + (size_t)off * AS + d, AS };
+    }
     // LLR element i of stage s (off = p.llr_off[s]) in lane `owner`'s space
     __device__ __forceinline__ float lld(int s, int off, int i, uint32_t owner) const
     {
@@ -56,12 +71,14 @@ __device__ __forceinline__ void sclf_fg(FLane& c, const SclFParams& p, int s, co
     const int h = 1 << (s - 1);
     const bool from_row = (s == p.S) && !p.root_leaf;
     const uint32_t o = c.own_llr.get(s), ol = c.own_L.get(s - 1);
-    const int src = p.llr_off[s], dst = p.llr_off[s - 1], lb = p.bitL_off[s - 1];
+    const int lb = p.bitL_off[s - 1];
+    const FLane::View src = from_row ? c.view(s - 1, p.llr_off[s - 1], (uint32_t)c.l) : c.view(s, p.llr_off[s], o);
+    const FLane::View dst = c.view(s - 1, p.llr_off[s - 1], (uint32_t)c.l);
     if (active) {
         uint32_t bw = 0;
         for (int j = 0; j < h; ++j) {
-            const float a = from_row ? row[j] : c.lld(s, src, j, o);
-            const float b = from_row ? row[h + j] : c.lld(s, src, h + j, o);
+            const float a = from_row ? __ldg(row + j) : src[j];
+            const float b = from_row ? __ldg(row + h + j) : src[h + j];
             float r;
             if (IS_G) {
                 if ((j & 31) == 0) bw = c.ld(lb + (j >> 5), ol);
@@ -69,7 +86,7 @@ __device__ __forceinline__ void sclf_fg(FLane& c, const SclFParams& p, int s, co
             } else {
                 r = f_f32(a, b);
             }
-            c.lst(s - 1, dst, j, r);
+            dst.set(j, r);
         }
     }
     c.own_llr.set(s - 1, (uint32_t)c.l);
@@ -81,14 +98,15 @@ __device__ __forceinline__ void sclf_fg(FLane& c, const SclFParams& p, int s, co
 template <bool WANT_ALL>
 __device__ __forceinline__ void sclf_sums(const FLane& c, const SclFParams& p, int s, float& neg, float& pos, float& all)
 {
-    const int n = 1 << s, off = p.llr_off[s];
+    const int n = 1 << s;
+    const FLane::View v = c.view(s, p.llr_off[s], (uint32_t)c.l);
     float an[8], ap[8], aa[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) an[k] = ap[k] = aa[k] = 0.0f;
     for (int i = 0; i < n; i += 8) {
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
-            const float x = (i + k < n) ? c.lld(s, off, i + k, (uint32_t)c.l) : 0.0f;
+            const float x = (i + k < n) ? v[i + k] : 0.0f;
             an[k] = fadd(an[k], fmin_ps(x, 0.0f));
             if (WANT_ALL) {
                 ap[k] = fadd(ap[k], fmax_ps(x, 0.0f));
@@ -123,28 +141,28 @@ __device__ __forceinline__ void sclf_find_weak(const FLane& c, int s, int off, i
     WeakIdx ix;
     ix.init();
     const int lim = n - 1 < want ? n - 1 : want;
-    const uint32_t me = (uint32_t)c.l;
+    const FLane::View v = c.view(s, off, (uint32_t)c.l);
     for (int i = 0; i < lim; ++i) {
-        const float vi = c.lld(s, off, i, me);
+        const float vi = v[i];
         float bv = vi;
         int bp = i;
         for (int j = i + 1; j < n; ++j) {
-            const float x = c.lld(s, off, j, me);
+            const float x = v[j];
             if (x < bv) {
                 bv = x;
                 bp = j;
             }
         }
         if (bp != i) {
-            c.lst(s, off, i, bv);
-            c.lst(s, off, bp, vi);
+            v.set(i, bv);
+            v.set(bp, vi);
         }
         ix.swap(i, bp);
     }
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         widx[k] = ix.I[k];
-        wval[k] = (k < n) ? c.lld(s, off, k, me) : INFINITY; // pads of the 8-float block hold +inf (:363-365,:517-519)
+        wval[k] = (k < n) ? v[k] : INFINITY; // pads of the 8-float block hold +inf (:363-365,:517-519)
     }
 }
 
@@ -152,14 +170,15 @@ __device__ __forceinline__ void sclf_find_weak(const FLane& c, int s, int off, i
 // parity of the signs
 __device__ __forceinline__ uint32_t sclf_signs_and_abs(const FLane& c, const SclFParams& p, int s, int side)
 {
-    const int n = 1 << s, off = p.llr_off[s], dst = side ? p.bitR_off[s] : p.bitL_off[s];
+    const int n = 1 << s, dst = side ? p.bitR_off[s] : p.bitL_off[s];
+    const FLane::View v = c.view(s, p.llr_off[s], (uint32_t)c.l);
     uint32_t par = 0, acc = 0;
     for (int j = 0; j < n; ++j) {
-        const float x = c.lld(s, off, j, (uint32_t)c.l);
+        const float x = v[j];
         const uint32_t sg = fsign(x);
         par ^= sg;
         acc |= sg << (j & 31);
-        c.lst(s, off, j, fabs_(x));
+        v.set(j, fabs_(x));
         if ((j & 31) == 31 || j == n - 1) {
             c.st(dst + (j >> 5), acc);
             acc = 0;
@@ -407,9 +426,14 @@ int plan_scl_f32(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, 
     // many of the small LLR stages as fit go to shared memory
     static const int cand[][2] = { { 128, 8 }, { 128, 6 }, { 128, 4 }, { 128, 3 }, { 128, 2 }, { 128, 1 }, { 64, 1 }, { 32, 1 } };
     int T = 0, per_sm = 0, smem_top = -1;
+    int force_t = -1, force_n = -1; // experiment overrides (tools/sweep_scl.sh)
+    if (const char* e = getenv("PC_SCLF_THREADS")) force_t = atoi(e);
+    if (const char* e = getenv("PC_SCLF_CTAS")) force_n = atoi(e);
+    for (int pass = 0; pass < 2 && !T; ++pass)
     for (size_t ci = 0; ci < sizeof(cand) / sizeof(cand[0]); ++ci) {
         const int t = cand[ci][0], n = cand[ci][1];
         if (t < G) continue;
+        if ((force_t > 0 && t != force_t) || (force_n > 0 && n != force_n)) continue;
         size_t per_cta = sm_total / n - 1024;
         if (per_cta > smem_max) per_cta = smem_max;
         if (per_cta < 1024) continue;
@@ -420,9 +444,11 @@ int plan_scl_f32(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, 
             w += 1 << s;
             top = s;
         }
-        // with several CTAs per SM wanted, insist on the whole tree (or at least stages <= 5) being on chip
-        if (n > 2 && top < top_llr) continue;
-        if (n == 2 && top < top_llr && top < 5) continue;
+        // first pass: the whole tree on chip with as many CTAs per SM as fit (at least 256 lanes); second pass: the most lanes whose
+        // decision words fit (measured, N=1024 L=8: 3 x 128 lanes 1.48 Gbit/s, 2 x 128 1.40, 1 x 128 0.82; the large
+        // stages then live in the arena). More than 3 CTAs would not be resident anyway (96 registers per thread).
+        if (force_n <= 0 && pass == 0 && (top < top_llr || t * n < 256)) continue;
+        if (force_n <= 0 && pass == 1 && n > 3) continue;
         T = t;
         per_sm = n;
         smem_top = top;

@@ -17,20 +17,42 @@
 //   stores its block, else lane 0.
 // Storage: shared memory only, word-granular, thread-interleaved (word w of a lane at smem[w * T + tid]); other
 // lanes' buffers are read at their tid.
+#include <cstdlib>
+
 #include "pc_fastssc_i8_core.h"
 #include "pc_kernels.cuh"
 #include "pc_scl_common.cuh"
 
 namespace pc {
 
+// word indices with kArena set address the L2-resident arena ([word][lane], lanes of a group adjacent) instead of
+// shared memory: the host planner moves the largest LLR stages there so that more codewords fit one SM
+constexpr int kArena = 1 << 30;
+
 struct Lane {
     uint32_t* sm;   // smem base + tid (word w at sm[w * T])
+    uint32_t* ar;   // arena base + global lane id (word w at ar[w * AS])
+    size_t AS;
     int T, G, l;    // threads per CTA, lanes per group, lane index inside the group
     int P;          // live paths (uniform)
     int metric;     // path metric (the reference uses long; |metric| <= 128 N fits easily)
     Tbl own_llr, own_L, own_R;
+    // decision words: shared memory only
     __device__ __forceinline__ uint32_t ld(int word, uint32_t owner) const { return sm[(size_t)word * T + ((int)owner - l)]; }
     __device__ __forceinline__ void st(int word, uint32_t v) const { sm[(size_t)word * T] = v; }
+    // LLR stage starting at word offset `off` (p.llr_off[s]) in lane `owner`'s space, resolved once per node step
+    struct View {
+        uint32_t* p;
+        size_t stride;
+        __device__ __forceinline__ uint32_t operator[](int w) const { return p[(size_t)w * stride]; }
+        __device__ __forceinline__ void set(int w, uint32_t v) const { p[(size_t)w * stride] = v; }
+    };
+    __device__ __forceinline__ View view(int off, uint32_t owner) const
+    {
+        const ptrdiff_t d = (int)owner - l;
+        if (off & kArena) return View{ ar + (size_t)(off & (kArena - 1)) * AS + d, AS };
+        return View{ sm + (size_t)off * T + d, (size_t)T };
+    }
 };
 
 __device__ __forceinline__ int stage_words(int s) { return s >= 2 ? (1 << (s - 2)) : 1; }   // LLR words
@@ -46,13 +68,14 @@ __device__ __forceinline__ void scl_fg(Lane& c, const SclParams& p, int s, const
     const uint32_t* grow = reinterpret_cast<const uint32_t*>(row);
     const bool from_row = (s == p.S) && !p.root_leaf;
     const uint32_t o = c.own_llr.get(s), ol = c.own_L.get(s - 1);
-    const int src = p.llr_off[s], dst = p.llr_off[s - 1], lb = p.bitL_off[s - 1];
+    const int lb = p.bitL_off[s - 1];
+    const Lane::View src = c.view(from_row ? p.llr_off[s - 1] : p.llr_off[s], o), dst = c.view(p.llr_off[s - 1], (uint32_t)c.l);
     if (active) {
         if (h >= 4) {
             const int hw = h >> 2;
             for (int j = 0; j < hw; ++j) {
-                const uint32_t a = from_row ? __ldg(grow + j) : c.ld(src + j, o);
-                const uint32_t b = from_row ? __ldg(grow + hw + j) : c.ld(src + hw + j, o);
+                const uint32_t a = from_row ? __ldg(grow + j) : src[j];
+                const uint32_t b = from_row ? __ldg(grow + hw + j) : src[hw + j];
                 uint32_t r;
                 if (IS_G) {
                     const uint32_t bw = c.ld(lb + (j >> 3), ol);
@@ -60,17 +83,17 @@ __device__ __forceinline__ void scl_fg(Lane& c, const SclParams& p, int s, const
                 } else {
                     r = sw_f(a, b);
                 }
-                c.st(dst + j, r);
+                dst.set(j, r);
             }
         } else {
-            const uint32_t w = from_row ? __ldg(grow) : c.ld(src, o);
+            const uint32_t w = from_row ? __ldg(grow) : src[0];
             const uint32_t hi = w >> (8 * h);
             uint32_t r;
             if (IS_G)
                 r = sw_g(w, hi, sw_expand4(c.ld(lb, ol)));
             else
                 r = sw_f(w, hi);
-            c.st(dst, r & bytemask(h));
+            dst.set(0, r & bytemask(h));
         }
     }
     c.own_llr.set(s - 1, (uint32_t)c.l);
@@ -79,11 +102,12 @@ __device__ __forceinline__ void scl_fg(Lane& c, const SclParams& p, int s, const
 // sums of the negative / positive LLRs of the own stage-s buffer (exact integer sums, dp4a)
 __device__ __forceinline__ void llr_sums(const Lane& c, const SclParams& p, int s, int& neg, int& pos)
 {
-    const int n = 1 << s, nw = stage_words(s), off = p.llr_off[s];
+    const int n = 1 << s, nw = stage_words(s);
+    const Lane::View v = c.view(p.llr_off[s], (uint32_t)c.l);
     neg = 0;
     pos = 0;
     for (int j = 0; j < nw; ++j) {
-        uint32_t w = c.ld(off + j, (uint32_t)c.l);
+        uint32_t w = v[j];
         if (n < 4) w &= bytemask(n);
         const uint32_t f = sw_signfill(w);
         neg = __dp4a((int)(w & f), 0x01010101, neg);
@@ -112,12 +136,13 @@ __device__ __forceinline__ void scl_find_weak(const Lane& c, int off, int n, int
 {
     int I[4] = { 0, 1, 2, 3 }, ppos[4] = { -1, -1, -1, -1 }, pidx[4] = { 0, 0, 0, 0 };
     int np = 0;
+    const Lane::View v = c.view(off, (uint32_t)c.l);
     const int lim = n - 1 < want ? n - 1 : want;
     const int nw = (n + 3) >> 2;
     for (int i = 0; i < lim; ++i) {
         int bv = 256, bp = i;
         for (int w = i >> 2; w < nw; ++w) {
-            const uint32_t x = c.ld(off + w, (uint32_t)c.l);
+            const uint32_t x = v[w];
 #pragma unroll
             for (int b = 0; b < 4; ++b) {
                 const int pos = 4 * w + b, val = (int)((x >> (8 * b)) & 0xFFu);
@@ -128,12 +153,12 @@ __device__ __forceinline__ void scl_find_weak(const Lane& c, int off, int n, int
             }
         }
         // swap bytes i <-> bp
-        const uint32_t wi = c.ld(off + (i >> 2), (uint32_t)c.l);
+        const uint32_t wi = v[i >> 2];
         const int vi = (int)((wi >> (8 * (i & 3))) & 0xFFu);
         if (bp != i) {
-            c.st(off + (i >> 2), (wi & ~(0xFFu << (8 * (i & 3)))) | ((uint32_t)bv << (8 * (i & 3))));
-            const uint32_t wm = c.ld(off + (bp >> 2), (uint32_t)c.l);
-            c.st(off + (bp >> 2), (wm & ~(0xFFu << (8 * (bp & 3)))) | ((uint32_t)vi << (8 * (bp & 3))));
+            v.set(i >> 2, (wi & ~(0xFFu << (8 * (i & 3)))) | ((uint32_t)bv << (8 * (i & 3))));
+            const uint32_t wm = v[bp >> 2];
+            v.set(bp >> 2, (wm & ~(0xFFu << (8 * (bp & 3)))) | ((uint32_t)vi << (8 * (bp & 3))));
         }
         // Indices[i] <-> Indices[bp]
         int im = bp;
@@ -157,7 +182,7 @@ __device__ __forceinline__ void scl_find_weak(const Lane& c, int off, int n, int
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         widx[k] = I[k];
-        const uint32_t x = c.ld(off + (k >> 2), (uint32_t)c.l);
+        const uint32_t x = v[k >> 2];
         wval[k] = (k < n) ? (int)((x >> (8 * (k & 3))) & 0xFFu) : 0;
     }
 }
@@ -166,14 +191,15 @@ __device__ __forceinline__ void scl_find_weak(const Lane& c, int off, int n, int
 // returns the XOR of all LLR words (its byte MSBs give the parity)
 __device__ __forceinline__ uint32_t scl_signs_and_abs(const Lane& c, const SclParams& p, int s, int side)
 {
-    const int n = 1 << s, nw = stage_words(s), off = p.llr_off[s], dst = side ? p.bitR_off[s] : p.bitL_off[s];
+    const int n = 1 << s, nw = stage_words(s), dst = side ? p.bitR_off[s] : p.bitL_off[s];
+    const Lane::View v = c.view(p.llr_off[s], (uint32_t)c.l);
     uint32_t par = 0, acc = 0;
     for (int j = 0; j < nw; ++j) {
-        uint32_t w = c.ld(off + j, (uint32_t)c.l);
+        uint32_t w = v[j];
         if (n < 4) w &= bytemask(n);
         par ^= w;
         acc |= sw_movemask(w) << (4 * (j & 7));
-        c.st(off + j, sw_abs_sat(w));
+        v.set(j, sw_abs_sat(w));
         if ((j & 7) == 7 || j == nw - 1) {
             c.st(dst + (j >> 3), acc);
             acc = 0;
@@ -288,6 +314,8 @@ __global__ void __launch_bounds__(256) k_scl_i8(const __grid_constant__ SclParam
     __syncthreads();
     Lane c;
     c.sm = smem + 256 + t;
+    c.ar = p.arena + ((size_t)blockIdx.x * T + t);
+    c.AS = p.arena_stride;
     c.T = T;
     c.G = p.G;
     c.l = t & (p.G - 1);
@@ -308,9 +336,10 @@ __global__ void __launch_bounds__(256) k_scl_i8(const __grid_constant__ SclParam
         if (p.root_leaf && c.l == 0) { // stage the channel row (the root is a leaf)
             const int nw = stage_words(p.S);
             if (N >= 4) {
-                for (int j = 0; j < nw; ++j) c.st(p.llr_off[p.S] + j, reinterpret_cast<const uint32_t*>(row)[j]);
+                const Lane::View v = c.view(p.llr_off[p.S], (uint32_t)c.l);
+                for (int j = 0; j < nw; ++j) v.set(j, reinterpret_cast<const uint32_t*>(row)[j]);
             } else {
-                c.st(p.llr_off[p.S], (uint32_t)(uint8_t)row[0] | ((uint32_t)(uint8_t)row[1] << 8));
+                c.view(p.llr_off[p.S], (uint32_t)c.l).set(0, (uint32_t)(uint8_t)row[0] | ((uint32_t)(uint8_t)row[1] << 8));
             }
         }
         __syncwarp();
@@ -406,12 +435,59 @@ int plan_scl_i8(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, S
     p.L = L;
     p.G = G;
     p.root_leaf = root_leaf ? 1 : 0;
-    int w = 0;
     const int top_llr = root_leaf ? S : S - 1;
+    int bit_words = 0;
+    for (int s = 0; s <= S; ++s) bit_words += 2 * (s >= 5 ? (1 << (s - 5)) : 1);
+    // Lanes (= list paths) resident per SM decide throughput: the kernel is latency bound (one lane per path, long
+    // dependent chains), so the planner trades shared-memory residency of the largest LLR stages for more lanes.
+    // Candidates in order of preference; the first one that keeps stages <= `pref` in shared memory wins. Measured
+    // on B200 (N=1024, L=8, tools/perf_decoder.py): see DESIGN.md section 3.4.
+    int pref = 7, force_lanes = -1, force_top = -2;
+    if (const char* e = getenv("PC_SCL_PREF")) pref = atoi(e);
+    if (const char* e = getenv("PC_SCL_LANES")) force_lanes = atoi(e);
+    if (const char* e = getenv("PC_SCL_SMEMTOP")) force_top = atoi(e);
+    static const int cand[] = { 512, 384, 256, 192, 128, 96, 64, 32 };
+    int T = 0, per_sm = 0, smem_top = -1;
+    for (int pass = 0; pass < 2 && !T; ++pass) {
+        for (size_t ci = 0; ci < sizeof(cand) / sizeof(cand[0]); ++ci) {
+            const int lanes = cand[ci];
+            if (force_lanes > 0 && lanes != force_lanes) continue;
+            const int t = lanes <= 256 ? lanes : 128, n = lanes / t;
+            if (t < G || (t % G) != 0) continue;
+            size_t per_cta = 233472 / (size_t)n - 1024;
+            if (per_cta > smem_max) per_cta = smem_max;
+            const long budget = ((long)per_cta - 1024) / (4L * t); // words per lane
+            if (budget < bit_words) continue;
+            int w = bit_words, top = -1;
+            for (int st = 0; st <= top_llr; ++st) {
+                const int sw = st >= 2 ? (1 << (st - 2)) : 1;
+                if (w + sw > budget || (force_top > -2 && st > force_top)) break;
+                w += sw;
+                top = st;
+            }
+            // first pass: insist on the preferred residency; second pass: anything that fits
+            if (pass == 0 && force_lanes <= 0 && top < (top_llr < pref ? top_llr : pref)) continue;
+            T = t;
+            per_sm = n;
+            smem_top = top;
+            break;
+        }
+    }
+    if (!T) {
+        *msg = "SCL path state does not fit shared memory (block length too large for this list size)";
+        return 1;
+    }
+    int w = 0, aw = 0;
     for (int s = 0; s < 20; ++s) p.llr_off[s] = p.bitL_off[s] = p.bitR_off[s] = 0;
     for (int s = 0; s <= top_llr; ++s) {
-        p.llr_off[s] = w;
-        w += s >= 2 ? (1 << (s - 2)) : 1;
+        const int sw = s >= 2 ? (1 << (s - 2)) : 1;
+        if (s <= smem_top) {
+            p.llr_off[s] = w;
+            w += sw;
+        } else {
+            p.llr_off[s] = kArena | aw;
+            aw += sw;
+        }
     }
     for (int s = 0; s <= S; ++s) {
         const int bw = s >= 5 ? (1 << (s - 5)) : 1;
@@ -421,20 +497,11 @@ int plan_scl_i8(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, S
         w += bw;
     }
     p.words = w;
-    const size_t per_lane = 4 * (size_t)w;
-    int T = 256;
-    while (T >= 32 && (1024 + per_lane * T > smem_max || T < G)) T -= 32;
-    if (T < 32 || T < G || 1024 + per_lane * T > smem_max) {
-        *msg = "SCL path state does not fit shared memory (block length too large for this list size)";
-        return 1;
-    }
-    T = (T / G) * G;
+    p.arena_words = aw;
     out.threads = T;
-    out.smem_bytes = 1024 + per_lane * T;
-    int per_sm = (int)((233472) / (out.smem_bytes + 1024));
-    if (per_sm < 1) per_sm = 1;
-    if (per_sm * T > 1024) per_sm = 1024 / T > 0 ? 1024 / T : 1;
+    out.smem_bytes = 1024 + 4 * (size_t)w * T;
     out.grid = sms * per_sm;
+    p.arena_stride = (size_t)out.grid * T;
     return 0;
 }
 
