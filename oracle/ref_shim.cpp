@@ -42,9 +42,23 @@ int ref_frozen_bits(int N, int K, float dsnr, const char* type, unsigned* out)
 // kind: "char" / "float" / "mixed"; crc_bits<0 => keep the factory default (CRC-8, decoder.cpp:85);
 // is_float: llr points to float[B][N] else int8[B][N]. Returns seconds spent inside the decode loops
 // (max over threads), or a negative value on error.
+// fresh != 0: a NEW decoder object for every frame. SclAvxFloat never resets the metric of path 0 between decode()
+// calls (PathList::setFirstPath, scl_avx_float.cpp:103-109, assigns no metric; only the constructor does, :31,35), so
+// with one long-lived object every frame starts from the previous frame's best metric: harmless in exact arithmetic,
+// but float rounding then depends on the decoder's history. A fresh object per frame is the history-free behaviour.
+double ref_decode_batch2(int N, int L, const unsigned* frozen, int nf, const char* kind, int crc_bits,
+                         const char* crc_type, int systematic, int is_float, const void* llr, long B,
+                         unsigned char* out, unsigned char* ok, int threads, int repeat, int fresh);
 double ref_decode_batch(int N, int L, const unsigned* frozen, int nf, const char* kind, int crc_bits,
                         const char* crc_type, int systematic, int is_float, const void* llr, long B,
                         unsigned char* out, unsigned char* ok, int threads, int repeat)
+{
+    return ref_decode_batch2(N, L, frozen, nf, kind, crc_bits, crc_type, systematic, is_float, llr, B, out, ok, threads,
+                             repeat, 0);
+}
+double ref_decode_batch2(int N, int L, const unsigned* frozen, int nf, const char* kind, int crc_bits,
+                         const char* crc_type, int systematic, int is_float, const void* llr, long B,
+                         unsigned char* out, unsigned char* ok, int threads, int repeat, int fresh)
 {
     try {
         const int K = N - nf;
@@ -69,6 +83,12 @@ double ref_decode_batch(int N, int L, const unsigned* frozen, int nf, const char
                 for (int r = 0; r < repeat; ++r) {
                     for (long i = lo; i < hi; ++i) {
                         bool res;
+                        if (fresh && i > lo) {
+                            delete dec;
+                            dec = Decoding::create(N, L, fz, std::string(kind));
+                            if (det) dec->setErrorDetection(det);
+                            dec->setSystematic(systematic != 0);
+                        }
                         if (is_float)
                             res = dec->decode_vector(reinterpret_cast<const float*>(llr) + i * N, tmp.data());
                         else

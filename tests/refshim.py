@@ -24,6 +24,10 @@ def lib():
         L = ctypes.CDLL(os.path.join(REF_DIR, "libref_shim.so"))
         L.ref_frozen_bits.restype = ctypes.c_int
         L.ref_frozen_bits.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_float, ctypes.c_char_p, ctypes.c_void_p]
+        L.ref_decode_batch2.restype = ctypes.c_double
+        L.ref_decode_batch2.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_char_p, ctypes.c_int,
+                                        ctypes.c_char_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_long,
+                                        ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int]
         L.ref_decode_batch.restype = ctypes.c_double
         L.ref_decode_batch.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_char_p,
                                        ctypes.c_int, ctypes.c_char_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p,
@@ -54,7 +58,9 @@ def frozen_bits(N, K, dsnr, ctype="BB"):
 
 
 def decode_batch(N, L, frozen, kind, llr, crc_bits=-1, crc_type="crc", systematic=True, threads=1, repeat=1,
-                 return_time=False):
+                 return_time=False, fresh=False):
+    """fresh=True: a new decoder object per frame (see oracle/ref_shim.cpp: SclAvxFloat keeps its best path metric
+    across decode() calls, which makes float results depend on the decoder's history)"""
     frozen = np.ascontiguousarray(frozen, dtype=np.uint32)
     llr = np.ascontiguousarray(llr)
     is_float = llr.dtype == np.float32
@@ -64,8 +70,8 @@ def decode_batch(N, L, frozen, kind, llr, crc_bits=-1, crc_type="crc", systemati
     kb = (K + 7) // 8
     out = np.zeros((B, kb), dtype=np.uint8)
     ok = np.zeros(B, dtype=np.uint8)
-    t = lib().ref_decode_batch(N, L, _p(frozen), len(frozen), kind.encode(), crc_bits, crc_type.encode(),
-                               int(systematic), int(is_float), _p(llr), B, _p(out), _p(ok), threads, repeat)
+    t = lib().ref_decode_batch2(N, L, _p(frozen), len(frozen), kind.encode(), crc_bits, crc_type.encode(),
+                                int(systematic), int(is_float), _p(llr), B, _p(out), _p(ok), threads, repeat, int(fresh))
     if t < 0:
         raise RuntimeError("reference decode failed")
     return (out, ok, t) if return_time else (out, ok)

@@ -71,7 +71,7 @@ def _tx_float_llrs(ref, rng, N, K, fz, crc_bits, crc_type, B):
     code, _ = ref.encode_batch(N, fz, info, crc_bits=crc_bits, crc_type=crc_type)
     x = 1.0 - 2.0 * np.unpackbits(code, axis=1, bitorder="big")[:, :N].astype(np.float32)
     out = []
-    for sigma, scale, rint in ((0.7, 4.0, False), (0.9, 10.0, True), (1.0, 2.0, True), (0.5, 3.0, False)):
+    for sigma, scale, rint in ((0.7, 4.0, False), (0.9, 10.0, True), (1.0, 2.0, True), (0.5, 3.0, False), (1.0, 4.0, False)):
         y = (x + sigma * rng.standard_normal((B, N))).astype(np.float32) * np.float32(scale)
         out.append(np.rint(y).astype(np.float32) if rint else y.astype(np.float32))
     return np.concatenate(out)
@@ -92,7 +92,9 @@ def test_scl_float_parity(pcb, ref, N, K, L, crc_bits, crc_type):
     dec = pcb.PolarDecoder(N, L, list(fz), "float")
     dec.setErrorDetection(crc_bits, crc_type)
     got, ok = dec.decode_batch(llr, return_ok=True)
-    exp, eok = ref.decode_batch(N, L, fz, "float", llr, crc_bits=crc_bits, crc_type=crc_type)
+    # fresh=True: a new reference object per frame; a long-lived SclAvxFloat carries its best path metric from frame to
+    # frame (tests/test_oracle.py::test_reference_float_list_decoder_keeps_metric_across_frames)
+    exp, eok = ref.decode_batch(N, L, fz, "float", llr, crc_bits=crc_bits, crc_type=crc_type, fresh=True, threads=8)
     assert _agree(got, exp) >= MIN_FRAME_AGREEMENT
     bad = (got != exp).any(axis=1)
     assert not bad.any(), f"{bad.sum()} of {len(bad)} frames differ (first {np.flatnonzero(bad)[:5]})"
@@ -107,7 +109,7 @@ def test_adaptive_mixed_parity(pcb, ref, N, K, L, dsnr):
     llr = _tx_float_llrs(ref, rng, N, K, fz, 8, "crc", 256)
     dec = pcb.PolarDecoder(N, L, list(fz), "mixed")
     got, ok = dec.decode_batch(llr, return_ok=True)
-    exp, eok = ref.decode_batch(N, L, fz, "mixed", llr)
+    exp, eok = ref.decode_batch(N, L, fz, "mixed", llr, fresh=True, threads=8)
     assert N not in (64, 1024) or 0 < ok.mean() < 1  # both passes are exercised
     assert np.array_equal(got, exp) and np.array_equal(ok, eok)
     # ragged batch sizes and the non-systematic flavour
@@ -117,7 +119,7 @@ def test_adaptive_mixed_parity(pcb, ref, N, K, L, dsnr):
     if N >= 256:
         dec.setSystematic(False)
         got, ok = dec.decode_batch(llr, return_ok=True)
-        exp, eok = ref.decode_batch(N, L, fz, "mixed", llr, systematic=False)
+        exp, eok = ref.decode_batch(N, L, fz, "mixed", llr, systematic=False, fresh=True, threads=8)
         assert np.array_equal(got, exp) and np.array_equal(ok, eok)
 
 
@@ -131,5 +133,5 @@ def test_scl_float_kat_n8_and_int8_input(pcb, ref):
     fz = ref.frozen_bits(N, K, 0.0)
     llr8 = np.clip(np.rint(10 * (1 + 0.8 * rng.standard_normal((200, N)))), -128, 127).astype(np.int8)
     got, ok = pcb.PolarDecoder(N, L, list(fz), "float").decode_batch(llr8, return_ok=True)
-    exp, eok = ref.decode_batch(N, L, fz, "float", llr8)
+    exp, eok = ref.decode_batch(N, L, fz, "float", llr8, fresh=True)
     assert np.array_equal(got, exp) and np.array_equal(ok, eok)

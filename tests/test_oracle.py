@@ -161,3 +161,30 @@ def test_differential_construction(orc, ref):
             for d in (-1.5, 0.0, 1.0, 2.5):
                 assert np.array_equal(orc.frozen_bits(N, K, d), ref.frozen_bits(N, K, d)), (N, K, d)
             assert np.array_equal(orc.frozen_bits(N, K, 0.0, "BE"), ref.frozen_bits(N, K, 0.0, "BE"))
+
+
+def test_reference_float_list_decoder_keeps_metric_across_frames(ref):
+    """Pins a reference defect the GPU parity tests route around: SclAvxFloat never resets the metric of path 0 between
+    decode() calls (PathList::setFirstPath, scl_avx_float.cpp:103-109, assigns no metric; only the constructor zeroes
+    it), so every frame starts from the previous frame's best metric. In exact arithmetic (integer-valued LLRs) that
+    offset changes nothing; with continuous LLRs the float rounding of every later metric depends on the decoder's
+    history and near-tie decisions flip, more and more often as |metric| grows. A fresh object per frame is history
+    free -- that is what k_scl_f32 (metric starts at 0 for every frame) is compared with at scale (tools/parity_sweep.py)."""
+    N, K, L = 256, 128, 4
+    fz = ref.frozen_bits(N, K, 0.0)
+    rng = np.random.default_rng(0)
+    llr = (4.0 * (1 + rng.standard_normal((12000, N)))).astype(np.float32)
+    long_lived, _ = ref.decode_batch(N, L, fz, "float", llr, crc_bits=0, threads=1)
+    fresh, _ = ref.decode_batch(N, L, fz, "float", llr, crc_bits=0, threads=4, fresh=True)
+    bad = np.flatnonzero((long_lived != fresh).any(axis=1))
+    assert 0 < len(bad) < 0.05 * len(llr)
+    assert (bad >= len(llr) // 2).sum() > (bad < len(llr) // 2).sum()  # drifts: worse the longer the object lives
+    ints = np.rint(llr).astype(np.float32)
+    a, _ = ref.decode_batch(N, L, fz, "float", ints, crc_bits=0, threads=1)
+    b, _ = ref.decode_batch(N, L, fz, "float", ints, crc_bits=0, threads=4, fresh=True)
+    assert np.array_equal(a, b)
+    # the int8 list decoder has the same carry-over but integer metrics: no effect
+    i8 = np.clip(np.rint(llr * 2.5), -128, 127).astype(np.int8)
+    a, _ = ref.decode_batch(N, L, fz, "char", i8, crc_bits=0, threads=1)
+    b, _ = ref.decode_batch(N, L, fz, "char", i8, crc_bits=0, threads=4, fresh=True)
+    assert np.array_equal(a, b)

@@ -1,0 +1,76 @@
+#!/usr/bin/env python
+"""SURVEY.md 8(d) parity gate, run on the GPU box: for every Eb/N0 point the library's device-side channel generator
+makes the frames, the GPU decodes them, the SAME LLRs are copied back and replayed through the unmodified reference
+(oracle/_ref, all host threads), and info bytes + verdicts are compared frame by frame.
+  int8 kinds: 0 mismatching frames allowed.  float kinds: >= 99.99 % identical frames.
+  BLER of the GPU decode must lie inside the 95 % Clopper-Pearson interval of the reference's BLER (trivially true when
+  all frames agree; reported anyway).
+usage: tools/parity_sweep.py [--frames F] [--out profiles/x.json] case ...   with case = N:K:L:kind:crcbits"""
+import argparse, ctypes, json, os, sys, time
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+import numpy as np
+import torch
+from scipy.stats import beta
+import polar_b200_loader, refshim
+pcb = polar_b200_loader.load()
+L_, ptr, check = pcb.capi.lib(), pcb.capi.ptr, pcb.capi.check
+
+def cp_interval(k, n, conf=0.95):
+    a = (1 - conf) / 2
+    lo = 0.0 if k == 0 else beta.ppf(a, k, n - k + 1)
+    hi = 1.0 if k == n else beta.ppf(1 - a, k + 1, n - k)
+    return float(lo), float(hi)
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--frames", type=int, default=1 << 20)
+ap.add_argument("--out", default=None)
+ap.add_argument("--points", default="0,0.5,1,1.5,2,2.5,3,3.5,4")
+ap.add_argument("cases", nargs="+")
+a = ap.parse_args()
+points = [float(x) for x in a.points.split(",")]
+threads = os.cpu_count() or 1
+report = []
+for case in a.cases:
+    N, K, L, kind, crc = case.split(":"); N, K, L, crc = int(N), int(K), int(L), int(crc)
+    isf = "char" not in kind
+    F = a.frames if L == 1 else max(1 << 17, a.frames // 8)
+    fz = pcb.frozen_bits(N, K, 0.0)
+    dec = pcb.PolarDecoder(N, L, fz, kind); dec.setErrorDetection(crc, "crc")
+    kb = (K + 7) // 8
+    chunk = min(F, 1 << 18)
+    llr = torch.empty((chunk, N), dtype=torch.float32 if isf else torch.int8, device="cuda")
+    info = torch.empty((chunk, kb), dtype=torch.uint8, device="cuda")
+    for p, eb in enumerate(points):
+        amp = 4.0 * 10 ** (eb / 10) if isf else 10.0
+        mism = okm = fe_gpu = fe_ref = drift = 0; t_ref = 0.0
+        for lo in range(0, F, chunk):
+            n = min(chunk, F - lo)
+            check(L_.pc_awgn_generate(dec._h, ctypes.c_uint64(0x5EED), ctypes.c_uint64((p << 40) + lo), ctypes.c_float(eb),
+                                      ctypes.c_float(amp), int(isf), ptr(llr), ptr(info), n, None))
+            out, ok = dec.decode_batch(llr[:n], return_ok=True)
+            h_llr = llr[:n].cpu().numpy(); h_out = out.cpu().numpy(); h_ok = ok.cpu().numpy(); h_info = info[:n].cpu().numpy()
+            t0 = time.time()
+            # float list decoders: the reference object keeps its best path metric across decode() calls (no reset in
+            # PathList::setFirstPath), so its float rounding depends on the frames it decoded before; the comparison is
+            # against a fresh object per frame, and the disagreement of the long-lived object with ITSELF is reported
+            fresh = isf and L > 1
+            exp, eok = refshim.decode_batch(N, L, np.array(fz, np.uint32), kind, h_llr, crc_bits=crc, crc_type="crc", threads=threads, fresh=fresh)
+            t_ref += time.time() - t0
+            if fresh:
+                old, _ = refshim.decode_batch(N, L, np.array(fz, np.uint32), kind, h_llr, crc_bits=crc, crc_type="crc", threads=threads)
+                drift += int((old != exp).any(axis=1).sum())
+            bad = (h_out != exp).any(axis=1)
+            mism += int(bad.sum()); okm += int((h_ok != eok).sum())
+            fe_gpu += int((h_out != h_info).any(axis=1).sum()); fe_ref += int((exp != h_info).any(axis=1).sum())
+        lo_ci, hi_ci = cp_interval(fe_ref, F)
+        row = {"case": case, "ebn0_db": eb, "frames": F, "mismatching_frames": mism, "mismatching_verdicts": okm,
+               "agreement": 1 - mism / F, "bler_gpu": fe_gpu / F, "bler_ref": fe_ref / F, "ref_ci95": [lo_ci, hi_ci],
+               "bler_inside_ci": lo_ci <= fe_gpu / F <= hi_ci, "ref_seconds": round(t_ref, 2), "ref_threads": threads,
+               "reference_fresh_object_per_frame": bool(isf and L > 1), "reference_long_lived_object_vs_fresh_mismatches": drift}
+        report.append(row); print(json.dumps(row), flush=True)
+bad = [r for r in report if (("char" in r["case"]) and (r["mismatching_frames"] or r["mismatching_verdicts"])) or r["agreement"] < 0.9999 or not r["bler_inside_ci"]]
+print("PARITY SWEEP:", "PASS" if not bad else f"FAIL ({len(bad)} rows)")
+if a.out:
+    json.dump({"rows": report, "pass": not bad}, open(a.out, "w"), indent=1)
+sys.exit(1 if bad else 0)
