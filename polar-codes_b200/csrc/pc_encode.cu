@@ -20,9 +20,9 @@ struct EncParams {
     unsigned long long B;
     int S, K, kb, kbp;    // kbp = kb rounded up to a multiple of 4 (row stride in shared memory)
     int systematic;
-    const uint2* runs;
-    const uint32_t* first;
-    const uint32_t* info_mask;
+    int direct;           // info rows are word aligned: read them without staging
+    const uint32_t* cnt;       // cnt[w] = number of info positions below code word w (N/32 + 1 entries)
+    const uint32_t* info_mask; // bit i%32 of word i/32 set for non-frozen positions
 };
 
 PC_HD uint32_t inword_transform(uint32_t x, int S)
@@ -34,6 +34,23 @@ PC_HD uint32_t inword_transform(uint32_t x, int S)
     if (S > 3) x ^= (x >> 8) & 0x00FF00FFu & lim;
     if (S > 4) x ^= (x >> 16) & 0x0000FFFFu;
     return x;
+}
+
+// software PDEP: the low bits of `src` go, in order, to the set bits of `mask`, one contiguous run of the mask at a
+// time (polar information sets are made of few long runs per word)
+__device__ __forceinline__ uint32_t deposit_bits(uint32_t src, uint32_t mask)
+{
+    uint32_t out = 0;
+    while (mask) {
+        const uint32_t low = mask & (0u - mask);   // lowest set bit
+        const uint32_t t = mask + low;             // clears the lowest run (carry ripples through it)
+        const uint32_t run = mask & ~t;            // the lowest run of ones
+        const int pos = __ffs(low) - 1, len = __popc(run);
+        out |= (src << pos) & run;
+        src >>= len;
+        mask &= t;
+    }
+    return out;
 }
 
 template <int R>
@@ -68,28 +85,47 @@ __global__ void __launch_bounds__(256) k_encode(const EncParams p)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int lig = lane % G, slot = warp * per_warp + lane / G; // codeword slot inside the CTA
     const int nbytes = p.S >= 3 ? (1 << (p.S - 3)) : 1;
+    // the lane's code words never change: keep their masks and info offsets in registers (short and medium codes)
+    constexpr bool HOIST = R <= 16;
+    constexpr int HR = HOIST ? R : 1;
+    uint32_t mk[HR], cn_[HR];
+#pragma unroll
+    for (int r = 0; r < HR; ++r) {
+        mk[r] = HOIST ? __ldg(p.info_mask + r * 32 + lig) : 0u;
+        cn_[r] = HOIST ? __ldg(p.cnt + r * 32 + lig) : 0u;
+    }
     for (unsigned long long base = (unsigned long long)blockIdx.x * per_cta; base < p.B;
          base += (unsigned long long)gridDim.x * per_cta) {
         const unsigned long long left = p.B - base;
         const int ncw = left < (unsigned long long)per_cta ? (int)left : per_cta;
-        // stage the contiguous info rows of this batch, padded to a 4-byte row stride
-        __syncthreads();
-        const uint8_t* src = p.info + base * (unsigned long long)p.kb;
-        for (int i = threadIdx.x; i < ncw * p.kb; i += blockDim.x) s_info[(i / p.kb) * p.kbp + (i % p.kb)] = src[i];
-        __syncthreads();
         const bool live = slot < ncw;
-        const uint32_t* row = reinterpret_cast<const uint32_t*>(s_info + (live ? slot : 0) * p.kbp);
+        const uint32_t* row;
+        if (p.direct) {
+            // rows are 4-byte aligned (kb % 4 == 0): the lanes of a group read their info words straight from HBM
+            // (one row is 1-2 cache lines shared by the whole group), no staging, no CTA barrier
+            row = reinterpret_cast<const uint32_t*>(p.info + (base + (live ? slot : 0)) * (unsigned long long)p.kb);
+        } else {
+            // stage the contiguous info rows of this batch, padded to a 4-byte row stride
+            __syncthreads();
+            const uint8_t* src = p.info + base * (unsigned long long)p.kb;
+            for (int i = threadIdx.x; i < ncw * p.kb; i += blockDim.x) s_info[(i / p.kb) * p.kbp + (i % p.kb)] = src[i];
+            __syncthreads();
+            row = reinterpret_cast<const uint32_t*>(s_info + (live ? slot : 0) * p.kbp);
+        }
+        // scatter (PackedContainer::insertPackedInformationBits): code word w takes the info bits cnt[w] .. cnt[w+1]-1,
+        // a contiguous piece of the info stream (funnel shift of two row words), deposited at the set bits of its mask
         uint32_t x[R];
+        const int nrw = p.kbp >> 2;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            const int w = r * 32 + lig;
+            const uint32_t m = HOIST ? mk[r < HR ? r : 0] : __ldg(p.info_mask + r * 32 + lig);
+            const uint32_t cn = HOIST ? cn_[r < HR ? r : 0] : __ldg(p.cnt + r * 32 + lig);
             uint32_t acc = 0;
-            const uint32_t r0 = p.first[w], r1 = p.first[w + 1];
-            for (uint32_t k = r0; k < r1; ++k) {
-                const uint2 run = p.runs[k];
-                const uint32_t sshift = (run.x >> 11) & 31u, len = ((run.x >> 16) & 31u) + 1u, dshift = (run.x >> 21) & 31u;
-                const uint32_t iw = msb_first_word(row[run.y]); // info bits, LSB first
-                acc |= ((iw >> dshift) & lowmask((int)len)) << sshift;
+            if (m) {
+                const int idx = (int)(cn >> 5), sh = (int)(cn & 31u);
+                const uint32_t lo = msb_first_word(p.direct ? __ldg(row + idx) : row[idx]); // info bits, LSB first
+                const uint32_t hi = (idx + 1 < nrw) ? msb_first_word(p.direct ? __ldg(row + idx + 1) : row[idx + 1]) : 0u;
+                acc = deposit_bits(__funnelshift_r(lo, hi, sh), m);
             }
             x[r] = acc;
         }
@@ -124,34 +160,17 @@ static cudaError_t launch_encode(const EncParams& p, int grid, size_t smem, cuda
     return cudaGetLastError();
 }
 
-// host side of the scatter tables: the decoder's gather runs, grouped by the code word they touch
+// host side of the scatter table: prefix count of information positions per code word
 int build_encoder_tables(pc_code* c)
 {
     const FastSscProgram& g = c->prog;
     const int W = (c->N + 31) / 32;
-    std::vector<uint2> runs;
-    std::vector<uint32_t> first(W + 1, 0u);
-    std::vector<std::vector<uint2>> by_word(W);
-    uint32_t dword = 0;
-    for (uint32_t run : g.runs) {
-        const uint32_t sword = run & 0x7FFu, last = (run >> 26) & 1u;
-        by_word[sword].push_back(make_uint2(run, dword));
-        if (last) dword++;
-    }
-    for (int w = 0; w < W; ++w) {
-        first[w] = (uint32_t)runs.size();
-        runs.insert(runs.end(), by_word[w].begin(), by_word[w].end());
-    }
-    first[W] = (uint32_t)runs.size();
-    cudaFree(c->d_enc_runs);
+    std::vector<uint32_t> cnt(W + 1, 0u);
+    for (int w = 0; w < W; ++w) cnt[w + 1] = cnt[w] + (uint32_t)__builtin_popcount(g.info_mask[w]);
     cudaFree(c->d_enc_first);
-    c->d_enc_runs = nullptr;
     c->d_enc_first = nullptr;
-    cudaError_t e = cudaMalloc(&c->d_enc_runs, (runs.size() + 1) * sizeof(uint2));
-    if (e == cudaSuccess) e = cudaMalloc(&c->d_enc_first, first.size() * 4);
-    if (e == cudaSuccess && !runs.empty())
-        e = cudaMemcpy(c->d_enc_runs, runs.data(), runs.size() * sizeof(uint2), cudaMemcpyHostToDevice);
-    if (e == cudaSuccess) e = cudaMemcpy(c->d_enc_first, first.data(), first.size() * 4, cudaMemcpyHostToDevice);
+    cudaError_t e = cudaMalloc(&c->d_enc_first, cnt.size() * 4);
+    if (e == cudaSuccess) e = cudaMemcpy(c->d_enc_first, cnt.data(), cnt.size() * 4, cudaMemcpyHostToDevice);
     return e == cudaSuccess ? PC_OK : cuda_fail(e, "encoder tables");
 }
 
@@ -167,8 +186,8 @@ int encode_device_raw(pc_code* c, const uint8_t* src, uint8_t* d_code, size_t B,
     p.kb = kb;
     p.kbp = (kb + 3) & ~3;
     p.systematic = c->systematic;
-    p.runs = c->d_enc_runs;
-    p.first = c->d_enc_first;
+    p.direct = (kb % 4 == 0 && (reinterpret_cast<uintptr_t>(src) & 3u) == 0) ? 1 : 0;
+    p.cnt = c->d_enc_first;
     p.info_mask = c->d_info_mask;
     const int W = c->S > 5 ? (1 << (c->S - 5)) : 1, G = W < 32 ? W : 32, R = W / G;
     const int per_cta = 8 * (32 / G);

@@ -26,8 +26,8 @@ struct pc_code {
     uint32_t* d_lut = nullptr;        // K info positions
     uint32_t* d_info_mask = nullptr;  // N/32 words
     // encoder tables: info-bit scatter runs grouped by code word (pc_encode.cu)
-    uint2* d_enc_runs = nullptr;      // (mk_run word, info word index)
-    uint32_t* d_enc_first = nullptr;  // first run of each code word, N/32 + 1 entries
+    uint2* d_enc_runs = nullptr;      // unused since the encoder deposits bits from (mask, prefix count)
+    uint32_t* d_enc_first = nullptr;  // number of info positions below each code word, N/32 + 1 entries
     uint8_t* d_enc_info = nullptr;    // scratch copy of the info blocks when the detector writes check bytes
     size_t enc_info_bytes = 0;
     void* d_quant = nullptr;          // int8 LLRs quantised from a float batch

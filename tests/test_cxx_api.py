@@ -21,7 +21,11 @@ def cxx(pcb):
     deps = [os.path.join(ROOT, "tests", "cxx_api.cpp"), os.path.join(ROOT, "include", "polarcode_b200.hpp"),
             os.path.join(ROOT, "include", "polar_b200.h")]
     if not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(d) for d in deps):
-        subprocess.check_call(["g++", "-std=c++17", "-O2", "-fPIC", "-shared", "-Wall", "-o", so, deps[0],
+        # -Bsymbolic + hidden visibility: the mirror has the reference's class names ON PURPOSE, and the test process
+        # also holds the real libPolarCode.so (RTLD_GLOBAL, the oracle); without this the dynamic linker would bind the
+        # harness's inline PolarCode::ErrorDetection::create(...) to the reference's symbol of the same name
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-fPIC", "-shared", "-Wall", "-fvisibility-inlines-hidden",
+                               "-Wl,-Bsymbolic", "-o", so, deps[0],
                                "-L" + os.path.join(ROOT, "polar-codes_b200"), "-lpolar_b200",
                                "-Wl,-rpath,$ORIGIN/../../polar-codes_b200"])
     return ctypes.CDLL(so)
