@@ -1,8 +1,12 @@
 // fp32 Fast-SSC batch decoder kernel for sm_100a: one thread per codeword interpreting the float node program
 // (pc_fastssc_f32_core.h). Replaces FastSscAvxFloat::decode (reference src/polarcode/decoding/fastssc_avx_float.cpp:940-955).
 // The float LLR tree of a codeword is 4 N bytes, far beyond shared memory at useful occupancy, so the per-thread
-// stages live in a thread-interleaved, L2-resident arena (every warp access to one element index is one coalesced
-// 128-byte transaction); the small stages (n <= 16) and the decision words sit in shared memory.
+// stages and the decision words live in a thread-interleaved arena (every warp access to one element index is one
+// coalesced 128-byte transaction). Measured (profiles/r01_fastssc_f32_full_v1.txt): at N=1024 the arena of 75 776
+// threads is 320 MB, far beyond the L2, and the kernel is DRAM-latency bound (long_scoreboard 22.7 cycles per issue,
+// 10 GB of DRAM traffic per 262 144 frames against 1.1 GB algorithmic). Moving stages <= 5 to shared memory through
+// generic pointers measured SLOWER (13.8 vs 17.5 Gbit/s); the fix is a warp per codeword with the tree in shared
+// memory, next round.
 // Compiled without FMA contraction (-fmad=false is applied through __fadd_rn in the core).
 #include "pc_fastssc_f32_core.h"
 #include "pc_kernels.cuh"
