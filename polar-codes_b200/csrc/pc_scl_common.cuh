@@ -113,6 +113,65 @@ __device__ __forceinline__ void scl_sort(const LN& c, V (&v)[C], int newP, V& ou
     }
 }
 
+// The same selection sort for INTEGER metrics with |metric| < 2^22 (int8 SCL, N <= 32768): value and current position
+// are packed into one key, (value << 8) | (255 - position), so "first maximum" is a plain integer max (a larger
+// value wins, equal values go to the lower position) and one pass costs one max-reduction instead of a compare
+// network over (value, position) pairs. The swap semantics are kept: the pass-i maximum is FINAL for new path i (its
+// value and candidate index go straight to lane i), the former content of slot i moves to the maximum's slot and
+// takes that slot's position bits; a finalised slot is marked consumed. The pass loop is unrolled over the slot index
+// inside a lane so that slot i is a compile-time register.
+template <int C, class LN>
+__device__ __forceinline__ void scl_sort_packed(const LN& c, const int (&v)[C], int newP, int& out_val, int& out_idx)
+{
+    static_assert((C & (C - 1)) == 0, "C must be a power of two");
+    constexpr int LOGC = C == 2 ? 1 : (C == 4 ? 2 : 3);
+    const int size = C * c.P, G = c.G;
+    int kv[C], idx[C];
+#pragma unroll
+    for (int k = 0; k < C; ++k) {
+        const int pos = c.l * C + k;
+        idx[k] = pos;
+        kv[k] = pos < size ? (int)(((unsigned)v[k] << 8) | (unsigned)(255 - pos)) : INT_MIN;
+    }
+    const int lim = size - 1 < newP ? size - 1 : newP;
+    out_val = 0;
+    out_idx = 0;
+    for (int li = 0; li * C < lim; ++li) {
+#pragma unroll
+        for (int ki = 0; ki < C; ++ki) {
+            const int i = li * C + ki;
+            if (i < lim) { // uniform
+                int m = kv[0];
+#pragma unroll
+                for (int k = 1; k < C; ++k) m = max(m, kv[k]);
+                for (int off = G >> 1; off; off >>= 1) m = max(m, __shfl_xor_sync(0xFFFFFFFFu, m, off));
+                const int bp = 255 - (m & 255), lm = bp >> LOGC, km = bp & (C - 1);
+                const int im = __shfl_sync(0xFFFFFFFFu, sel(idx, km), lm, G);
+                const int vi = __shfl_sync(0xFFFFFFFFu, kv[ki], li, G);
+                const int ii = __shfl_sync(0xFFFFFFFFu, idx[ki], li, G);
+                if (c.l == lm) {
+                    put(kv, km, (int)(((unsigned)vi & ~255u) | (unsigned)(255 - bp)));
+                    put(idx, km, ii);
+                }
+                if (c.l == li) kv[ki] = INT_MIN; // consumed (also when the maximum already sat in slot i)
+                if (c.l == i) {
+                    out_val = m >> 8;
+                    out_idx = im;
+                }
+            }
+        }
+    }
+    if (lim < newP) { // size == newP: the last slot was never the target of a pass and keeps its content
+        const int lj = lim >> LOGC, kj = lim & (C - 1);
+        const int vj = __shfl_sync(0xFFFFFFFFu, sel(kv, kj), lj, G);
+        const int ij = __shfl_sync(0xFFFFFFFFu, sel(idx, kj), lj, G);
+        if (c.l == lim) {
+            out_val = vj >> 8;
+            out_idx = ij;
+        }
+    }
+}
+
 // Indices[] bookkeeping of findWeakLlrs (arrayfuncs.h:209-231): the first four entries plus a patch list for
 // positions >= 4 (at most four swaps happen). swap(i, bp) is called once per pass with i < 4.
 struct WeakIdx {

@@ -43,15 +43,15 @@ struct Lane {
     // LLR stage starting at word offset `off` (p.llr_off[s]) in lane `owner`'s space, resolved once per node step
     struct View {
         uint32_t* p;
-        size_t stride;
-        __device__ __forceinline__ uint32_t operator[](int w) const { return p[(size_t)w * stride]; }
-        __device__ __forceinline__ void set(int w, uint32_t v) const { p[(size_t)w * stride] = v; }
+        uint32_t stride; // word index * stride stays below 2^32 (the planner bounds arena words * lanes)
+        __device__ __forceinline__ uint32_t operator[](int w) const { return p[(uint32_t)w * stride]; }
+        __device__ __forceinline__ void set(int w, uint32_t v) const { p[(uint32_t)w * stride] = v; }
     };
     __device__ __forceinline__ View view(int off, uint32_t owner) const
     {
         const ptrdiff_t d = (int)owner - l;
-        if (off & kArena) return View{ ar + (size_t)(off & (kArena - 1)) * AS + d, AS };
-        return View{ sm + (size_t)off * T + d, (size_t)T };
+        if (off & kArena) return View{ ar + (size_t)(off & (kArena - 1)) * AS + d, (uint32_t)AS };
+        return View{ sm + (size_t)off * T + d, (uint32_t)T };
     }
 };
 
@@ -220,7 +220,7 @@ __device__ __forceinline__ void scl_rep(Lane& c, const SclParams& p, int s, int 
     }
     const int newP = 2 * c.P < p.L ? 2 * c.P : p.L;
     int val, idx;
-    scl_sort<2>(c, v, newP, val, idx);
+    scl_sort_packed<2>(c, v, newP, val, idx);
     const bool live = c.l < newP;
     const int sp = live ? idx >> 1 : 0;
     scl_fork(c, sp, val, newP);
@@ -248,7 +248,7 @@ __device__ __forceinline__ void scl_r1(Lane& c, const SclParams& p, int s, int s
     __syncwarp();
     const int newP = 4 * c.P < p.L ? 4 * c.P : p.L;
     int val, idx;
-    scl_sort<4>(c, v, newP, val, idx);
+    scl_sort_packed<4>(c, v, newP, val, idx);
     const bool live = c.l < newP;
     const int sp = live ? idx >> 2 : 0;
     int fi[4];
@@ -290,7 +290,7 @@ __device__ __forceinline__ void scl_spc(Lane& c, const SclParams& p, int s, int 
     __syncwarp();
     const int newP = 8 * c.P < p.L ? 8 * c.P : p.L;
     int val, idx;
-    scl_sort<8>(c, v, newP, val, idx);
+    scl_sort_packed<8>(c, v, newP, val, idx);
     const bool live = c.l < newP;
     const int sp = live ? idx >> 3 : 0;
     int fi[4];
@@ -423,7 +423,7 @@ int plan_scl_i8(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, S
         *msg = "list size must be in [1, 32]";
         return 1;
     }
-    if (S > 17) {
+    if (S > 15) { // path metrics are packed into 24-bit sort keys (scl_sort_packed): |metric| <= 127 N < 2^22
         *msg = "block length too large for the SCL kernel";
         return 1;
     }
@@ -502,6 +502,10 @@ int plan_scl_i8(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, S
     out.smem_bytes = 1024 + 4 * (size_t)w * T;
     out.grid = sms * per_sm;
     p.arena_stride = (size_t)out.grid * T;
+    if ((unsigned long long)aw * p.arena_stride >= (1ull << 32)) {
+        *msg = "SCL arena too large for 32-bit word indexing";
+        return 1;
+    }
     return 0;
 }
 
