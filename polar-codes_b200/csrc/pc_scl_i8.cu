@@ -141,14 +141,34 @@ __device__ __forceinline__ void scl_find_weak(const Lane& c, int off, int n, int
     const int nw = (n + 3) >> 2;
     for (int i = 0; i < lim; ++i) {
         int bv = 256, bp = i;
-        for (int w = i >> 2; w < nw; ++w) {
-            const uint32_t x = v[w];
+        if (nw <= 256) {
+            // first minimum of [i, n) as the minimum of 16-bit keys (|llr| << 8 | word index), one running minimum per
+            // byte lane (VIMNMX.U16x2); excluded bytes are forced to 0xFF, above every |llr| <= 127
+            uint32_t me = 0xFFFFFFFFu, mo = 0xFFFFFFFFu;
+            for (int w = 0; w < nw; ++w) {
+                uint32_t x = v[w];
+                if (w == 0) x |= bytemask(i) | (n < 4 ? ~bytemask(n) : 0u);
+                me = __vminu2(me, __byte_perm(x, (uint32_t)w, 0x2404));
+                mo = __vminu2(mo, __byte_perm(x, (uint32_t)w, 0x3414));
+            }
+            uint32_t best = 0xFFFFFFFFu;
 #pragma unroll
             for (int b = 0; b < 4; ++b) {
-                const int pos = 4 * w + b, val = (int)((x >> (8 * b)) & 0xFFu);
-                if (pos >= i && pos < n && val < bv) {
-                    bv = val;
-                    bp = pos;
+                const uint32_t k = ((b & 1) ? mo : me) >> ((b & 2) ? 16 : 0) & 0xFFFFu;
+                best = min(best, ((k >> 8) << 10) | ((k & 0xFFu) << 2) | (uint32_t)b);
+            }
+            bv = (int)(best >> 10);
+            bp = (int)(best & 1023u);
+        } else {
+            for (int w = i >> 2; w < nw; ++w) {
+                const uint32_t x = v[w];
+#pragma unroll
+                for (int b = 0; b < 4; ++b) {
+                    const int pos = 4 * w + b, val = (int)((x >> (8 * b)) & 0xFFu);
+                    if (pos >= i && pos < n && val < bv) {
+                        bv = val;
+                        bp = pos;
+                    }
                 }
             }
         }

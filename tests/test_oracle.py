@@ -188,3 +188,38 @@ def test_reference_float_list_decoder_keeps_metric_across_frames(ref):
     a, _ = ref.decode_batch(N, L, fz, "char", i8, crc_bits=0, threads=1)
     b, _ = ref.decode_batch(N, L, fz, "char", i8, crc_bits=0, threads=4, fresh=True)
     assert np.array_equal(a, b)
+
+
+# ---- list decoder restatement (oracle/pc_oracle_scl.c) -------------------------------------------------------------
+GOLD_LIST = np.load(os.path.join(os.path.dirname(__file__), "golden", "reference_vectors_list.npz"))
+SCLC_KEYS = sorted(k[:-4] for k in GOLD_LIST.files if k.startswith("sclc_") and k.endswith("_llr"))
+
+
+def _crc_kind(bits, typ):
+    return 17 if (bits == 16 and typ == "crcnr") else bits
+
+
+@pytest.mark.parametrize("key", SCLC_KEYS)
+def test_scl_restatement_golden(orc, key):
+    """SclFipChar outputs recorded by tests/golden/make_golden_list.py"""
+    _, N, K, L, cb, ct = key.split("_")
+    N, L = int(N), int(L)
+    got, ok = orc.scl_i8_decode(N, GOLD_LIST[key + "_frozen"], L, GOLD_LIST[key + "_llr"], crc=_crc_kind(int(cb), ct))
+    assert np.array_equal(got, GOLD_LIST[key + "_info"])
+    assert np.array_equal(ok, GOLD_LIST[key + "_ok"])
+
+
+@pytest.mark.parametrize("N,K,L", [(1024, 512, 8), (256, 128, 4), (64, 32, 2), (128, 96, 16), (512, 128, 32), (16, 8, 4)])
+def test_scl_restatement_differential(orc, ref, N, K, L):
+    """random noisy all-zero codewords, saturated and uniformly random LLRs: the adversarial inputs for the partial
+    sort and the weak-LLR search (many equal metrics)"""
+    from conftest import awgn_llr_i8
+    rng = np.random.default_rng(N + L)
+    fz = ref.frozen_bits(N, K, 0.0)
+    B = 60 if N <= 256 else 24
+    llr = np.concatenate([awgn_llr_i8(rng, B, N, 1.0, K / N, 10.0), awgn_llr_i8(rng, B, N, 3.0, K / N, 50.0),
+                          rng.choice(np.array([-128, -127, 127, 0], np.int8), (B // 2, N)),
+                          rng.integers(-128, 128, (B // 2, N), dtype=np.int8)])
+    exp, eok = ref.decode_batch(N, L, fz, "char", llr, crc_bits=8)
+    got, ok = orc.scl_i8_decode(N, fz, L, llr, crc=8)
+    assert np.array_equal(got, exp) and np.array_equal(ok, eok)
