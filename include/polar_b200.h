@@ -40,7 +40,11 @@ enum {
     PC_DEC_FASTSSC_F32 = 1, /* 'float', L == 1 : FastSscAvxFloat */
     PC_DEC_SCL_I8 = 2,     /* 'char',  L  > 1 : SclFipChar      */
     PC_DEC_SCL_F32 = 3,    /* 'float', L  > 1 : SclAvxFloat     */
-    PC_DEC_ADAPTIVE_F32 = 4 /* 'mixed', L  > 1 : AdaptiveFloat   */
+    PC_DEC_ADAPTIVE_F32 = 4, /* 'mixed', L  > 1 : AdaptiveFloat   */
+    /* the two wrappers pcsim builds directly (src/simulation/simulator.cpp:721-733), not reachable through
+     * Decoding::create's type strings: */
+    PC_DEC_ADAPTIVE_I8 = 5,   /* AdaptiveChar  (adaptive_char.cpp:35-46):  FastSscFipChar, then SclFipChar  */
+    PC_DEC_ADAPTIVE_MIXED = 6 /* AdaptiveMixed (adaptive_mixed.cpp:36-47): FastSscFipChar, then SclAvxFloat */
 };
 
 /* error detectors -- ErrorDetection::create(size, type) (errordetector.cpp:27-88) */

@@ -414,6 +414,34 @@ private:
     }
 };
 
+// The reference's concrete decoder classes as thin subclasses that only pick the kind, so that code which constructs
+// them directly (pcsim's SimulationWorker::setCoders, src/simulation/simulator.cpp:703-765) compiles against this
+// header unchanged. Unlike makeDecoder, the reference constructors install no detector (the Dummy stays).
+#define PC_B200_DECODER_CLASS_1(NAME, KIND)                                                                        \
+    class NAME : public Decoder                                                                                    \
+    {                                                                                                              \
+    public:                                                                                                        \
+        NAME(size_t blockLength, const std::vector<unsigned>& frozenBits) : Decoder(blockLength, 1, frozenBits, KIND) {} \
+    };
+#define PC_B200_DECODER_CLASS_L(NAME, KIND)                                                                        \
+    class NAME : public Decoder                                                                                    \
+    {                                                                                                              \
+    public:                                                                                                        \
+        NAME(size_t blockLength, size_t listSize, const std::vector<unsigned>& frozenBits)                         \
+            : Decoder(blockLength, listSize, frozenBits, KIND)                                                     \
+        {                                                                                                          \
+        }                                                                                                          \
+    };
+PC_B200_DECODER_CLASS_1(FastSscFipChar, PC_DEC_FASTSSC_I8)   // fastssc_fip_char.h
+PC_B200_DECODER_CLASS_1(FastSscAvxFloat, PC_DEC_FASTSSC_F32) // fastssc_avx_float.h
+PC_B200_DECODER_CLASS_L(SclFipChar, PC_DEC_SCL_I8)           // scl_fip_char.h
+PC_B200_DECODER_CLASS_L(SclAvxFloat, PC_DEC_SCL_F32)         // scl_avx_float.h
+PC_B200_DECODER_CLASS_L(AdaptiveFloat, PC_DEC_ADAPTIVE_F32)  // adaptive_float.h
+PC_B200_DECODER_CLASS_L(AdaptiveChar, PC_DEC_ADAPTIVE_I8)    // adaptive_char.h
+PC_B200_DECODER_CLASS_L(AdaptiveMixed, PC_DEC_ADAPTIVE_MIXED) // adaptive_mixed.h
+#undef PC_B200_DECODER_CLASS_1
+#undef PC_B200_DECODER_CLASS_L
+
 // decoder.cpp:54-87. decoder_impl: 0 char, 1 float, 2 mixed (3 = scan is rejected: there is no CPU fallback).
 // Installs a CRC-8 detector like the reference (:85; the object is leaked there too).
 inline Decoder* makeDecoder(size_t blockLength, size_t listSize, const std::vector<unsigned>& frozenBits, int decoder_impl = 0)

@@ -11,6 +11,8 @@
 // Threading mirrors pcsim's worker model (src/simulation/simulator.cpp:87-116): one private codec object
 // per std::thread, frames split into contiguous slices.
 #include <polarcode/construction/constructor.h>
+#include <polarcode/decoding/adaptive_char.h>
+#include <polarcode/decoding/adaptive_mixed.h>
 #include <polarcode/decoding/decoder.h>
 #include <polarcode/encoding/butterfly_fip_packed.h>
 #include <polarcode/errordetection/errordetector.h>
@@ -22,6 +24,15 @@
 #include <vector>
 
 using namespace PolarCode;
+
+// "adaptive_char" / "adaptive_mixed": the two wrappers pcsim constructs by class (simulator.cpp:721-733); everything
+// else goes through the reference factory. (They carry "char" / "mixed" in their names, so test them first.)
+static Decoding::Decoder* make_decoder(int N, int L, const std::vector<unsigned>& fz, const std::string& kind)
+{
+    if (kind == "adaptive_char") return new Decoding::AdaptiveChar(N, L, fz);
+    if (kind == "adaptive_mixed") return new Decoding::AdaptiveMixed(N, L, fz);
+    return Decoding::create(N, L, fz, kind);
+}
 
 static std::vector<unsigned> mkfrozen(const unsigned* f, int nf) { return std::vector<unsigned>(f, f + nf); }
 
@@ -39,7 +50,7 @@ int ref_frozen_bits(int N, int K, float dsnr, const char* type, unsigned* out)
     }
 }
 
-// kind: "char" / "float" / "mixed"; crc_bits<0 => keep the factory default (CRC-8, decoder.cpp:85);
+// kind: "char" / "float" / "mixed" / "adaptive_char" / "adaptive_mixed" (the last two take float LLRs only); crc_bits<0 => keep the factory default (CRC-8, decoder.cpp:85);
 // is_float: llr points to float[B][N] else int8[B][N]. Returns seconds spent inside the decode loops
 // (max over threads), or a negative value on error.
 // fresh != 0: a NEW decoder object for every frame. SclAvxFloat never resets the metric of path 0 between decode()
@@ -70,7 +81,7 @@ double ref_decode_batch2(int N, int L, const unsigned* frozen, int nf, const cha
         auto fz = mkfrozen(frozen, nf);
         for (int t = 0; t < threads; ++t) {
             pool.emplace_back([&, t]() {
-                Decoding::Decoder* dec = Decoding::create(N, L, fz, std::string(kind));
+                Decoding::Decoder* dec = make_decoder(N, L, fz, std::string(kind));
                 ErrorDetection::Detector* det = nullptr;
                 if (crc_bits >= 0) {
                     det = ErrorDetection::create(crc_bits, std::string(crc_type));
@@ -85,7 +96,7 @@ double ref_decode_batch2(int N, int L, const unsigned* frozen, int nf, const cha
                         bool res;
                         if (fresh && i > lo) {
                             delete dec;
-                            dec = Decoding::create(N, L, fz, std::string(kind));
+                            dec = make_decoder(N, L, fz, std::string(kind));
                             if (det) dec->setErrorDetection(det);
                             dec->setSystematic(systematic != 0);
                         }

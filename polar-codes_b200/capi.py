@@ -11,7 +11,8 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libpolar_b200.so")
 
-PC_DEC_FASTSSC_I8, PC_DEC_FASTSSC_F32, PC_DEC_SCL_I8, PC_DEC_SCL_F32, PC_DEC_ADAPTIVE_F32 = range(5)
+PC_DEC_FASTSSC_I8, PC_DEC_FASTSSC_F32, PC_DEC_SCL_I8, PC_DEC_SCL_F32, PC_DEC_ADAPTIVE_F32, PC_DEC_ADAPTIVE_I8, \
+    PC_DEC_ADAPTIVE_MIXED = range(7)
 PC_OK, PC_ERR_ARG, PC_ERR_CUDA, PC_ERR_UNSUPPORTED = range(4)
 
 _vp, _i, _sz, _u64 = ctypes.c_void_p, ctypes.c_int, ctypes.c_size_t, ctypes.c_uint64

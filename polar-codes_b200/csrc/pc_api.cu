@@ -269,7 +269,7 @@ int pc_crc_bytes(int crc_kind)
 
 pc_code* pc_code_create(int N, const unsigned* frozen, int n_frozen, int kind, int L)
 {
-    if (kind < PC_DEC_FASTSSC_I8 || kind > PC_DEC_ADAPTIVE_F32) {
+    if (kind < PC_DEC_FASTSSC_I8 || kind > PC_DEC_ADAPTIVE_MIXED) {
         set_error("Unknown PolarDecoder type!");
         return nullptr;
     }
@@ -310,7 +310,7 @@ pc_code* pc_code_create(int N, const unsigned* frozen, int n_frozen, int kind, i
             st = upload(&c->d_f32_code, c->f32_prog.code);
         }
     }
-    if (st == PC_OK && (kind == PC_DEC_SCL_I8)) {
+    if (st == PC_OK && (kind == PC_DEC_SCL_I8 || (kind == PC_DEC_ADAPTIVE_I8 && L > 1))) {
         if (!compile_scl(N, frozen, n_frozen, c->scl_prog, &msg)) {
             set_error(msg);
             st = PC_ERR_ARG;
@@ -318,7 +318,7 @@ pc_code* pc_code_create(int N, const unsigned* frozen, int n_frozen, int kind, i
             st = upload(&c->d_scl_code, c->scl_prog.code);
         }
     }
-    if (st == PC_OK && (kind == PC_DEC_SCL_F32 || (kind == PC_DEC_ADAPTIVE_F32 && L > 1))) {
+    if (st == PC_OK && (kind == PC_DEC_SCL_F32 || ((kind == PC_DEC_ADAPTIVE_F32 || kind == PC_DEC_ADAPTIVE_MIXED) && L > 1))) {
         if (!compile_scl(N, frozen, n_frozen, c->sclf_prog, &msg, true)) {
             set_error(msg);
             st = PC_ERR_ARG;
@@ -377,6 +377,7 @@ void pc_code_destroy(pc_code* c)
     cudaFree(c->d_stage_ok);
     for (auto& s : c->streams)
         if (s) cudaStreamDestroy(s);
+    if (c->ev_decode) cudaEventDestroy(c->ev_decode);
     delete c;
 }
 

@@ -75,6 +75,7 @@ struct pc_code {
     uint8_t* d_stage_ok = nullptr;
     size_t stage_in_bytes = 0, stage_out_bytes = 0, stage_ok_bytes = 0;
     cudaStream_t streams[2] = { nullptr, nullptr };
+    cudaEvent_t ev_decode = nullptr; // chains the decode kernels of consecutive host-batch slices
 };
 
 namespace pc {

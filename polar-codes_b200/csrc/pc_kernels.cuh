@@ -42,6 +42,8 @@ struct SclParams {
     uint8_t* info;
     uint8_t* ok;
     unsigned long long B;
+    const unsigned* frame_idx;         // optional indirection (adaptive second pass): frame = frame_idx[i]
+    const unsigned long long* count;   // optional device-side frame count (overrides B when non-null)
     int S, K, L, G, nruns, systematic, root_leaf;
     CrcSpec crc;
     const uint32_t* code;
@@ -62,7 +64,8 @@ struct SclLaunch {
     size_t smem_bytes;
 };
 
-cudaError_t launch_scl_i8(const SclLaunch& L, const int8_t* d_llr, uint8_t* d_info, uint8_t* d_ok, size_t B, cudaStream_t st);
+cudaError_t launch_scl_i8(const SclLaunch& L, const int8_t* d_llr, uint8_t* d_info, uint8_t* d_ok, size_t B,
+                          const unsigned* d_frame_idx, const unsigned long long* d_count, cudaStream_t st);
 int plan_scl_i8(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, SclLaunch& out, const char** msg);
 
 // ---- SCL fp32 (pc_scl_f32.cu) ----

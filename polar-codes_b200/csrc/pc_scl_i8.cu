@@ -15,8 +15,10 @@
 // * Hard decisions are one bit per element (only the MSB of the reference's bit bytes is ever consumed).
 // * extractBestPath: every lane gathers its path's info bits and runs the detector; the first passing lane (ballot)
 //   stores its block, else lane 0.
-// Storage: shared memory only, word-granular, thread-interleaved (word w of a lane at smem[w * T + tid]); other
-// lanes' buffers are read at their tid.
+// * Optional indirection (frame_idx / count) lets the adaptive decoders (AdaptiveChar) run this kernel over the
+//   frames whose Fast-SSC pass failed the detector only.
+// Storage: word-granular, thread-interleaved (word w of a lane at smem[w * T + tid]); other lanes' buffers are read
+// at their tid; the largest LLR stages live in an L2-resident arena (see kArena).
 #include <cstdlib>
 
 #include "pc_fastssc_i8_core.h"
@@ -342,11 +344,14 @@ __global__ void __launch_bounds__(256) k_scl_i8(const __grid_constant__ SclParam
     const int gpc = T / p.G; // codewords per CTA
     const int N = 1 << p.S, kb = (p.K + 7) >> 3;
     const unsigned gmask = (p.G == 32 ? 0xFFFFFFFFu : ((1u << p.G) - 1u)) << ((t & 31) & ~(p.G - 1));
-    const unsigned long long nbatch = (p.B + gpc - 1) / gpc;
+    const unsigned long long nfr = p.count ? *p.count : p.B;
+    if (nfr == 0) return;
+    const unsigned long long nbatch = (nfr + gpc - 1) / gpc;
     for (unsigned long long bi = blockIdx.x; bi < nbatch; bi += gridDim.x) {
         const unsigned long long fl = bi * gpc + (unsigned long long)(t / p.G);
-        const bool live_frame = fl < p.B;
-        const unsigned long long f = live_frame ? fl : p.B - 1;
+        const bool live_frame = fl < nfr;
+        unsigned long long f = live_frame ? fl : nfr - 1;
+        if (p.frame_idx) f = p.frame_idx[f];
         const int8_t* row = p.llr + f * N;
         c.P = 1;
         c.metric = 0;
@@ -420,13 +425,16 @@ __global__ void __launch_bounds__(256) k_scl_i8(const __grid_constant__ SclParam
     }
 }
 
-cudaError_t launch_scl_i8(const SclLaunch& L, const int8_t* d_llr, uint8_t* d_info, uint8_t* d_ok, size_t B, cudaStream_t st)
+cudaError_t launch_scl_i8(const SclLaunch& L, const int8_t* d_llr, uint8_t* d_info, uint8_t* d_ok, size_t B,
+                          const unsigned* d_frame_idx, const unsigned long long* d_count, cudaStream_t st)
 {
     SclParams p = L.p;
     p.llr = d_llr;
     p.info = d_info;
     p.ok = d_ok;
     p.B = B;
+    p.frame_idx = d_frame_idx;
+    p.count = d_count;
     cudaError_t e = cudaFuncSetAttribute(k_scl_i8, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes);
     if (e != cudaSuccess) return e;
     const int gpc = L.threads / p.G;

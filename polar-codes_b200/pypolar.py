@@ -31,6 +31,12 @@ def frozen_bits(blockLength, infoLength, designSNR, constructorType="BB"):
 
 
 def _kind_from_string(decoderType, listSize):
+    # extension: an int selects a PC_DEC_* kind directly (AdaptiveChar / AdaptiveMixed have no type string in the
+    # reference factory; pcsim constructs them by class, simulator.cpp:721-733)
+    if isinstance(decoderType, int):
+        if not 0 <= decoderType <= capi.PC_DEC_ADAPTIVE_MIXED:
+            raise RuntimeError("Unknown PolarDecoder type!")
+        return decoderType
     # Decoding::create (reference src/polarcode/decoding/decoder.cpp:26-52): lower-case substring match
     t = decoderType.lower()
     if "char" in t:

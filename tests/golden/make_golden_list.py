@@ -24,6 +24,9 @@ FLOAT_CASES = [(1024, 512, 8, 16, "crc", 32), (256, 128, 4, 8, "crc", 64), (64, 
                (512, 128, 8, 24, "crc", 32), (1024, 512, 1, 8, "crc", 32), (128, 64, 1, 8, "crc", 96),
                (2048, 1800, 1, 8, "crc", 8)]
 MIXED_CASES = [(1024, 512, 8, 16, "crc", 32), (256, 128, 4, 8, "crc", 64)]
+# AdaptiveChar / AdaptiveMixed (pcsim precision 8 / 832, simulator.cpp:721-733): float LLRs = 10 * y (setup.cpp:58)
+PCSIM_CASES = [("adaptive_char", 1024, 512, 8, 16, "crc", 48), ("adaptive_char", 256, 128, 4, 8, "crc", 64),
+               ("adaptive_mixed", 1024, 512, 8, 16, "crc", 32), ("adaptive_mixed", 128, 64, 4, 8, "crc", 64)]
 
 
 def transmit(rng, N, K, fz, crc_bits, crc_type, B, ebn0):
@@ -55,6 +58,13 @@ def main():
             info, ok = refshim.decode_batch(N, L, fz, kind, llr, crc_bits=cb, crc_type=ct, fresh=True)
             key = f"{kind}_{N}_{K}_{L}_{cb}_{ct}"
             out[key + "_frozen"], out[key + "_llr"], out[key + "_info"], out[key + "_ok"] = fz, llr.astype(np.float32), info, ok
+    for kind, N, K, L, cb, ct, B in PCSIM_CASES:
+        fz = refshim.frozen_bits(N, K, 0.0)
+        y = np.concatenate([transmit(rng, N, K, fz, cb, ct, B // 2, 1.0), transmit(rng, N, K, fz, cb, ct, B - B // 2, 2.5)])
+        llr = (np.float32(10.0) * y).astype(np.float32)
+        info, ok = refshim.decode_batch(N, L, fz, kind, llr, crc_bits=cb, crc_type=ct, fresh=True)
+        key = f"{kind.replace('_', '')}_{N}_{K}_{L}_{cb}_{ct}"
+        out[key + "_frozen"], out[key + "_llr"], out[key + "_info"], out[key + "_ok"] = fz, llr, info, ok
     np.savez_compressed(os.path.join(HERE, "reference_vectors_list.npz"), **out)
     print("wrote", len(out), "arrays")
 

@@ -10,7 +10,7 @@ pytestmark = pytest.mark.gpu
 
 GOLD = np.load(os.path.join(os.path.dirname(__file__), "golden", "reference_vectors_list.npz"))
 KEYS = sorted(k[:-4] for k in GOLD.files if k.endswith("_llr"))
-KIND = {"sclc": "char", "float": "float", "mixed": "mixed"}
+KIND = {"sclc": "char", "float": "float", "mixed": "mixed", "adaptivechar": 5, "adaptivemixed": 6}   # 5/6: PC_DEC_ADAPTIVE_I8/_MIXED
 
 
 @pytest.mark.parametrize("key", KEYS)
