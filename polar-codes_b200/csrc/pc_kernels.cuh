@@ -60,7 +60,7 @@ struct SclParams {
 
 struct SclLaunch {
     SclParams p;
-    int threads, grid;
+    int threads, grid, per_sm;
     size_t smem_bytes;
 };
 
@@ -92,7 +92,7 @@ struct SclFParams {
 };
 struct SclFLaunch {
     SclFParams p;
-    int threads, grid;
+    int threads, grid, per_sm;
     size_t smem_bytes;
 };
 cudaError_t launch_scl_f32(const SclFLaunch& L, const float* d_llr, uint8_t* d_info, uint8_t* d_ok, size_t B,

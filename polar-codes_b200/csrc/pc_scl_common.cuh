@@ -228,10 +228,23 @@ __device__ __forceinline__ void scl_comb(LN& c, const PR& p, int s, int side)
     if (active) {
         if (h >= 32) {
             const int hw = h >> 5;
-            for (int j = 0; j < hw; ++j) {
-                const uint32_t a = c.ld(lo + j, ol), b = c.ld(ro + j, orr);
-                c.st(dst + j, a ^ b);
-                c.st(dst + hw + j, b);
+            if (hw >= 4) {
+                for (int j = 0; j < hw; j += 4) { // loads first: the stores may alias them as far as the compiler knows
+                    uint32_t a[4], b[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) a[u] = c.ld(lo + j + u, ol), b[u] = c.ld(ro + j + u, orr);
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        c.st(dst + j + u, a[u] ^ b[u]);
+                        c.st(dst + hw + j + u, b[u]);
+                    }
+                }
+            } else {
+                for (int j = 0; j < hw; ++j) {
+                    const uint32_t a = c.ld(lo + j, ol), b = c.ld(ro + j, orr);
+                    c.st(dst + j, a ^ b);
+                    c.st(dst + hw + j, b);
+                }
             }
         } else {
             const uint32_t m = (1u << h) - 1u;

@@ -76,6 +76,35 @@ __device__ __forceinline__ void sclf_fg(FLane& c, const SclFParams& p, int s, co
     const FLane::View dst = c.view(s - 1, p.llr_off[s - 1], (uint32_t)c.l);
     if (active) {
         uint32_t bw = 0;
+        if (h >= 4) {
+            // four elements per step, all loads first (source and destination may alias as far as the compiler knows,
+            // so a rolled loop serialises load -> f/g -> store); the channel row as 16-byte loads
+            const bool row16 = from_row && ((reinterpret_cast<uintptr_t>(row) & 15u) == 0);
+            for (int j = 0; j < h; j += 4) {
+                float a[4], b[4], r[4];
+                if (row16) {
+                    const float4 va = __ldg(reinterpret_cast<const float4*>(row + j)), vb = __ldg(reinterpret_cast<const float4*>(row + h + j));
+                    a[0] = va.x, a[1] = va.y, a[2] = va.z, a[3] = va.w;
+                    b[0] = vb.x, b[1] = vb.y, b[2] = vb.z, b[3] = vb.w;
+                } else {
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        a[u] = from_row ? __ldg(row + j + u) : src[j + u];
+                        b[u] = from_row ? __ldg(row + h + j + u) : src[h + j + u];
+                    }
+                }
+                if (IS_G) {
+                    if ((j & 31) == 0) bw = c.ld(lb + (j >> 5), ol);
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) r[u] = g_f32(a[u], b[u], (bw >> ((j & 31) + u)) & 1u);
+                } else {
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) r[u] = f_f32(a[u], b[u]);
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) dst.set(j + u, r[u]);
+            }
+        } else
         for (int j = 0; j < h; ++j) {
             const float a = from_row ? __ldg(row + j) : src[j];
             const float b = from_row ? __ldg(row + h + j) : src[h + j];
@@ -391,6 +420,11 @@ cudaError_t launch_scl_f32(const SclFLaunch& L, const float* d_llr, uint8_t* d_i
     p.frame_idx = d_frame_idx;
     p.count = d_count;
     cudaError_t e = cudaFuncSetAttribute(k_scl_f32, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes);
+    // several CTAs per SM only fit when the L1/shared split is at its shared-memory maximum; a single CTA keeps the
+    // default split (the rest stays L1 for the channel rows and the arena)
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(k_scl_f32, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                 L.per_sm > 1 ? (int)cudaSharedmemCarveoutMaxShared : (int)cudaSharedmemCarveoutDefault);
     if (e != cudaSuccess) return e;
     const int gpc = L.threads / p.G;
     size_t nb = (B + gpc - 1) / gpc;
@@ -482,6 +516,7 @@ int plan_scl_f32(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, 
     out.threads = T;
     out.smem_bytes = 1024 + 4 * (size_t)w * T;
     out.grid = sms * per_sm;
+    out.per_sm = per_sm;
     // keep the arena within ~1 GiB
     while (out.grid > sms && (size_t)4 * e * out.grid * T > ((size_t)1 << 30)) out.grid -= sms;
     p.arena_stride = (size_t)out.grid * T;

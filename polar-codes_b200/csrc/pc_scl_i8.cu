@@ -19,6 +19,7 @@
 //   frames whose Fast-SSC pass failed the detector only.
 // Storage: word-granular, thread-interleaved (word w of a lane at smem[w * T + tid]); other lanes' buffers are read
 // at their tid; the largest LLR stages live in an L2-resident arena (see kArena).
+#include <cstdio>
 #include <cstdlib>
 
 #include "pc_fastssc_i8_core.h"
@@ -73,7 +74,36 @@ __device__ __forceinline__ void scl_fg(Lane& c, const SclParams& p, int s, const
     const int lb = p.bitL_off[s - 1];
     const Lane::View src = c.view(from_row ? p.llr_off[s - 1] : p.llr_off[s], o), dst = c.view(p.llr_off[s - 1], (uint32_t)c.l);
     if (active) {
-        if (h >= 4) {
+        if (h >= 16) {
+            // four words per step: all loads first (source and destination may alias as far as the compiler knows, so
+            // a rolled loop serialises load -> f/g -> store), the channel row as 16-byte loads
+            const int hw = h >> 2;
+            const bool row16 = from_row && ((reinterpret_cast<uintptr_t>(row) & 15u) == 0);
+            for (int j = 0; j < hw; j += 4) {
+                uint32_t a[4], b[4], r[4];
+                if (row16) {
+                    const uint4 va = __ldg(reinterpret_cast<const uint4*>(grow + j)), vb = __ldg(reinterpret_cast<const uint4*>(grow + hw + j));
+                    a[0] = va.x, a[1] = va.y, a[2] = va.z, a[3] = va.w;
+                    b[0] = vb.x, b[1] = vb.y, b[2] = vb.z, b[3] = vb.w;
+                } else {
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        a[u] = from_row ? __ldg(grow + j + u) : src[j + u];
+                        b[u] = from_row ? __ldg(grow + hw + j + u) : src[hw + j + u];
+                    }
+                }
+                if (IS_G) {
+                    const uint32_t bw = c.ld(lb + (j >> 3), ol) >> (4 * (j & 7));
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) r[u] = sw_g(a[u], b[u], sw_expand4(bw >> (4 * u)));
+                } else {
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) r[u] = sw_f(a[u], b[u]);
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) dst.set(j + u, r[u]);
+            }
+        } else if (h >= 4) {
             const int hw = h >> 2;
             for (int j = 0; j < hw; ++j) {
                 const uint32_t a = from_row ? __ldg(grow + j) : src[j];
@@ -108,6 +138,24 @@ __device__ __forceinline__ void llr_sums(const Lane& c, const SclParams& p, int 
     const Lane::View v = c.view(p.llr_off[s], (uint32_t)c.l);
     neg = 0;
     pos = 0;
+    if (nw >= 4) {
+        int n1 = 0, p1 = 0; // two accumulator pairs, four loads in flight
+        for (int j = 0; j < nw; j += 4) {
+            const uint32_t w0 = v[j], w1 = v[j + 1], w2 = v[j + 2], w3 = v[j + 3];
+            const uint32_t f0 = sw_signfill(w0), f1 = sw_signfill(w1), f2 = sw_signfill(w2), f3 = sw_signfill(w3);
+            neg = __dp4a((int)(w0 & f0), 0x01010101, neg);
+            pos = __dp4a((int)(w0 & ~f0), 0x01010101, pos);
+            n1 = __dp4a((int)(w1 & f1), 0x01010101, n1);
+            p1 = __dp4a((int)(w1 & ~f1), 0x01010101, p1);
+            neg = __dp4a((int)(w2 & f2), 0x01010101, neg);
+            pos = __dp4a((int)(w2 & ~f2), 0x01010101, pos);
+            n1 = __dp4a((int)(w3 & f3), 0x01010101, n1);
+            p1 = __dp4a((int)(w3 & ~f3), 0x01010101, p1);
+        }
+        neg += n1;
+        pos += p1;
+        return;
+    }
     for (int j = 0; j < nw; ++j) {
         uint32_t w = v[j];
         if (n < 4) w &= bytemask(n);
@@ -216,6 +264,22 @@ __device__ __forceinline__ uint32_t scl_signs_and_abs(const Lane& c, const SclPa
     const int n = 1 << s, nw = stage_words(s), dst = side ? p.bitR_off[s] : p.bitL_off[s];
     const Lane::View v = c.view(p.llr_off[s], (uint32_t)c.l);
     uint32_t par = 0, acc = 0;
+    if (nw >= 8) { // eight words (one decision word) per step, loads first
+        for (int j = 0; j < nw; j += 8) {
+            uint32_t w[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) w[u] = v[j + u];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                par ^= w[u];
+                acc |= sw_movemask(w[u]) << (4 * u);
+                v.set(j + u, sw_abs_sat(w[u]));
+            }
+            c.st(dst + (j >> 3), acc);
+            acc = 0;
+        }
+        return par;
+    }
     for (int j = 0; j < nw; ++j) {
         uint32_t w = v[j];
         if (n < 4) w &= bytemask(n);
@@ -436,7 +500,17 @@ cudaError_t launch_scl_i8(const SclLaunch& L, const int8_t* d_llr, uint8_t* d_in
     p.frame_idx = d_frame_idx;
     p.count = d_count;
     cudaError_t e = cudaFuncSetAttribute(k_scl_i8, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes);
+    // several CTAs per SM only fit when the L1/shared split is at its shared-memory maximum; a single CTA keeps the
+    // default split (the rest stays L1 for the channel rows and the arena)
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(k_scl_i8, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                 L.per_sm > 1 ? (int)cudaSharedmemCarveoutMaxShared : (int)cudaSharedmemCarveoutDefault);
     if (e != cudaSuccess) return e;
+    if (getenv("PC_DEBUG_OCC")) {
+        int occ = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_scl_i8, L.threads, L.smem_bytes);
+        fprintf(stderr, "k_scl_i8: %d threads, %zu B smem, grid %d, occupancy %d CTAs/SM\n", L.threads, L.smem_bytes, L.grid, occ);
+    }
     const int gpc = L.threads / p.G;
     size_t nb = (B + gpc - 1) / gpc;
     const int grid = (int)(nb < (size_t)L.grid ? nb : (size_t)L.grid);
@@ -529,6 +603,7 @@ int plan_scl_i8(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, S
     out.threads = T;
     out.smem_bytes = 1024 + 4 * (size_t)w * T;
     out.grid = sms * per_sm;
+    out.per_sm = per_sm;
     p.arena_stride = (size_t)out.grid * T;
     if ((unsigned long long)aw * p.arena_stride >= (1ull << 32)) {
         *msg = "SCL arena too large for 32-bit word indexing";
