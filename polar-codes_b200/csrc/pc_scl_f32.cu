@@ -63,6 +63,41 @@ struct FLane {
 // _mm256_max_ps lane: returns the second operand unless a > b
 __device__ __forceinline__ float fmax_ps(float a, float b) { return a > b ? a : b; }
 
+template <bool IS_G, int UNR>
+__device__ __forceinline__ void fg_block(const FLane& c, const float* row, const FLane::View& src, const FLane::View& dst, bool from_row,
+                                         int h, int lb, uint32_t ol)
+{
+    const bool row16 = from_row && ((reinterpret_cast<uintptr_t>(row) & 15u) == 0);
+    uint32_t bw = 0;
+    for (int j = 0; j < h; j += UNR) {
+        float a[UNR], b[UNR], r[UNR];
+        if (row16) {
+#pragma unroll
+            for (int u = 0; u < UNR; u += 4) {
+                const float4 va = __ldg(reinterpret_cast<const float4*>(row + j + u)), vb = __ldg(reinterpret_cast<const float4*>(row + h + j + u));
+                a[u] = va.x, a[u + 1] = va.y, a[u + 2] = va.z, a[u + 3] = va.w;
+                b[u] = vb.x, b[u + 1] = vb.y, b[u + 2] = vb.z, b[u + 3] = vb.w;
+            }
+        } else {
+#pragma unroll
+            for (int u = 0; u < UNR; ++u) {
+                a[u] = from_row ? __ldg(row + j + u) : src[j + u];
+                b[u] = from_row ? __ldg(row + h + j + u) : src[h + j + u];
+            }
+        }
+        if (IS_G) {
+            if ((j & 31) == 0) bw = c.ld(lb + (j >> 5), ol);
+#pragma unroll
+            for (int u = 0; u < UNR; ++u) r[u] = g_f32(a[u], b[u], (bw >> ((j & 31) + u)) & 1u);
+        } else {
+#pragma unroll
+            for (int u = 0; u < UNR; ++u) r[u] = f_f32(a[u], b[u]);
+        }
+#pragma unroll
+        for (int u = 0; u < UNR; ++u) dst.set(j + u, r[u]);
+    }
+}
+
 // f / g step of a node of size 2^s (RateRNode::decode scl_avx_float.cpp:238-262)
 template <bool IS_G>
 __device__ __forceinline__ void sclf_fg(FLane& c, const SclFParams& p, int s, const float* row)
@@ -77,33 +112,13 @@ __device__ __forceinline__ void sclf_fg(FLane& c, const SclFParams& p, int s, co
     if (active) {
         uint32_t bw = 0;
         if (h >= 4) {
-            // four elements per step, all loads first (source and destination may alias as far as the compiler knows,
-            // so a rolled loop serialises load -> f/g -> store); the channel row as 16-byte loads
-            const bool row16 = from_row && ((reinterpret_cast<uintptr_t>(row) & 15u) == 0);
-            for (int j = 0; j < h; j += 4) {
-                float a[4], b[4], r[4];
-                if (row16) {
-                    const float4 va = __ldg(reinterpret_cast<const float4*>(row + j)), vb = __ldg(reinterpret_cast<const float4*>(row + h + j));
-                    a[0] = va.x, a[1] = va.y, a[2] = va.z, a[3] = va.w;
-                    b[0] = vb.x, b[1] = vb.y, b[2] = vb.z, b[3] = vb.w;
-                } else {
-#pragma unroll
-                    for (int u = 0; u < 4; ++u) {
-                        a[u] = from_row ? __ldg(row + j + u) : src[j + u];
-                        b[u] = from_row ? __ldg(row + h + j + u) : src[h + j + u];
-                    }
-                }
-                if (IS_G) {
-                    if ((j & 31) == 0) bw = c.ld(lb + (j >> 5), ol);
-#pragma unroll
-                    for (int u = 0; u < 4; ++u) r[u] = g_f32(a[u], b[u], (bw >> ((j & 31) + u)) & 1u);
-                } else {
-#pragma unroll
-                    for (int u = 0; u < 4; ++u) r[u] = f_f32(a[u], b[u]);
-                }
-#pragma unroll
-                for (int u = 0; u < 4; ++u) dst.set(j + u, r[u]);
-            }
+            // UNR elements per step, all loads first (source and destination may alias as far as the compiler knows, so
+            // a rolled loop serialises load -> f/g -> store; the big stages live in the L2 arena and want many loads in
+            // flight); the channel row as 16-byte loads
+            if (h >= 8)
+                fg_block<IS_G, 8>(c, row, src, dst, from_row, h, lb, ol);
+            else
+                fg_block<IS_G, 4>(c, row, src, dst, from_row, h, lb, ol);
         } else
         for (int j = 0; j < h; ++j) {
             const float a = from_row ? __ldg(row + j) : src[j];
@@ -175,6 +190,7 @@ __device__ __forceinline__ void sclf_find_weak(const FLane& c, int s, int off, i
         const float vi = v[i];
         float bv = vi;
         int bp = i;
+#pragma unroll 4
         for (int j = i + 1; j < n; ++j) {
             const float x = v[j];
             if (x < bv) {
@@ -202,6 +218,23 @@ __device__ __forceinline__ uint32_t sclf_signs_and_abs(const FLane& c, const Scl
     const int n = 1 << s, dst = side ? p.bitR_off[s] : p.bitL_off[s];
     const FLane::View v = c.view(s, p.llr_off[s], (uint32_t)c.l);
     uint32_t par = 0, acc = 0;
+    if (n >= 4) { // four loads in flight, then the in-place stores
+        for (int j = 0; j < n; j += 4) {
+            const float x0 = v[j], x1 = v[j + 1], x2 = v[j + 2], x3 = v[j + 3];
+            const uint32_t s4 = fsign(x0) | (fsign(x1) << 1) | (fsign(x2) << 2) | (fsign(x3) << 3);
+            acc |= s4 << (j & 31);
+            v.set(j, fabs_(x0));
+            v.set(j + 1, fabs_(x1));
+            v.set(j + 2, fabs_(x2));
+            v.set(j + 3, fabs_(x3));
+            if ((j & 31) == 28 || j == n - 4) {
+                par ^= acc;
+                c.st(dst + (j >> 5), acc);
+                acc = 0;
+            }
+        }
+        return __popc(par) & 1u;
+    }
     for (int j = 0; j < n; ++j) {
         const float x = v[j];
         const uint32_t sg = fsign(x);
