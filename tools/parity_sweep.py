@@ -5,7 +5,9 @@ makes the frames, the GPU decodes them, the SAME LLRs are copied back and replay
   int8 kinds: 0 mismatching frames allowed.  float kinds: >= 99.99 % identical frames.
   BLER of the GPU decode must lie inside the 95 % Clopper-Pearson interval of the reference's BLER (trivially true when
   all frames agree; reported anyway).
-usage: tools/parity_sweep.py [--frames F] [--out profiles/x.json] case ...   with case = N:K:L:kind:crcbits"""
+usage: tools/parity_sweep.py [--frames F] [--out profiles/x.json] case ...   with case = N:K:L:kind:crcbits
+kind: char | float | mixed (Decoding::create strings) | achar | amixed (AdaptiveChar / AdaptiveMixed, pcsim's wrappers:
+float LLRs scaled by 10 as pcsim feeds them)"""
 import argparse, ctypes, json, os, sys, time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -33,16 +35,19 @@ threads = os.cpu_count() or 1
 report = []
 for case in a.cases:
     N, K, L, kind, crc = case.split(":"); N, K, L, crc = int(N), int(K), int(L), int(crc)
-    isf = "char" not in kind
+    pcsim_kind = kind in ("achar", "amixed")
+    isf = "char" not in kind or pcsim_kind
+    gpu_kind = {"achar": pcb.capi.PC_DEC_ADAPTIVE_I8, "amixed": pcb.capi.PC_DEC_ADAPTIVE_MIXED}.get(kind, kind)
+    ref_kind = {"achar": "adaptive_char", "amixed": "adaptive_mixed"}.get(kind, kind)
     F = a.frames if L == 1 else max(1 << 17, a.frames // 8)
     fz = pcb.frozen_bits(N, K, 0.0)
-    dec = pcb.PolarDecoder(N, L, fz, kind); dec.setErrorDetection(crc, "crc")
+    dec = pcb.PolarDecoder(N, L, fz, gpu_kind); dec.setErrorDetection(crc, "crc")
     kb = (K + 7) // 8
     chunk = min(F, 1 << 18)
     llr = torch.empty((chunk, N), dtype=torch.float32 if isf else torch.int8, device="cuda")
     info = torch.empty((chunk, kb), dtype=torch.uint8, device="cuda")
     for p, eb in enumerate(points):
-        amp = 4.0 * 10 ** (eb / 10) if isf else 10.0
+        amp = 4.0 * 10 ** (eb / 10) if (isf and not pcsim_kind) else 10.0
         mism = okm = fe_gpu = fe_ref = drift = 0; t_ref = 0.0
         for lo in range(0, F, chunk):
             n = min(chunk, F - lo)
@@ -54,11 +59,11 @@ for case in a.cases:
             # float list decoders: the reference object keeps its best path metric across decode() calls (no reset in
             # PathList::setFirstPath), so its float rounding depends on the frames it decoded before; the comparison is
             # against a fresh object per frame, and the disagreement of the long-lived object with ITSELF is reported
-            fresh = isf and L > 1
-            exp, eok = refshim.decode_batch(N, L, np.array(fz, np.uint32), kind, h_llr, crc_bits=crc, crc_type="crc", threads=threads, fresh=fresh)
+            fresh = isf and L > 1 and kind != "achar"
+            exp, eok = refshim.decode_batch(N, L, np.array(fz, np.uint32), ref_kind, h_llr, crc_bits=crc, crc_type="crc", threads=threads, fresh=fresh)
             t_ref += time.time() - t0
             if fresh:
-                old, _ = refshim.decode_batch(N, L, np.array(fz, np.uint32), kind, h_llr, crc_bits=crc, crc_type="crc", threads=threads)
+                old, _ = refshim.decode_batch(N, L, np.array(fz, np.uint32), ref_kind, h_llr, crc_bits=crc, crc_type="crc", threads=threads)
                 drift += int((old != exp).any(axis=1).sum())
             bad = (h_out != exp).any(axis=1)
             mism += int(bad.sum()); okm += int((h_ok != eok).sum())
@@ -67,9 +72,9 @@ for case in a.cases:
         row = {"case": case, "ebn0_db": eb, "frames": F, "mismatching_frames": mism, "mismatching_verdicts": okm,
                "agreement": 1 - mism / F, "bler_gpu": fe_gpu / F, "bler_ref": fe_ref / F, "ref_ci95": [lo_ci, hi_ci],
                "bler_inside_ci": lo_ci <= fe_gpu / F <= hi_ci, "ref_seconds": round(t_ref, 2), "ref_threads": threads,
-               "reference_fresh_object_per_frame": bool(isf and L > 1), "reference_long_lived_object_vs_fresh_mismatches": drift}
+               "reference_fresh_object_per_frame": bool(fresh), "reference_long_lived_object_vs_fresh_mismatches": drift}
         report.append(row); print(json.dumps(row), flush=True)
-bad = [r for r in report if (("char" in r["case"]) and (r["mismatching_frames"] or r["mismatching_verdicts"])) or r["agreement"] < 0.9999 or not r["bler_inside_ci"]]
+bad = [r for r in report if ((":char:" in r["case"] or ":achar:" in r["case"]) and (r["mismatching_frames"] or r["mismatching_verdicts"])) or r["agreement"] < 0.9999 or not r["bler_inside_ci"]]
 print("PARITY SWEEP:", "PASS" if not bad else f"FAIL ({len(bad)} rows)")
 if a.out:
     json.dump({"rows": report, "pass": not bad}, open(a.out, "w"), indent=1)
