@@ -208,7 +208,8 @@ def main():
         tx = torch.empty((frames, kb), dtype=torch.uint8, device=dev)
         o = torch.empty((frames, kb), dtype=torch.uint8, device=dev)
         v = torch.empty((frames,), dtype=torch.uint8, device=dev)
-        amp = 4.0 * 10.0 ** (EBN0_DB / 10.0) if is_float else AMP
+        # pcsim scaling: 4 * Eb/N0 for the float decoders, the fixed amplification for int8 and for AdaptiveMixed (-p 832)
+        amp = 4.0 * 10.0 ** (EBN0_DB / 10.0) if (is_float and kind != capi.PC_DEC_ADAPTIVE_MIXED) else AMP
         capi.check(capi.lib().pc_awgn_generate(d._h, ctypes.c_uint64(0x5EED), ctypes.c_uint64(rank * frames),
                                                ctypes.c_float(EBN0_DB), ctypes.c_float(amp), int(is_float), capi.ptr(x),
                                                capi.ptr(tx), frames, None))
@@ -236,6 +237,9 @@ def main():
             "scl_l8_int8_crc16": timed_kind("char", 8, 16, 1 << 16, False, 5),
             "scl_l8_fp32_crc16": timed_kind("float", 8, 16, 1 << 15, True, 5),
             "adaptive_l8_fp32_crc16": timed_kind("mixed", 8, 16, 1 << 17, True, 5),
+            # pcsim's L > 1 decoders at precision 8 / 832 (simulator.cpp:721-733): Fast-SSC int8, failures to the list kernel
+            "adaptive_l8_int8_crc16": timed_kind(capi.PC_DEC_ADAPTIVE_I8, 8, 16, 1 << 18, False, 5),
+            "adaptive_l8_int8_fp32_crc16": timed_kind(capi.PC_DEC_ADAPTIVE_MIXED, 8, 16, 1 << 17, True, 5),
             "fastssc_fp32_crc8": timed_kind("float", 1, 8, 1 << 17, True, 5),
         }
 

@@ -6,6 +6,9 @@ $P 1024 512 1 float 8 262144 2.0
 $P 1024 512 8 char 16 65536 2.0
 $P 1024 512 8 float 16 32768 2.0
 $P 1024 512 8 mixed 16 262144 2.0
+$P 1024 512 8 achar 16 262144 2.0
+$P 1024 512 8 amixed 16 262144 2.0
+$P 1024 512 8 achar 16 1048576 3.0
 $P 64 40 4 mixed 8 1048576 2.0
 $P 64 40 4 float 8 262144 2.0
 $P 512 128 8 float 24 65536 2.0

@@ -1,5 +1,6 @@
 #!/usr/bin/env python
-"""times one decoder configuration on the GPU with device-generated LLRs: tools/perf_decoder.py N K L kind crc frames ebn0"""
+"""times one decoder configuration on the GPU with device-generated LLRs: tools/perf_decoder.py N K L kind crc frames ebn0
+kind: char | float | mixed | achar | amixed"""
 import ctypes, sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
@@ -7,13 +8,15 @@ import polar_b200_loader
 pcb = polar_b200_loader.load()
 N, K, L, kind, crc, B, ebn0 = int(sys.argv[1]), int(sys.argv[2]), int(sys.argv[3]), sys.argv[4], int(sys.argv[5]), int(sys.argv[6]), float(sys.argv[7])
 fz = pcb.frozen_bits(N, K, 0.0)
-dec = pcb.PolarDecoder(N, L, fz, kind)
+# achar / amixed: AdaptiveChar / AdaptiveMixed (pcsim -p 8 / -p 832 with L > 1), LLRs scaled by 10 like pcsim
+gpu_kind = {"achar": pcb.capi.PC_DEC_ADAPTIVE_I8, "amixed": pcb.capi.PC_DEC_ADAPTIVE_MIXED}.get(kind, kind)
+dec = pcb.PolarDecoder(N, L, fz, gpu_kind)
 dec.setErrorDetection(crc, "crc")
 isf = "char" not in kind
 llr = torch.empty((B, N), dtype=torch.float32 if isf else torch.int8, device="cuda")
 info = torch.empty((B, (K + 7) // 8), dtype=torch.uint8, device="cuda")
 Lb = pcb.capi.lib(); ptr = pcb.capi.ptr
-amp = 4.0 * 10 ** (ebn0 / 10) if isf else 10.0
+amp = 4.0 * 10 ** (ebn0 / 10) if (isf and kind != "amixed") else 10.0
 pcb.capi.check(Lb.pc_awgn_generate(dec._h, 1, 0, ebn0, amp, int(isf), ptr(llr), ptr(info), B, None))
 out, ok = dec.decode_batch(llr, return_ok=True)
 torch.cuda.synchronize()
