@@ -145,20 +145,56 @@ PC_HD uint32_t spc4_bits(const float (&y)[4])
 // ---- internal nodes --------------------------------------------------------------------------------------------
 // RateRNode / ShortRateRNode / ROneNode / ZeroRNode (fastssc_avx_float.cpp:148-238): element-wise, lane structure
 // does not matter
-PC_HD void fop_f(const FCtx& c, const FView& in, int s)
+// Eight elements per step with all loads before the stores: `in` and the destination stage may alias as far as the
+// compiler can tell, so a rolled loop serialises load -> op -> store (one memory latency per element on the device,
+// where the stages live in a DRAM/L2 arena).
+template <class Op>
+PC_HD void fop_map(const FCtx& c, const FView& in, int s, const Op& op)
 {
     const int h = 1 << (s - 1);
-    for (int i = 0; i < h; ++i) c.st(s - 1, i, f_f32(in[i], in[i + h]));
+    if (h >= 8) {
+        for (int i = 0; i < h; i += 8) {
+            float a[8], b[8];
+#ifdef __CUDA_ARCH__
+#pragma unroll
+#endif
+            for (int k = 0; k < 8; ++k) a[k] = in[i + k], b[k] = in[i + k + h];
+#ifdef __CUDA_ARCH__
+#pragma unroll
+#endif
+            for (int k = 0; k < 8; ++k) c.st(s - 1, i + k, op(a[k], b[k], i + k));
+        }
+    } else {
+        for (int i = 0; i < h; ++i) c.st(s - 1, i, op(in[i], in[i + h], i));
+    }
+}
+PC_HD void fop_f(const FCtx& c, const FView& in, int s)
+{
+    fop_map(c, in, s, [](float a, float b, int) { return f_f32(a, b); });
 }
 PC_HD void fop_g(const FCtx& c, const FView& in, int s, int off)
 {
     const int h = 1 << (s - 1);
-    for (int i = 0; i < h; ++i) c.st(s - 1, i, g_f32(in[i], in[i + h], c.bit(off + i)));
+    if (h >= 8) { // the 8 decisions of a step sit in one word (off is a multiple of h)
+        for (int i = 0; i < h; i += 8) {
+            float a[8], b[8];
+            const uint32_t bw = c.bld((off + i) >> 5) >> ((off + i) & 31);
+#ifdef __CUDA_ARCH__
+#pragma unroll
+#endif
+            for (int k = 0; k < 8; ++k) a[k] = in[i + k], b[k] = in[i + k + h];
+#ifdef __CUDA_ARCH__
+#pragma unroll
+#endif
+            for (int k = 0; k < 8; ++k) c.st(s - 1, i + k, g_f32(a[k], b[k], (bw >> k) & 1u));
+        }
+    } else {
+        for (int i = 0; i < h; ++i) c.st(s - 1, i, g_f32(in[i], in[i + h], c.bit(off + i)));
+    }
 }
 PC_HD void fop_g0(const FCtx& c, const FView& in, int s)
 {
-    const int h = 1 << (s - 1);
-    for (int i = 0; i < h; ++i) c.st(s - 1, i, fadd(in[i], in[i + h]));
+    fop_map(c, in, s, [](float a, float b, int) { return fadd(a, b); });
 }
 // right child rate-1: decisions = sign(g); parent = [left ^ right, right]   (ROneNode::rightDecode :204-219)
 PC_HD void fop_g1(const FCtx& c, const FView& in, int s, int off)
@@ -168,9 +204,16 @@ PC_HD void fop_g1(const FCtx& c, const FView& in, int s, int off)
         for (int w = 0; w < (h >> 5); ++w) {
             const uint32_t left = c.bld((off >> 5) + w);
             uint32_t r = 0;
-            for (int k = 0; k < 32; ++k) {
-                const int i = 32 * w + k;
-                r |= fsign(g_f32(in[i], in[i + h], (left >> k) & 1u)) << k;
+            for (int k0 = 0; k0 < 32; k0 += 8) {
+                float a[8], b[8];
+#ifdef __CUDA_ARCH__
+#pragma unroll
+#endif
+                for (int k = 0; k < 8; ++k) a[k] = in[32 * w + k0 + k], b[k] = in[32 * w + k0 + k + h];
+#ifdef __CUDA_ARCH__
+#pragma unroll
+#endif
+                for (int k = 0; k < 8; ++k) r |= fsign(g_f32(a[k], b[k], (left >> (k0 + k)) & 1u)) << (k0 + k);
             }
             c.bst((off >> 5) + w, left ^ r);
             c.bst(((off + h) >> 5) + w, r);
