@@ -128,6 +128,23 @@ int pc_awgn_generate(pc_code* c, uint64_t seed, uint64_t first_frame, float ebn0
 int pc_count_errors(const uint8_t* d_info_ref, const uint8_t* d_info_dec, const uint8_t* d_ok, int K, size_t B,
                     unsigned long long* d_counts, void* stream);
 
+/* Puncturer for block lengths that are not a power of two (PolarCode::Puncturer, include/polarcode/puncturer.h:37-101,
+ * src/polarcode/puncturer.cpp:52-89; pybind python/bindings/puncturer_python.cc). The parent length is the next power
+ * of two; the first (parent - block_length) entries of `frozen` are punctured. NULL + pc_last_error() when there are
+ * not enough frozen positions (std::out_of_range in the reference). */
+typedef struct pc_puncturer pc_puncturer;
+pc_puncturer* pc_puncturer_create(size_t block_length, const unsigned* frozen, int n_frozen);
+void pc_puncturer_destroy(pc_puncturer* p);
+size_t pc_puncturer_block_length(const pc_puncturer* p);        /* Puncturer::blockLength()       */
+size_t pc_puncturer_parent_block_length(const pc_puncturer* p); /* Puncturer::parentBlockLength() */
+int pc_puncturer_positions(const pc_puncturer* p, unsigned* out); /* blockOutputPositions(); returns the count */
+/* puncture<T>: d_out[B][M] = gather of d_in[B][Np]; depuncture<T>: d_out[B][Np] = scatter of d_in[B][M], punctured
+ * positions 0. elem_bytes 1 (bits as bytes, int8 LLRs), 4 (float) or 8 (double); asynchronous on `stream`. */
+int pc_puncture_batch(const pc_puncturer* p, const void* d_in, void* d_out, int elem_bytes, size_t B, void* stream);
+int pc_depuncture_batch(const pc_puncturer* p, const void* d_in, void* d_out, int elem_bytes, size_t B, void* stream);
+/* puncturePacked: MSB-first packed bits, d_in[B][Np/8] -> d_out[B][M/8] (both lengths multiples of 8) */
+int pc_puncture_packed_batch(const pc_puncturer* p, const uint8_t* d_in, uint8_t* d_out, size_t B, void* stream);
+
 /* device memory helpers so that non-CUDA hosts (ctypes, cgo, JNI) can drive the library alone */
 void* pc_device_alloc(size_t bytes);
 void pc_device_free(void* d);

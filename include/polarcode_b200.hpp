@@ -55,6 +55,94 @@ inline std::vector<unsigned> frozen_bits(const int blockLength, const int infoLe
 }
 } // namespace Construction
 
+// puncturer.h:37-101. Per-vector calls copy through the device (host pointers, like the reference); the *_batch
+// members take device pointers and run one launch.
+class Puncturer
+{
+protected:
+    pc_puncturer* mHandle = nullptr;
+    size_t mBlockLength = 0, mParentBlockLength = 0;
+    std::vector<unsigned> mOutputPositions;
+
+    template <typename T>
+    void run(T* pOutput, const T* pInput, size_t nIn, size_t nOut, bool scatter)
+    {
+        static_assert(sizeof(T) == 1 || sizeof(T) == 4 || sizeof(T) == 8, "element size must be 1, 4 or 8 bytes");
+        void* dIn = pc_device_alloc(nIn * sizeof(T));
+        void* dOut = pc_device_alloc(nOut * sizeof(T));
+        if (!dIn || !dOut) {
+            pc_device_free(dIn);
+            pc_device_free(dOut);
+            throw std::runtime_error(pc_last_error());
+        }
+        int st = pc_memcpy_h2d(dIn, pInput, nIn * sizeof(T));
+        if (st == PC_OK)
+            st = scatter ? pc_depuncture_batch(mHandle, dIn, dOut, (int)sizeof(T), 1, nullptr)
+                         : pc_puncture_batch(mHandle, dIn, dOut, (int)sizeof(T), 1, nullptr);
+        if (st == PC_OK) st = pc_memcpy_d2h(pOutput, dOut, nOut * sizeof(T));
+        pc_device_free(dIn);
+        pc_device_free(dOut);
+        detail::check(st);
+    }
+
+public:
+    Puncturer(const size_t blockLength, const std::vector<unsigned> frozenBitPositions)
+    {
+        mHandle = pc_puncturer_create(blockLength, frozenBitPositions.data(), (int)frozenBitPositions.size());
+        if (!mHandle) {
+            const std::string msg = pc_last_error();
+            if (msg.find("exceeds frozen") != std::string::npos) throw std::out_of_range(msg); // puncturer.cpp:57-60
+            throw std::runtime_error(msg);
+        }
+        mBlockLength = pc_puncturer_block_length(mHandle);
+        mParentBlockLength = pc_puncturer_parent_block_length(mHandle);
+        mOutputPositions.resize(mBlockLength);
+        pc_puncturer_positions(mHandle, mOutputPositions.data());
+    }
+    Puncturer(const Puncturer&) = delete;
+    Puncturer& operator=(const Puncturer&) = delete;
+    virtual ~Puncturer() { pc_puncturer_destroy(mHandle); }
+
+    size_t blockLength() { return mBlockLength; }
+    size_t parentBlockLength() { return mParentBlockLength; }
+    std::vector<unsigned> blockOutputPositions() { return mOutputPositions; }
+
+    template <typename T>
+    void puncture(T* pOutput, const T* pInput)
+    {
+        run(pOutput, pInput, mParentBlockLength, mBlockLength, false);
+    }
+    template <typename T>
+    void depuncture(T* pOutput, const T* pInput)
+    {
+        run(pOutput, pInput, mBlockLength, mParentBlockLength, true);
+    }
+    void puncturePacked(unsigned char* pOutput, const unsigned char* pInput)
+    {
+        void* dIn = pc_device_alloc(mParentBlockLength / 8);
+        void* dOut = pc_device_alloc(mBlockLength / 8);
+        int st = (dIn && dOut) ? pc_memcpy_h2d(dIn, pInput, mParentBlockLength / 8) : PC_ERR_CUDA;
+        if (st == PC_OK) st = pc_puncture_packed_batch(mHandle, (const uint8_t*)dIn, (uint8_t*)dOut, 1, nullptr);
+        if (st == PC_OK) st = pc_memcpy_d2h(pOutput, dOut, mBlockLength / 8);
+        pc_device_free(dIn);
+        pc_device_free(dOut);
+        detail::check(st);
+    }
+    // batch extensions: device pointers, asynchronous on `stream`
+    void puncture_batch(void* dOut, const void* dIn, int elemBytes, size_t B, void* stream = nullptr)
+    {
+        detail::check(pc_puncture_batch(mHandle, dIn, dOut, elemBytes, B, stream));
+    }
+    void depuncture_batch(void* dOut, const void* dIn, int elemBytes, size_t B, void* stream = nullptr)
+    {
+        detail::check(pc_depuncture_batch(mHandle, dIn, dOut, elemBytes, B, stream));
+    }
+    void puncturePacked_batch(uint8_t* dOut, const uint8_t* dIn, size_t B, void* stream = nullptr)
+    {
+        detail::check(pc_puncture_packed_batch(mHandle, dIn, dOut, B, stream));
+    }
+};
+
 namespace ErrorDetection {
 
 // errordetector.h:24-78. One concrete class covers the CRC family and the dummy. The single-block methods are

@@ -16,9 +16,11 @@
 #include <polarcode/decoding/decoder.h>
 #include <polarcode/encoding/butterfly_fip_packed.h>
 #include <polarcode/errordetection/errordetector.h>
+#include <polarcode/puncturer.h>
 
 #include <chrono>
 #include <cstring>
+#include <stdexcept>
 #include <string>
 #include <thread>
 #include <vector>
@@ -202,6 +204,39 @@ int ref_quantize(int N, const float* in, long B, signed char* out)
             memcpy(out + i * N, c.data(), N);
         }
         return 0;
+    } catch (...) {
+        return -1;
+    }
+}
+
+// PolarCode::Puncturer (src/polarcode/puncturer.cpp, include/polarcode/puncturer.h) over a batch.
+// mode 0: blockOutputPositions -> out (unsigned[M]); 1: puncturePacked; 2/3/4: puncture<uint8_t/float/double>;
+// 5/6/7: depuncture<uint8_t/float/double>. Returns parentBlockLength, -2 for std::out_of_range, -1 otherwise.
+long ref_puncturer(long blockLength, const unsigned* frozen, int nf, int mode, const void* in, long B, void* out)
+{
+    try {
+        Puncturer p(blockLength, mkfrozen(frozen, nf));
+        const long M = p.blockLength(), Np = p.parentBlockLength();
+        if (mode == 0) {
+            auto pos = p.blockOutputPositions();
+            memcpy(out, pos.data(), sizeof(unsigned) * pos.size());
+            return Np;
+        }
+        for (long b = 0; b < B; ++b) {
+            switch (mode) {
+            case 1: p.puncturePacked((unsigned char*)out + b * (M / 8), (const unsigned char*)in + b * (Np / 8)); break;
+            case 2: p.puncture<unsigned char>((unsigned char*)out + b * M, (const unsigned char*)in + b * Np); break;
+            case 3: p.puncture<float>((float*)out + b * M, (const float*)in + b * Np); break;
+            case 4: p.puncture<double>((double*)out + b * M, (const double*)in + b * Np); break;
+            case 5: p.depuncture<unsigned char>((unsigned char*)out + b * Np, (const unsigned char*)in + b * M); break;
+            case 6: p.depuncture<float>((float*)out + b * Np, (const float*)in + b * M); break;
+            case 7: p.depuncture<double>((double*)out + b * Np, (const double*)in + b * M); break;
+            default: return -1;
+            }
+        }
+        return Np;
+    } catch (const std::out_of_range&) {
+        return -2;
     } catch (...) {
         return -1;
     }

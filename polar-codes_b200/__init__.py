@@ -5,4 +5,4 @@ The directory name carries a hyphen (it follows the reference's repository name)
 `polar_b200_loader.load()` at the repository root, or add it to sys.modules under `polar_codes_b200`.
 """
 from . import capi, pcsim, pypolar, sweep  # noqa: F401
-from .pypolar import Detector, PolarDecoder, PolarEncoder, frozen_bits  # noqa: F401
+from .pypolar import Detector, PolarDecoder, PolarEncoder, Puncturer, frozen_bits  # noqa: F401

@@ -19,6 +19,14 @@ _vp, _i, _sz, _u64 = ctypes.c_void_p, ctypes.c_int, ctypes.c_size_t, ctypes.c_ui
 
 # name -> (restype, argtypes); mirrors include/polar_b200.h one to one (tests check the export list)
 SIGNATURES = {
+    "pc_puncturer_create": (_vp, [ctypes.c_size_t, _vp, _i]),
+    "pc_puncturer_destroy": (None, [_vp]),
+    "pc_puncturer_block_length": (ctypes.c_size_t, [_vp]),
+    "pc_puncturer_parent_block_length": (ctypes.c_size_t, [_vp]),
+    "pc_puncturer_positions": (_i, [_vp, _vp]),
+    "pc_puncture_batch": (_i, [_vp, _vp, _vp, _i, ctypes.c_size_t, _vp]),
+    "pc_depuncture_batch": (_i, [_vp, _vp, _vp, _i, ctypes.c_size_t, _vp]),
+    "pc_puncture_packed_batch": (_i, [_vp, _vp, _vp, ctypes.c_size_t, _vp]),
     "pc_last_error": (ctypes.c_char_p, []),
     "pc_version": (ctypes.c_char_p, []),
     "pc_frozen_bits": (_i, [_i, _i, ctypes.c_float, ctypes.c_char_p, _vp]),

@@ -286,3 +286,100 @@ def _run_rows(fn, rows, writeback=False):
             check(lib().pc_memcpy_d2h(ptr(rows), ctypes.c_void_p(d), nbytes))
     finally:
         lib().pc_device_free(ctypes.c_void_p(d))
+
+
+class Puncturer:
+    """pypolar.Puncturer (reference python/bindings/puncturer_python.cc:19-150 over src/polarcode/puncturer.cpp):
+    same methods, argument checks and dtypes (uint8 / float32 / float64) for one vector; `*_batch` take [B, n] numpy
+    arrays or torch CUDA tensors and run one gather / scatter launch."""
+    _DTYPES = {np.dtype(np.uint8): 1, np.dtype(np.int8): 1, np.dtype(np.float32): 4, np.dtype(np.float64): 8}
+
+    def __init__(self, blockLength, frozenBitPositions):
+        f = np.ascontiguousarray(np.asarray(frozenBitPositions, dtype=np.uint32))
+        self._h = lib().pc_puncturer_create(int(blockLength), ptr(f), int(f.size))
+        if not self._h:
+            msg = capi.last_error()
+            if "exceeds frozen" in msg:
+                raise IndexError(msg)                      # std::out_of_range -> IndexError through pybind11
+            raise RuntimeError(msg)
+        self._h = ctypes.c_void_p(self._h)
+        self._M = int(lib().pc_puncturer_block_length(self._h))
+        self._Np = int(lib().pc_puncturer_parent_block_length(self._h))
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            try:
+                lib().pc_puncturer_destroy(h)
+            except Exception:
+                pass
+
+    def blockLength(self):
+        return self._M
+
+    def parentBlockLength(self):
+        return self._Np
+
+    def blockOutputPositions(self):
+        out = np.zeros(self._M, dtype=np.uint32)
+        lib().pc_puncturer_positions(self._h, ptr(out))
+        return [int(v) for v in out]
+
+    # ---- batch entry points ------------------------------------------------------------------------------------
+    def _run(self, fn, x, n_in, n_out, elem=None):
+        import torch
+        is_t = hasattr(x, "is_cuda")
+        if is_t and x.is_cuda:
+            if x.dim() != 2 or x.shape[1] != n_in:
+                raise RuntimeError("Input must be [B, %d]" % n_in)
+            x = x.contiguous()
+            out = torch.empty((x.shape[0], n_out), dtype=x.dtype, device=x.device)
+            st = ctypes.c_void_p(torch.cuda.current_stream(x.device).cuda_stream)
+            e = x.element_size() if elem is None else elem
+            check(fn(ptr(x), ptr(out), e, x.shape[0], st))
+            return out
+        a = np.ascontiguousarray(x.numpy() if is_t else x)
+        if a.ndim != 2 or a.shape[1] != n_in:
+            raise RuntimeError("Input must be [B, %d]" % n_in)
+        if a.dtype not in self._DTYPES:
+            raise TypeError("unsupported dtype %s" % a.dtype)
+        d = torch.from_numpy(a).cuda()
+        return self._run(fn, d, n_in, n_out, elem).cpu().numpy()
+
+    def puncture_batch(self, x):
+        return self._run(lambda i, o, e, B, st: lib().pc_puncture_batch(self._h, i, o, e, B, st), x, self._Np, self._M)
+
+    def depuncture_batch(self, x):
+        return self._run(lambda i, o, e, B, st: lib().pc_depuncture_batch(self._h, i, o, e, B, st), x, self._M, self._Np)
+
+    def puncturePacked_batch(self, x):
+        return self._run(lambda i, o, e, B, st: lib().pc_puncture_packed_batch(self._h, i, o, B, st), x, self._Np // 8,
+                         self._M // 8, elem=1)
+
+    # ---- the reference's per-vector calls ---------------------------------------------------------------------------
+    @staticmethod
+    def _vector(array, size, what):
+        a = np.asarray(array)
+        if a.dtype not in (np.uint8, np.float32, np.float64):
+            a = a.astype(np.float64)                       # pybind11 overload order: double first, forcecast
+        if a.ndim != 1:
+            raise RuntimeError("Only ONE-dimensional vectors allowed!")
+        if a.size != size:
+            raise RuntimeError(what)
+        return a
+
+    def puncture(self, array):
+        a = self._vector(array, self._Np, "Input vector size != parentBlockSize!")
+        return self.puncture_batch(a.reshape(1, -1))[0]
+
+    def depuncture(self, array):
+        a = self._vector(array, self._M, "Input vector size != blockSize!")
+        return self.depuncture_batch(a.reshape(1, -1))[0]
+
+    def puncturePacked(self, array):
+        a = np.asarray(array, dtype=np.uint8)
+        if a.ndim != 1:
+            raise RuntimeError("Only ONE-dimensional vectors allowed!")
+        if a.size != self._Np // 8:
+            raise RuntimeError("Input vector size != parentBlockSize!")
+        return self.puncturePacked_batch(a.reshape(1, -1))[0]

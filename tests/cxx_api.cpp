@@ -109,4 +109,26 @@ int cxx_decode(int N, int L, const unsigned* frozen, int nf, const char* kind, i
         *list_size = (int)dec->getListSize();
     });
 }
+// Puncturer (puncturer.h:37-101): positions, then puncture<float>, puncturePacked, depuncture<float> of one vector
+// each; status 5 = std::out_of_range (checked before logic_error, its base class)
+int cxx_puncturer(long blockLength, const unsigned* frozen, int nf, unsigned* positions, long* parent, const float* in,
+                  float* punctured, const unsigned char* packed_in, unsigned char* packed_out, float* depunctured)
+{
+    try {
+        Puncturer p(blockLength, std::vector<unsigned>(frozen, frozen + nf));
+        *parent = (long)p.parentBlockLength();
+        auto pos = p.blockOutputPositions();
+        std::memcpy(positions, pos.data(), 4 * pos.size());
+        p.puncture<float>(punctured, in);
+        p.puncturePacked(packed_out, packed_in);
+        p.depuncture<float>(depunctured, punctured);
+        return (long)p.blockLength() == blockLength ? 0 : 4;
+    } catch (const std::out_of_range&) {
+        return 5;
+    } catch (const std::runtime_error&) {
+        return 3;
+    } catch (...) {
+        return 4;
+    }
+}
 }

@@ -41,6 +41,9 @@ def lib():
                                     ctypes.c_long, ctypes.c_long, ctypes.c_void_p, ctypes.c_void_p]
         L.ref_quantize.restype = ctypes.c_int
         L.ref_quantize.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_long, ctypes.c_void_p]
+        L.ref_puncturer.restype = ctypes.c_long
+        L.ref_puncturer.argtypes = [ctypes.c_long, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_long,
+                                    ctypes.c_void_p]
         _LIB = L
     return _LIB
 
@@ -123,4 +126,32 @@ def quantize(N, llr_f32):
     out = np.zeros((B, N), dtype=np.int8)
     if lib().ref_quantize(N, _p(x), B, _p(out)) < 0:
         raise RuntimeError("reference quantize failed")
+    return out
+
+
+def puncturer(blockLength, frozen, mode, data=None):
+    """PolarCode::Puncturer over a batch; mode: 'positions' | 'packed' | 'puncture' | 'depuncture' (dtype of `data`
+    picks the template instance). Raises IndexError where the reference throws std::out_of_range."""
+    frozen = np.ascontiguousarray(frozen, dtype=np.uint32)
+    Np = 1
+    while Np < blockLength:
+        Np *= 2
+    if mode == "positions":
+        out = np.zeros(blockLength, dtype=np.uint32)
+        r = lib().ref_puncturer(blockLength, _p(frozen), len(frozen), 0, None, 0, _p(out))
+    else:
+        data = np.ascontiguousarray(data)
+        B = data.shape[0]
+        t = {np.dtype(np.uint8): 0, np.dtype(np.float32): 1, np.dtype(np.float64): 2}[data.dtype]
+        if mode == "packed":
+            out, m = np.zeros((B, blockLength // 8), np.uint8), 1
+        elif mode == "puncture":
+            out, m = np.zeros((B, blockLength), data.dtype), 2 + t
+        else:
+            out, m = np.zeros((B, Np), data.dtype), 5 + t
+        r = lib().ref_puncturer(blockLength, _p(frozen), len(frozen), m, _p(data), B, _p(out))
+    if r == -2:
+        raise IndexError("Number of required puncturing positions exceeds frozen bit positions!")
+    if r < 0:
+        raise RuntimeError("reference puncturer failed")
     return out

@@ -121,3 +121,22 @@ def test_cxx_decoder_matches_reference(cxx, ref, N, K, L, kind, crc, typ):
     # decoder.cpp:45: std::logic_error("Unknown PolarDecoder type!")
     assert cxx.cxx_decode(N, L, _p(fz), len(fz), b"bogus", crc, typ.encode(), 1, 0, _p(llr8), ctypes.c_long(1), _p(out),
                           _p(ok), 0, mode, ctypes.byref(ls)) == 2
+
+
+@pytest.mark.gpu
+def test_cxx_puncturer_matches_reference(cxx, ref):
+    N, M = 256, 200
+    rng = np.random.default_rng(1)
+    f = np.ascontiguousarray(ref.frozen_bits(N, 128, 0.0), np.uint32)
+    pos = np.zeros(M, np.uint32)
+    parent = ctypes.c_long(0)
+    x = rng.standard_normal(N).astype(np.float32)
+    bits = rng.integers(0, 256, N // 8, dtype=np.uint8)
+    punct, packed, dep = np.zeros(M, np.float32), np.zeros(M // 8, np.uint8), np.zeros(N, np.float32)
+    cxx.cxx_puncturer.argtypes = [ctypes.c_long, VP, ctypes.c_int, VP, ctypes.POINTER(ctypes.c_long), VP, VP, VP, VP, VP]
+    assert cxx.cxx_puncturer(M, _p(f), len(f), _p(pos), ctypes.byref(parent), _p(x), _p(punct), _p(bits), _p(packed), _p(dep)) == 0
+    assert parent.value == N and pos.tolist() == ref.puncturer(M, f, "positions").tolist()
+    assert np.array_equal(punct, ref.puncturer(M, f, "puncture", x[None])[0])
+    assert np.array_equal(packed, ref.puncturer(M, f, "packed", bits[None])[0])
+    assert np.array_equal(dep, ref.puncturer(M, f, "depuncture", punct[None])[0])
+    assert cxx.cxx_puncturer(100, _p(f), 10, _p(pos), ctypes.byref(parent), _p(x), _p(punct), _p(bits), _p(packed), _p(dep)) == 5
