@@ -16,4 +16,8 @@ if __name__ == "__main__":
         import torch.distributed as dist
         torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
         dist.init_process_group("nccl")
-    sys.exit(pcsim.main())
+    rc = pcsim.main()
+    if "RANK" in os.environ and int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+    sys.exit(rc)
