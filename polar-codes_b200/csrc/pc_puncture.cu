@@ -53,13 +53,30 @@ struct alignas(sizeof(T) * V) Pack {
 };
 template <class T, int V>
 __global__ void __launch_bounds__(256) k_puncture_v(const T* __restrict__ in, Pack<T, V>* __restrict__ out, const unsigned* __restrict__ pos,
-                                                    unsigned Mv, unsigned Np, unsigned long long total)
+                                                    unsigned Mv, unsigned Np, unsigned long long total, bool row_aligned)
 {
     const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
     for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
         const unsigned long long b = i / Mv;
         const unsigned jv = (unsigned)(i - b * Mv);
         const T* row = in + b * Np;
+        if constexpr (sizeof(T) == 1 && V == 16) {
+            // positions ascend, so first/last 15 apart means 16 consecutive bytes: two index loads instead of sixteen
+            // (the index table is 4x the payload for 1-byte elements), the bytes through aligned words + funnel shifts
+            const unsigned p0 = __ldg(pos + (size_t)jv * V), p15 = __ldg(pos + (size_t)jv * V + 15);
+            if (p15 - p0 == 15u && row_aligned) {
+                const uint32_t* w = reinterpret_cast<const uint32_t*>(row + (p0 & ~3u));
+                const unsigned sh = (p0 & 3u) * 8u;
+                const uint32_t w0 = w[0], w1 = w[1], w2 = w[2], w3 = w[3], w4 = sh ? w[4] : 0u;
+                uint4 o4;
+                o4.x = __funnelshift_r(w0, w1, sh);
+                o4.y = __funnelshift_r(w1, w2, sh);
+                o4.z = __funnelshift_r(w2, w3, sh);
+                o4.w = __funnelshift_r(w3, w4, sh);
+                *reinterpret_cast<uint4*>(out + i) = o4;
+                continue;
+            }
+        }
         const Pack<unsigned, V> p = *reinterpret_cast<const Pack<unsigned, V>*>(pos + (size_t)jv * V);
         Pack<T, V> o;
 #pragma unroll
@@ -69,13 +86,28 @@ __global__ void __launch_bounds__(256) k_puncture_v(const T* __restrict__ in, Pa
 }
 template <class T, int V>
 __global__ void __launch_bounds__(256) k_depuncture_v(const T* __restrict__ in, Pack<T, V>* __restrict__ out, const int* __restrict__ inv,
-                                                      unsigned M, unsigned Npv, unsigned long long total)
+                                                      unsigned M, unsigned Npv, unsigned long long total, bool row_aligned)
 {
     const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
     for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
         const unsigned long long b = i / Npv;
         const unsigned pv = (unsigned)(i - b * Npv);
         const T* row = in + b * M;
+        if constexpr (sizeof(T) == 1 && V == 16) {
+            const int j0 = __ldg(inv + (size_t)pv * V), j15 = __ldg(inv + (size_t)pv * V + 15);
+            if (j0 >= 0 && j15 - j0 == 15 && row_aligned) { // sixteen surviving positions in a row
+                const uint32_t* w = reinterpret_cast<const uint32_t*>(row + ((unsigned)j0 & ~3u));
+                const unsigned sh = ((unsigned)j0 & 3u) * 8u;
+                const uint32_t w0 = w[0], w1 = w[1], w2 = w[2], w3 = w[3], w4 = sh ? w[4] : 0u;
+                uint4 o4;
+                o4.x = __funnelshift_r(w0, w1, sh);
+                o4.y = __funnelshift_r(w1, w2, sh);
+                o4.z = __funnelshift_r(w2, w3, sh);
+                o4.w = __funnelshift_r(w3, w4, sh);
+                *reinterpret_cast<uint4*>(out + i) = o4;
+                continue;
+            }
+        }
         const Pack<int, V> j = *reinterpret_cast<const Pack<int, V>*>(inv + (size_t)pv * V);
         Pack<T, V> o;
 #pragma unroll
@@ -134,13 +166,14 @@ static int run_gather(const pc_puncturer* p, const void* d_in, void* d_out, size
     const bool vec = V > 1 && (p->M % V) == 0 && (p->Np % V) == 0 && (reinterpret_cast<uintptr_t>(d_out) % (sizeof(T) * V)) == 0;
     if (!vec && V > 4) return run_gather<T, 4>(p, d_in, d_out, B, st, scatter);
     if (vec) {
+        const bool in_al = (reinterpret_cast<uintptr_t>(d_in) & 3u) == 0; // rows start 4-byte aligned (both lengths are multiples of V)
         const unsigned long long total = (unsigned long long)B * ((scatter ? p->Np : p->M) / V);
         if (scatter)
             k_depuncture_v<T, V><<<grid_for(total), 256, 0, st>>>(static_cast<const T*>(d_in), static_cast<Pack<T, V>*>(d_out), p->d_inv,
-                                                                  (unsigned)p->M, (unsigned)(p->Np / V), total);
+                                                                  (unsigned)p->M, (unsigned)(p->Np / V), total, in_al);
         else
             k_puncture_v<T, V><<<grid_for(total), 256, 0, st>>>(static_cast<const T*>(d_in), static_cast<Pack<T, V>*>(d_out), p->d_pos,
-                                                                (unsigned)(p->M / V), (unsigned)p->Np, total);
+                                                                (unsigned)(p->M / V), (unsigned)p->Np, total, in_al);
     } else {
         const unsigned long long total = (unsigned long long)B * (scatter ? p->Np : p->M);
         if (scatter)
