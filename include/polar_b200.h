@@ -69,8 +69,10 @@ enum {
 const char* pc_last_error(void);
 const char* pc_version(void);
 
-/* host-only: frozen set for (N, K) by "BB" (Bhattacharyya, design SNR in dB), "BE" (beta expansion) or
- * "5G"; writes N-K sorted indices to out (capacity N), returns N-K or a negative status */
+/* host-only: frozen set for (N, K) by "BB" (Bhattacharyya, design SNR in dB) or "BE" (beta expansion), the
+ * substring match of Construction::frozen_bits (constructor.cpp:41-63); writes N-K sorted indices to out
+ * (capacity N), returns N-K or a negative status. "5G" (FiveGList, the 3GPP reliability table) is recognised and
+ * refused with PC_ERR_UNSUPPORTED: the table is not vendored into this library. */
 int pc_frozen_bits(int N, int K, float design_snr_db, const char* type, unsigned* out);
 
 /* error detector id from the reference's (size, type) pair; negative on the sizes create() rejects */
