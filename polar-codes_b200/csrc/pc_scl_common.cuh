@@ -12,6 +12,10 @@
 
 namespace pc {
 
+// word offsets with this bit set address the lane's rows of the L2/HBM arena instead of shared memory: the largest LLR
+// stages (so that more codewords fit one SM) and, for long codes, the decision words of the largest stages
+constexpr int kArena = 1 << 30;
+
 struct Tbl { // 5-bit owner lane per stage
     uint32_t w[3];
     __device__ __forceinline__ uint32_t get(int s) const

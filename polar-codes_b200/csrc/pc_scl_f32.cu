@@ -20,7 +20,8 @@
 
 namespace pc {
 
-struct FLane {
+template <bool BA> // BA: some decision words live in the arena (long codes); off = no flag tests
+struct FLaneT {
     uint32_t* sm;   // smem base + tid (word w at sm[w * T])
     float* ar;      // arena base + global lane id (element e at ar[e * AS])
     size_t AS;
@@ -29,8 +30,19 @@ struct FLane {
     int smem_top;
     float metric;
     Tbl own_llr, own_L, own_R;
-    __device__ __forceinline__ uint32_t ld(int word, uint32_t owner) const { return sm[(size_t)word * T + ((int)owner - l)]; }
-    __device__ __forceinline__ void st(int word, uint32_t v) const { sm[(size_t)word * T] = v; }
+    // decision words: shared memory, or the arena for the largest stages of long codes (flag in the offset)
+    __device__ __forceinline__ uint32_t ld(int word, uint32_t owner) const
+    {
+        if (BA && (word & kArena)) return reinterpret_cast<const uint32_t*>(ar)[(size_t)(word & (kArena - 1)) * AS + ((int)owner - l)];
+        return sm[(size_t)word * T + ((int)owner - l)];
+    }
+    __device__ __forceinline__ void st(int word, uint32_t v) const
+    {
+        if (BA && (word & kArena))
+            reinterpret_cast<uint32_t*>(ar)[(size_t)(word & (kArena - 1)) * AS] = v;
+        else
+            sm[(size_t)word * T] = v;
+    }
     // LLR stage s (off = p.llr_off[s]) in lane `owner`'s space, resolved once per node step
     struct View {
         float* p;
@@ -63,8 +75,8 @@ struct FLane {
 // _mm256_max_ps lane: returns the second operand unless a > b
 __device__ __forceinline__ float fmax_ps(float a, float b) { return a > b ? a : b; }
 
-template <bool IS_G, int UNR>
-__device__ __forceinline__ void fg_block(const FLane& c, const float* row, const FLane::View& src, const FLane::View& dst, bool from_row,
+template <bool IS_G, int UNR, class FLane>
+__device__ __forceinline__ void fg_block(const FLane& c, const float* row, const typename FLane::View& src, const typename FLane::View& dst, bool from_row,
                                          int h, int lb, uint32_t ol)
 {
     const bool row16 = from_row && ((reinterpret_cast<uintptr_t>(row) & 15u) == 0);
@@ -99,7 +111,7 @@ __device__ __forceinline__ void fg_block(const FLane& c, const float* row, const
 }
 
 // f / g step of a node of size 2^s (RateRNode::decode scl_avx_float.cpp:238-262)
-template <bool IS_G>
+template <bool IS_G, class FLane>
 __device__ __forceinline__ void sclf_fg(FLane& c, const SclFParams& p, int s, const float* row)
 {
     const bool active = c.l < c.P;
@@ -107,8 +119,8 @@ __device__ __forceinline__ void sclf_fg(FLane& c, const SclFParams& p, int s, co
     const bool from_row = (s == p.S) && !p.root_leaf;
     const uint32_t o = c.own_llr.get(s), ol = c.own_L.get(s - 1);
     const int lb = p.bitL_off[s - 1];
-    const FLane::View src = from_row ? c.view(s - 1, p.llr_off[s - 1], (uint32_t)c.l) : c.view(s, p.llr_off[s], o);
-    const FLane::View dst = c.view(s - 1, p.llr_off[s - 1], (uint32_t)c.l);
+    const typename FLane::View src = from_row ? c.view(s - 1, p.llr_off[s - 1], (uint32_t)c.l) : c.view(s, p.llr_off[s], o);
+    const typename FLane::View dst = c.view(s - 1, p.llr_off[s - 1], (uint32_t)c.l);
     if (active) {
         uint32_t bw = 0;
         if (h >= 4) {
@@ -139,11 +151,11 @@ __device__ __forceinline__ void sclf_fg(FLane& c, const SclFParams& p, int s, co
 // the three sums of a leaf (own stage buffer), each in the reference's order: lane k of 8 accumulates elements
 // k, k+8, ... starting from +0, pads of a short node are 0, then x[0]+x[1]+...+x[7] left to right
 // (RateZeroDecoder :316-337, RepetitionDecoder :428-455, reduce_add_ps avxconvenience.h:256-272)
-template <bool WANT_ALL>
+template <bool WANT_ALL, class FLane>
 __device__ __forceinline__ void sclf_sums(const FLane& c, const SclFParams& p, int s, float& neg, float& pos, float& all)
 {
     const int n = 1 << s;
-    const FLane::View v = c.view(s, p.llr_off[s], (uint32_t)c.l);
+    const typename FLane::View v = c.view(s, p.llr_off[s], (uint32_t)c.l);
     float an[8], ap[8], aa[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) an[k] = ap[k] = aa[k] = 0.0f;
@@ -164,6 +176,7 @@ __device__ __forceinline__ void sclf_sums(const FLane& c, const SclFParams& p, i
 }
 
 // RateZeroDecoder::decode scl_avx_float.cpp:316-337: metric += sum(min(llr, 0)), decisions 0, no fork, no re-sort
+template <class FLane>
 __device__ __forceinline__ void sclf_r0(FLane& c, const SclFParams& p, int s, int side)
 {
     if (c.l < c.P) {
@@ -179,13 +192,14 @@ __device__ __forceinline__ void sclf_r0(FLane& c, const SclFParams& p, int s, in
 // findWeakLlrs (arrayfuncs.h:209-231) on the |LLR| floats stored in place in the own stage buffer (the reference
 // works on a scratch copy mTemp; the LLRs of a leaf are dead once their signs are taken): `want` passes of a
 // selection sort that takes the FIRST minimum (strict '<') of positions [i, n) and swaps it to position i.
+template <class FLane>
 __device__ __forceinline__ void sclf_find_weak(const FLane& c, int s, int off, int want, int (&widx)[4], float (&wval)[4])
 {
     const int n = 1 << s;
     WeakIdx ix;
     ix.init();
     const int lim = n - 1 < want ? n - 1 : want;
-    const FLane::View v = c.view(s, off, (uint32_t)c.l);
+    const typename FLane::View v = c.view(s, off, (uint32_t)c.l);
     for (int i = 0; i < lim; ++i) {
         const float vi = v[i];
         float bv = vi;
@@ -213,10 +227,11 @@ __device__ __forceinline__ void sclf_find_weak(const FLane& c, int s, int off, i
 
 // first phase of RateOne / SPC leaves: decisions = sign bits into the own side buffer, |llr| in place; returns the
 // parity of the signs
+template <class FLane>
 __device__ __forceinline__ uint32_t sclf_signs_and_abs(const FLane& c, const SclFParams& p, int s, int side)
 {
     const int n = 1 << s, dst = side ? p.bitR_off[s] : p.bitL_off[s];
-    const FLane::View v = c.view(s, p.llr_off[s], (uint32_t)c.l);
+    const typename FLane::View v = c.view(s, p.llr_off[s], (uint32_t)c.l);
     uint32_t par = 0, acc = 0;
     if (n >= 4) { // four loads in flight, then the in-place stores
         for (int j = 0; j < n; j += 4) {
@@ -250,6 +265,7 @@ __device__ __forceinline__ uint32_t sclf_signs_and_abs(const FLane& c, const Scl
 }
 
 // RepetitionDecoder::decode scl_avx_float.cpp:428-481 (only built for n < 8)
+template <class FLane>
 __device__ __forceinline__ void sclf_rep(FLane& c, const SclFParams& p, int s, int side)
 {
     float v[2] = { -INFINITY, -INFINITY };
@@ -276,6 +292,7 @@ __device__ __forceinline__ void sclf_rep(FLane& c, const SclFParams& p, int s, i
 }
 
 // RateOneDecoder::decode scl_avx_float.cpp:353-413
+template <class FLane>
 __device__ __forceinline__ void sclf_r1(FLane& c, const SclFParams& p, int s, int side)
 {
     float v[4] = { -INFINITY, -INFINITY, -INFINITY, -INFINITY };
@@ -307,6 +324,7 @@ __device__ __forceinline__ void sclf_r1(FLane& c, const SclFParams& p, int s, in
 }
 
 // SpcDecoder::decode scl_avx_float.cpp:498-621
+template <class FLane>
 __device__ __forceinline__ void sclf_spc(FLane& c, const SclFParams& p, int s, int side)
 {
     float v[8];
@@ -349,8 +367,10 @@ __device__ __forceinline__ void sclf_spc(FLane& c, const SclFParams& p, int s, i
     set_side(c, s, side);
 }
 
+template <bool BA>
 __global__ void __launch_bounds__(128) k_scl_f32(const __grid_constant__ SclFParams p)
 {
+    using FLane = FLaneT<BA>;
     extern __shared__ __align__(16) uint32_t smem[];
     const int T = blockDim.x, t = threadIdx.x;
     uint32_t* crc_table = smem; // 256 words
@@ -452,17 +472,20 @@ cudaError_t launch_scl_f32(const SclFLaunch& L, const float* d_llr, uint8_t* d_i
     p.B = B;
     p.frame_idx = d_frame_idx;
     p.count = d_count;
-    cudaError_t e = cudaFuncSetAttribute(k_scl_f32, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes);
+    // decision words in the arena (long codes) -> the instantiation whose ld / st test the offset flag
+    const bool ba = (p.bitR_off[p.S] & kArena) != 0;
+    void (*kern)(SclFParams) = ba ? k_scl_f32<true> : k_scl_f32<false>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes);
     // several CTAs per SM only fit when the L1/shared split is at its shared-memory maximum; a single CTA keeps the
     // default split (the rest stays L1 for the channel rows and the arena)
     if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(k_scl_f32, cudaFuncAttributePreferredSharedMemoryCarveout,
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout,
                                  L.per_sm > 1 ? (int)cudaSharedmemCarveoutMaxShared : (int)cudaSharedmemCarveoutDefault);
     if (e != cudaSuccess) return e;
     const int gpc = L.threads / p.G;
     size_t nb = (B + gpc - 1) / gpc;
     const int grid = (int)(nb < (size_t)L.grid ? nb : (size_t)L.grid);
-    k_scl_f32<<<grid, L.threads, L.smem_bytes, st>>>(p);
+    kern<<<grid, L.threads, L.smem_bytes, st>>>(p);
     return cudaGetLastError();
 }
 
@@ -486,40 +509,47 @@ int plan_scl_f32(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, 
     p.G = G;
     p.root_leaf = root_leaf ? 1 : 0;
     const int top_llr = root_leaf ? S : S - 1;
-    int bit_words = 0;
-    for (int s = 0; s <= S; ++s) bit_words += 2 * (s >= 5 ? (1 << (s - 5)) : 1);
     const size_t sm_total = 233472 < smem_max + 1024 ? 233472 : smem_max + 1024; // per SM, 1 KiB reserved per CTA
     // candidates in order of preference: (threads, CTAs per SM); the first whose decision words fit wins, then as
     // many of the small LLR stages as fit go to shared memory
     static const int cand[][2] = { { 128, 8 }, { 128, 6 }, { 128, 4 }, { 128, 3 }, { 128, 2 }, { 128, 1 }, { 64, 1 }, { 32, 1 } };
-    int T = 0, per_sm = 0, smem_top = -1;
+    int T = 0, per_sm = 0, smem_top = -1, bit_top = S;
     int force_t = -1, force_n = -1; // experiment overrides (tools/sweep_scl.sh)
     if (const char* e = getenv("PC_SCLF_THREADS")) force_t = atoi(e);
     if (const char* e = getenv("PC_SCLF_CTAS")) force_n = atoi(e);
-    for (int pass = 0; pass < 2 && !T; ++pass)
-    for (size_t ci = 0; ci < sizeof(cand) / sizeof(cand[0]); ++ci) {
-        const int t = cand[ci][0], n = cand[ci][1];
-        if (t < G) continue;
-        if ((force_t > 0 && t != force_t) || (force_n > 0 && n != force_n)) continue;
-        size_t per_cta = sm_total / n - 1024;
-        if (per_cta > smem_max) per_cta = smem_max;
-        if (per_cta < 1024) continue;
-        const long budget = (long)((per_cta - 1024) / (4 * (size_t)t)); // words per lane
-        if (budget < bit_words) continue;
-        int w = bit_words, top = -1;
-        for (int s = 0; s <= top_llr && w + (1 << s) <= budget; ++s) {
-            w += 1 << s;
-            top = s;
+    // decision words of the stages > bit_top go to the arena: only when nothing fits otherwise (long codes)
+    const int bit_lo = S < 5 ? S : 5;
+    for (bit_top = S; bit_top >= bit_lo && !T; --bit_top) {
+        int bw_smem = 0;
+        for (int s = 0; s <= S; ++s)
+            if (s <= bit_top) bw_smem += 2 * (s >= 5 ? (1 << (s - 5)) : 1);
+        for (int pass = 0; pass < 2 && !T; ++pass)
+        for (size_t ci = 0; ci < sizeof(cand) / sizeof(cand[0]); ++ci) {
+            const int t = cand[ci][0], n = cand[ci][1];
+            if (t < G) continue;
+            if ((force_t > 0 && t != force_t) || (force_n > 0 && n != force_n)) continue;
+            if (bit_top < S && bit_top > 5 && t * n < 128) continue; // rather move another stage out than run 32 lanes
+            size_t per_cta = sm_total / n - 1024;
+            if (per_cta > smem_max) per_cta = smem_max;
+            if (per_cta < 1024) continue;
+            const long budget = (long)((per_cta - 1024) / (4 * (size_t)t)); // words per lane
+            if (budget < bw_smem) continue;
+            int w = bw_smem, top = -1;
+            for (int s = 0; s <= top_llr && w + (1 << s) <= budget; ++s) {
+                w += 1 << s;
+                top = s;
+            }
+            // first pass: the whole tree on chip with as many CTAs per SM as fit (at least 256 lanes); second pass: the most lanes whose
+            // decision words fit (measured, N=1024 L=8: 3 x 128 lanes 1.48 Gbit/s, 2 x 128 1.40, 1 x 128 0.82; the large
+            // stages then live in the arena). More than 3 CTAs would not be resident anyway (96 registers per thread).
+            if (force_n <= 0 && pass == 0 && (top < top_llr || t * n < 256)) continue;
+            if (force_n <= 0 && pass == 1 && n > 3) continue;
+            T = t;
+            per_sm = n;
+            smem_top = top;
+            break;
         }
-        // first pass: the whole tree on chip with as many CTAs per SM as fit (at least 256 lanes); second pass: the most lanes whose
-        // decision words fit (measured, N=1024 L=8: 3 x 128 lanes 1.48 Gbit/s, 2 x 128 1.40, 1 x 128 0.82; the large
-        // stages then live in the arena). More than 3 CTAs would not be resident anyway (96 registers per thread).
-        if (force_n <= 0 && pass == 0 && (top < top_llr || t * n < 256)) continue;
-        if (force_n <= 0 && pass == 1 && n > 3) continue;
-        T = t;
-        per_sm = n;
-        smem_top = top;
-        break;
+        if (T) break;
     }
     if (!T) {
         *msg = "SCL path state does not fit shared memory (block length too large for this list size)";
@@ -538,10 +568,17 @@ int plan_scl_f32(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, 
     }
     for (int s = 0; s <= S; ++s) {
         const int bw = s >= 5 ? (1 << (s - 5)) : 1;
-        p.bitL_off[s] = w;
-        w += bw;
-        p.bitR_off[s] = w;
-        w += bw;
+        if (s <= bit_top) {
+            p.bitL_off[s] = w;
+            w += bw;
+            p.bitR_off[s] = w;
+            w += bw;
+        } else { // 4-byte arena elements hold floats or decision words alike
+            p.bitL_off[s] = kArena | e;
+            e += bw;
+            p.bitR_off[s] = kArena | e;
+            e += bw;
+        }
     }
     p.words = w;
     p.smem_top = smem_top;

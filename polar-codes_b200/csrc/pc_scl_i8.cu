@@ -28,11 +28,8 @@
 
 namespace pc {
 
-// word indices with kArena set address the L2-resident arena ([word][lane], lanes of a group adjacent) instead of
-// shared memory: the host planner moves the largest LLR stages there so that more codewords fit one SM
-constexpr int kArena = 1 << 30;
-
-struct Lane {
+template <bool BA> // BA: some decision words live in the arena (long codes); off = no flag tests
+struct LaneT {
     uint32_t* sm;   // smem base + tid (word w at sm[w * T])
     uint32_t* ar;   // arena base + global lane id (word w at ar[w * AS])
     size_t AS;
@@ -40,9 +37,19 @@ struct Lane {
     int P;          // live paths (uniform)
     int metric;     // path metric (the reference uses long; |metric| <= 128 N fits easily)
     Tbl own_llr, own_L, own_R;
-    // decision words: shared memory only
-    __device__ __forceinline__ uint32_t ld(int word, uint32_t owner) const { return sm[(size_t)word * T + ((int)owner - l)]; }
-    __device__ __forceinline__ void st(int word, uint32_t v) const { sm[(size_t)word * T] = v; }
+    // decision words: shared memory, or the arena for the largest stages of long codes (flag in the offset)
+    __device__ __forceinline__ uint32_t ld(int word, uint32_t owner) const
+    {
+        if (BA && (word & kArena)) return ar[(size_t)(word & (kArena - 1)) * AS + ((int)owner - l)];
+        return sm[(size_t)word * T + ((int)owner - l)];
+    }
+    __device__ __forceinline__ void st(int word, uint32_t v) const
+    {
+        if (BA && (word & kArena))
+            ar[(size_t)(word & (kArena - 1)) * AS] = v;
+        else
+            sm[(size_t)word * T] = v;
+    }
     // LLR stage starting at word offset `off` (p.llr_off[s]) in lane `owner`'s space, resolved once per node step
     struct View {
         uint32_t* p;
@@ -63,7 +70,7 @@ __device__ __forceinline__ uint32_t bytemask(int nbytes) { return nbytes >= 4 ? 
 
 // f / g step of a node of size 2^s: parent LLRs (stage s, through the owner table or the channel row) -> child
 // LLRs (stage s-1, own buffer). RateRNode::decode scl_fip_char.cpp:315-349.
-template <bool IS_G>
+template <bool IS_G, class Lane>
 __device__ __forceinline__ void scl_fg(Lane& c, const SclParams& p, int s, const int8_t* row)
 {
     const bool active = c.l < c.P;
@@ -72,7 +79,7 @@ __device__ __forceinline__ void scl_fg(Lane& c, const SclParams& p, int s, const
     const bool from_row = (s == p.S) && !p.root_leaf;
     const uint32_t o = c.own_llr.get(s), ol = c.own_L.get(s - 1);
     const int lb = p.bitL_off[s - 1];
-    const Lane::View src = c.view(from_row ? p.llr_off[s - 1] : p.llr_off[s], o), dst = c.view(p.llr_off[s - 1], (uint32_t)c.l);
+    const typename Lane::View src = c.view(from_row ? p.llr_off[s - 1] : p.llr_off[s], o), dst = c.view(p.llr_off[s - 1], (uint32_t)c.l);
     if (active) {
         if (h >= 16) {
             // four words per step: all loads first (source and destination may alias as far as the compiler knows, so
@@ -132,10 +139,11 @@ __device__ __forceinline__ void scl_fg(Lane& c, const SclParams& p, int s, const
 }
 
 // sums of the negative / positive LLRs of the own stage-s buffer (exact integer sums, dp4a)
+template <class Lane>
 __device__ __forceinline__ void llr_sums(const Lane& c, const SclParams& p, int s, int& neg, int& pos)
 {
     const int n = 1 << s, nw = stage_words(s);
-    const Lane::View v = c.view(p.llr_off[s], (uint32_t)c.l);
+    const typename Lane::View v = c.view(p.llr_off[s], (uint32_t)c.l);
     neg = 0;
     pos = 0;
     if (nw >= 4) {
@@ -166,6 +174,7 @@ __device__ __forceinline__ void llr_sums(const Lane& c, const SclParams& p, int 
 }
 
 // RateZeroDecoder::decode scl_fip_char.cpp:387-421: metric += sum(min(llr, 0)), decisions 0, no fork, no re-sort
+template <class Lane>
 __device__ __forceinline__ void scl_r0(Lane& c, const SclParams& p, int s, int side)
 {
     if (c.l < c.P) {
@@ -182,11 +191,12 @@ __device__ __forceinline__ void scl_r0(Lane& c, const SclParams& p, int s, int s
 // a selection sort that takes the FIRST minimum (strict '<') of positions [i, n) and swaps it to position i. The
 // swaps mutate the array, which decides later ties, so they are performed for real. The Indices array of the
 // reference is tracked as its first four entries plus a patch list for positions >= 4.
+template <class Lane>
 __device__ __forceinline__ void scl_find_weak(const Lane& c, int off, int n, int want, int (&widx)[4], int (&wval)[4])
 {
     int I[4] = { 0, 1, 2, 3 }, ppos[4] = { -1, -1, -1, -1 }, pidx[4] = { 0, 0, 0, 0 };
     int np = 0;
-    const Lane::View v = c.view(off, (uint32_t)c.l);
+    const typename Lane::View v = c.view(off, (uint32_t)c.l);
     const int lim = n - 1 < want ? n - 1 : want;
     const int nw = (n + 3) >> 2;
     for (int i = 0; i < lim; ++i) {
@@ -259,10 +269,11 @@ __device__ __forceinline__ void scl_find_weak(const Lane& c, int off, int n, int
 
 // first phase of RateOne / SPC leaves: decisions = signs into the own side buffer, |max(llr, -127)| in place,
 // returns the XOR of all LLR words (its byte MSBs give the parity)
+template <class Lane>
 __device__ __forceinline__ uint32_t scl_signs_and_abs(const Lane& c, const SclParams& p, int s, int side)
 {
     const int n = 1 << s, nw = stage_words(s), dst = side ? p.bitR_off[s] : p.bitL_off[s];
-    const Lane::View v = c.view(p.llr_off[s], (uint32_t)c.l);
+    const typename Lane::View v = c.view(p.llr_off[s], (uint32_t)c.l);
     uint32_t par = 0, acc = 0;
     if (nw >= 8) { // eight words (one decision word) per step, loads first
         for (int j = 0; j < nw; j += 8) {
@@ -295,6 +306,7 @@ __device__ __forceinline__ uint32_t scl_signs_and_abs(const Lane& c, const SclPa
 }
 
 // RepetitionDecoder::decode scl_fip_char.cpp:508-581
+template <class Lane>
 __device__ __forceinline__ void scl_rep(Lane& c, const SclParams& p, int s, int side)
 {
     int v[2] = { INT_MIN, INT_MIN };
@@ -319,6 +331,7 @@ __device__ __forceinline__ void scl_rep(Lane& c, const SclParams& p, int s, int 
 }
 
 // RateOneDecoder::decode scl_fip_char.cpp:423-505
+template <class Lane>
 __device__ __forceinline__ void scl_r1(Lane& c, const SclParams& p, int s, int side)
 {
     int v[4] = { INT_MIN, INT_MIN, INT_MIN, INT_MIN };
@@ -348,6 +361,7 @@ __device__ __forceinline__ void scl_r1(Lane& c, const SclParams& p, int s, int s
 }
 
 // SpcDecoder::decode scl_fip_char.cpp:583-726
+template <class Lane>
 __device__ __forceinline__ void scl_spc(Lane& c, const SclParams& p, int s, int side)
 {
     int v[8];
@@ -390,8 +404,10 @@ __device__ __forceinline__ void scl_spc(Lane& c, const SclParams& p, int s, int 
     set_side(c, s, side);
 }
 
+template <bool BA>
 __global__ void __launch_bounds__(256) k_scl_i8(const __grid_constant__ SclParams p)
 {
+    using Lane = LaneT<BA>;
     extern __shared__ __align__(16) uint32_t smem[];
     const int T = blockDim.x, t = threadIdx.x;
     uint32_t* crc_table = smem; // 256 words
@@ -425,7 +441,7 @@ __global__ void __launch_bounds__(256) k_scl_i8(const __grid_constant__ SclParam
         if (p.root_leaf && c.l == 0) { // stage the channel row (the root is a leaf)
             const int nw = stage_words(p.S);
             if (N >= 4) {
-                const Lane::View v = c.view(p.llr_off[p.S], (uint32_t)c.l);
+                const typename Lane::View v = c.view(p.llr_off[p.S], (uint32_t)c.l);
                 for (int j = 0; j < nw; ++j) v.set(j, reinterpret_cast<const uint32_t*>(row)[j]);
             } else {
                 c.view(p.llr_off[p.S], (uint32_t)c.l).set(0, (uint32_t)(uint8_t)row[0] | ((uint32_t)(uint8_t)row[1] << 8));
@@ -499,22 +515,25 @@ cudaError_t launch_scl_i8(const SclLaunch& L, const int8_t* d_llr, uint8_t* d_in
     p.B = B;
     p.frame_idx = d_frame_idx;
     p.count = d_count;
-    cudaError_t e = cudaFuncSetAttribute(k_scl_i8, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes);
+    // decision words in the arena (long codes) -> the instantiation whose ld / st test the offset flag
+    const bool ba = (p.bitR_off[p.S] & kArena) != 0;
+    void (*kern)(SclParams) = ba ? k_scl_i8<true> : k_scl_i8<false>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes);
     // several CTAs per SM only fit when the L1/shared split is at its shared-memory maximum; a single CTA keeps the
     // default split (the rest stays L1 for the channel rows and the arena)
     if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(k_scl_i8, cudaFuncAttributePreferredSharedMemoryCarveout,
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout,
                                  L.per_sm > 1 ? (int)cudaSharedmemCarveoutMaxShared : (int)cudaSharedmemCarveoutDefault);
     if (e != cudaSuccess) return e;
     if (getenv("PC_DEBUG_OCC")) {
         int occ = 0;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_scl_i8, L.threads, L.smem_bytes);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, L.threads, L.smem_bytes);
         fprintf(stderr, "k_scl_i8: %d threads, %zu B smem, grid %d, occupancy %d CTAs/SM\n", L.threads, L.smem_bytes, L.grid, occ);
     }
     const int gpc = L.threads / p.G;
     size_t nb = (B + gpc - 1) / gpc;
     const int grid = (int)(nb < (size_t)L.grid ? nb : (size_t)L.grid);
-    k_scl_i8<<<grid, L.threads, L.smem_bytes, st>>>(p);
+    kern<<<grid, L.threads, L.smem_bytes, st>>>(p);
     return cudaGetLastError();
 }
 
@@ -538,8 +557,6 @@ int plan_scl_i8(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, S
     p.G = G;
     p.root_leaf = root_leaf ? 1 : 0;
     const int top_llr = root_leaf ? S : S - 1;
-    int bit_words = 0;
-    for (int s = 0; s <= S; ++s) bit_words += 2 * (s >= 5 ? (1 << (s - 5)) : 1);
     // Lanes (= list paths) resident per SM decide throughput: the kernel is latency bound (one lane per path, long
     // dependent chains), so the planner trades shared-memory residency of the largest LLR stages for more lanes.
     // Candidates in order of preference; the first one that keeps stages <= `pref` in shared memory wins. Measured
@@ -549,31 +566,40 @@ int plan_scl_i8(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, S
     if (const char* e = getenv("PC_SCL_LANES")) force_lanes = atoi(e);
     if (const char* e = getenv("PC_SCL_SMEMTOP")) force_top = atoi(e);
     static const int cand[] = { 512, 384, 256, 192, 128, 96, 64, 32 };
-    int T = 0, per_sm = 0, smem_top = -1;
-    for (int pass = 0; pass < 2 && !T; ++pass) {
-        for (size_t ci = 0; ci < sizeof(cand) / sizeof(cand[0]); ++ci) {
-            const int lanes = cand[ci];
-            if (force_lanes > 0 && lanes != force_lanes) continue;
-            const int t = lanes <= 256 ? lanes : 128, n = lanes / t;
-            if (t < G || (t % G) != 0) continue;
-            size_t per_cta = 233472 / (size_t)n - 1024;
-            if (per_cta > smem_max) per_cta = smem_max;
-            const long budget = ((long)per_cta - 1024) / (4L * t); // words per lane
-            if (budget < bit_words) continue;
-            int w = bit_words, top = -1;
-            for (int st = 0; st <= top_llr; ++st) {
-                const int sw = st >= 2 ? (1 << (st - 2)) : 1;
-                if (w + sw > budget || (force_top > -2 && st > force_top)) break;
-                w += sw;
-                top = st;
+    int T = 0, per_sm = 0, smem_top = -1, bit_top = S;
+    // decision words of the stages > bit_top go to the arena: only when nothing fits otherwise (N >= 16384 at L = 8)
+    const int bit_lo = S < 5 ? S : 5;
+    for (bit_top = S; bit_top >= bit_lo && !T; --bit_top) {
+        int bw_smem = 0;
+        for (int s = 0; s <= S; ++s)
+            if (s <= bit_top) bw_smem += 2 * (s >= 5 ? (1 << (s - 5)) : 1);
+        for (int pass = 0; pass < 2 && !T; ++pass) {
+            for (size_t ci = 0; ci < sizeof(cand) / sizeof(cand[0]); ++ci) {
+                const int lanes = cand[ci];
+                if (force_lanes > 0 && lanes != force_lanes) continue;
+                if (bit_top < S && bit_top > 5 && lanes < 128) continue; // rather move another stage out than run 32 lanes
+                const int t = lanes <= 256 ? lanes : 128, n = lanes / t;
+                if (t < G || (t % G) != 0) continue;
+                size_t per_cta = 233472 / (size_t)n - 1024;
+                if (per_cta > smem_max) per_cta = smem_max;
+                const long budget = ((long)per_cta - 1024) / (4L * t); // words per lane
+                if (budget < bw_smem) continue;
+                int w = bw_smem, top = -1;
+                for (int st = 0; st <= top_llr; ++st) {
+                    const int sw = st >= 2 ? (1 << (st - 2)) : 1;
+                    if (w + sw > budget || (force_top > -2 && st > force_top)) break;
+                    w += sw;
+                    top = st;
+                }
+                // first pass: insist on the preferred residency; second pass: anything that fits
+                if (pass == 0 && force_lanes <= 0 && top < (top_llr < pref ? top_llr : pref)) continue;
+                T = t;
+                per_sm = n;
+                smem_top = top;
+                break;
             }
-            // first pass: insist on the preferred residency; second pass: anything that fits
-            if (pass == 0 && force_lanes <= 0 && top < (top_llr < pref ? top_llr : pref)) continue;
-            T = t;
-            per_sm = n;
-            smem_top = top;
-            break;
         }
+        if (T) break;
     }
     if (!T) {
         *msg = "SCL path state does not fit shared memory (block length too large for this list size)";
@@ -593,10 +619,17 @@ int plan_scl_i8(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, S
     }
     for (int s = 0; s <= S; ++s) {
         const int bw = s >= 5 ? (1 << (s - 5)) : 1;
-        p.bitL_off[s] = w;
-        w += bw;
-        p.bitR_off[s] = w;
-        w += bw;
+        if (s <= bit_top) {
+            p.bitL_off[s] = w;
+            w += bw;
+            p.bitR_off[s] = w;
+            w += bw;
+        } else {
+            p.bitL_off[s] = kArena | aw;
+            aw += bw;
+            p.bitR_off[s] = kArena | aw;
+            aw += bw;
+        }
     }
     p.words = w;
     p.arena_words = aw;
