@@ -1,6 +1,7 @@
 // C-ABI of libpolar_b200.so (include/polar_b200.h): handle management, host-side tree compilation,
 // launch planning. No CPU fallback: every compute entry point needs a usable CUDA device.
 #include <algorithm>
+#include <cstdio>
 #include <atomic>
 #include <climits>
 #include <cstdlib>
@@ -76,13 +77,15 @@ static int device_props(int* sms, size_t* smem_optin)
 // Greedy placement per candidate geometry: stages ascending into shared memory while they fit, the rest into
 // tensor memory while it fits, the rest into the arena; decision words likewise.
 // Environment overrides (tuning only): PC_FASTSSC_THREADS, PC_FASTSSC_CTAS, PC_FASTSSC_NOTMEM=1.
-static int plan_fastssc(pc_code* c)
+// cap_T: largest CTA size considered. 1024 for batches that fill the GPU; smaller for small batches, so that every SM gets
+// a CTA (N=16384, 65 536 frames: 64 CTAs of 1024 threads 76 Gbit/s, 128 CTAs of 512 threads 102)
+static int plan_fastssc(pc_code* c, int cap_T = 1024)
 {
     int sms = 0;
     size_t smem_max = 0;
     int st = device_props(&sms, &smem_max);
     if (st != PC_OK) return st;
-    FastSscLaunch& P = c->plan;
+    FastSscLaunch& P = cap_T >= 1024 ? c->plan : c->plan_small;
     const FastSscProgram& g = c->prog;
     P.S = g.S;
     P.K = g.K;
@@ -110,7 +113,7 @@ static int plan_fastssc(pc_code* c)
     } best;
     for (int per_sm = 1; per_sm <= 2; ++per_sm) {
         if (force_ctas != -1 && per_sm != force_ctas) continue;
-        for (int T = 1024; T >= 32; T -= 32) {
+        for (int T = cap_T; T >= 32; T -= 32) {
             if (force_T != -1 ? T != force_T : (T != 32 && T != 64 && (T % 128) != 0)) continue;
             const size_t cta_budget = std::min(smem_max, sm_smem / per_sm - 1024);
             if (cta_budget < 1024 + 64 * (size_t)T) continue;
@@ -169,7 +172,10 @@ static int plan_fastssc(pc_code* c)
             if (q.score > best.score) best = q;
         }
     }
-    if (best.score < 0) return fail(PC_ERR_UNSUPPORTED, "fastssc_i8: no launch configuration fits the on-chip memories");
+    if (best.score < 0) {
+        if (getenv("PC_DEBUG_OCC")) fprintf(stderr, "plan_fastssc: cap_T %d top %d smem_max %zu nbw %d\n", cap_T, top, smem_max, P.nbw);
+        return fail(PC_ERR_UNSUPPORTED, "fastssc_i8: no launch configuration fits the on-chip memories");
+    }
     P.threads = best.T;
     P.ctas_per_sm = best.per_sm;
     P.grid = sms * best.per_sm;
@@ -191,8 +197,11 @@ static int plan_fastssc(pc_code* c)
         if (e != cudaSuccess) return cuda_fail(e, "cudaMalloc(arena)");
         c->arena_bytes = need;
     }
-    P.arena = c->arena;
-    c->plan_valid = true;
+    P.arena = c->arena; // refreshed at every launch (the other plan may have grown the buffer)
+    if (cap_T >= 1024)
+        c->plan_valid = true;
+    else
+        c->plan_small_cap = cap_T;
     return PC_OK;
 }
 
@@ -388,6 +397,7 @@ int pc_code_set_crc(pc_code* c, int crc_kind)
     if (!crc_spec(crc_kind, s)) return fail(PC_ERR_ARG, "CRC INVALID SIZE!");
     c->crc_kind = crc_kind;
     c->plan_valid = false;
+    c->plan_small_cap = 0;
     c->scl_plan_valid = false;
     c->f32_plan_valid = false;
     c->sclf_plan_valid = false;
@@ -399,6 +409,7 @@ int pc_code_set_systematic(pc_code* c, int systematic)
     if (!c) return fail(PC_ERR_ARG, "null code");
     c->systematic = systematic ? 1 : 0;
     c->plan_valid = false;
+    c->plan_small_cap = 0;
     c->scl_plan_valid = false;
     c->f32_plan_valid = false;
     c->sclf_plan_valid = false;

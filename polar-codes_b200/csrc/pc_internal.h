@@ -67,6 +67,8 @@ struct pc_code {
     // Fast-SSC launch plan
     pc::FastSscLaunch plan;
     bool plan_valid = false;
+    pc::FastSscLaunch plan_small; // the same code planned with smaller CTAs, for batches that would leave SMs idle
+    int plan_small_cap = 0;       // CTA size cap plan_small was made for (0 = none)
     uint32_t* arena = nullptr;
     size_t arena_bytes = 0;
     // staging for the *_host entry points

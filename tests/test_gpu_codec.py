@@ -184,3 +184,22 @@ def test_channel_generator_and_counting(pcb, ref):
     diff = np.unpackbits(h_info ^ exp, axis=1).sum(axis=1)
     assert counts.tolist() == [B, int((diff > 0).sum()), int(diff.sum()), int((eok == 0).sum())]
     assert 0.01 < counts[1].item() / B < 0.5
+
+
+@pytest.mark.parametrize("N,K,B", [(1024, 512, 8192), (1024, 512, 40000), (1024, 512, 70000), (16384, 8192, 8192),
+                                   (4096, 3072, 20000), (256, 128, 100000)])
+def test_fastssc_small_batch_plans(pcb, ref, N, K, B):
+    """batches that would leave SMs idle with the big-batch plan run a plan with smaller CTAs (pc_api_decode.inc
+    run_fastssc_i8): same answers, checked against the reference on a slice and against the big-batch plan on all"""
+    import torch
+    rng = np.random.default_rng(B)
+    fz = ref.frozen_bits(N, K, 0.0)
+    dec = pcb.PolarDecoder(N, 1, list(fz), "char")
+    base = awgn_llr_i8(rng, 2048, N, 2.0, K / N)
+    llr = torch.from_numpy(base).cuda().repeat((B + 2047) // 2048, 1)[:B].contiguous()
+    got, ok = dec.decode_batch(llr, return_ok=True)
+    exp, eok = ref.decode_batch(N, 1, fz, "char", base, threads=8)
+    g, o = got.cpu().numpy(), ok.cpu().numpy()
+    for lo in range(0, B, 2048):
+        n = min(2048, B - lo)
+        assert np.array_equal(g[lo:lo + n], exp[:n]) and np.array_equal(o[lo:lo + n], eok[:n])
