@@ -2,11 +2,11 @@
 // (pc_fastssc_f32_core.h). Replaces FastSscAvxFloat::decode (reference src/polarcode/decoding/fastssc_avx_float.cpp:940-955).
 // The float LLR tree of a codeword is 4 N bytes, far beyond shared memory at useful occupancy, so the per-thread
 // stages and the decision words live in a thread-interleaved arena (every warp access to one element index is one
-// coalesced 128-byte transaction). Measured (profiles/r01_fastssc_f32_full_v1.txt): at N=1024 the arena of 75 776
-// threads is 320 MB, far beyond the L2, and the kernel is DRAM-latency bound (long_scoreboard 22.7 cycles per issue,
-// 10 GB of DRAM traffic per 262 144 frames against 1.1 GB algorithmic). Moving stages <= 5 to shared memory through
-// generic pointers measured SLOWER (13.8 vs 17.5 Gbit/s); the fix is a warp per codeword with the tree in shared
-// memory, next round.
+// coalesced 128-byte transaction). With the f / g loops loading eight element pairs before they store, the kernel is
+// DRAM-bandwidth bound on that arena (profiles/r01_fastssc_f32_full_v2.txt: 3.7 TB/s, 47 KB of traffic per codeword).
+// Moving the small stages to shared memory through generic pointers measured SLOWER both before and after that change
+// (stages <= 3 / 4 / 5 on chip: 37 / 33 / 28 Gbit/s against 41 all-arena, N=1024); the way down is a warp per codeword
+// with the whole tree in shared memory, next round.
 // Compiled without FMA contraction (-fmad=false is applied through __fadd_rn in the core).
 #include "pc_fastssc_f32_core.h"
 #include "pc_kernels.cuh"
