@@ -203,3 +203,42 @@ def test_fastssc_small_batch_plans(pcb, ref, N, K, B):
     for lo in range(0, B, 2048):
         n = min(2048, B - lo)
         assert np.array_equal(g[lo:lo + n], exp[:n]) and np.array_equal(o[lo:lo + n], eok[:n])
+
+
+@pytest.mark.parametrize("N,K,B", [(1024, 512, 1 << 20), (16384, 8192, 1 << 16)])
+def test_full_size_properties(pcb, N, K, B):
+    """BASELINE.json batch sizes, size-independent properties of the code (no oracle needed): linearity of both encoder
+    modes, the systematic property, and encode -> noiseless BPSK -> decode round trips through every decoder family"""
+    import torch
+    fz = pcb.frozen_bits(N, K, 0.0)
+    kb = K // 8
+    g = torch.Generator(device="cuda").manual_seed(N)
+    a = torch.randint(0, 256, (B, kb), device="cuda", dtype=torch.uint8, generator=g)
+    b = torch.randint(0, 256, (B, kb), device="cuda", dtype=torch.uint8, generator=g)
+    enc = pcb.PolarEncoder(N, fz)                                   # Dummy detector: all K bits are payload
+    info_pos = torch.ones(N, dtype=torch.bool, device="cuda")
+    info_pos[torch.tensor(fz, device="cuda")] = False
+    for syst in (True, False):
+        enc.setSystematic(syst)
+        ca, cb, cab = enc.encode_batch(a), enc.encode_batch(b), enc.encode_batch(a ^ b)
+        assert torch.equal(ca ^ cb, cab)                            # linear code
+        if syst:
+            # systematic property on a slice (unpacking 2^20 x N bits at once would be 1 GiB of bools)
+            n = min(B, 1 << 14)
+            bits = ((ca[:n].unsqueeze(-1) >> torch.arange(7, -1, -1, device="cuda", dtype=torch.uint8)) & 1).reshape(n, N)
+            ibits = ((a[:n].unsqueeze(-1) >> torch.arange(7, -1, -1, device="cuda", dtype=torch.uint8)) & 1).reshape(n, K)
+            assert torch.equal(bits[:, info_pos], ibits)
+    # round trips: transmitted word -> LLR +-100 (bit 0 -> +) -> decoder returns the info block, detector true
+    enc.setSystematic(True)
+    enc.setErrorDetection(8, "crc")
+    code, sent = enc.encode_batch(a, return_info=True)              # `sent` carries the CRC-8 byte
+    n = B if N == 1024 else B // 4
+    for kind, L, frames in (("char", 1, n), ("float", 1, n // 4), ("char", 4, n // 64), ("float", 4, n // 128), (5, 4, n // 4)):
+        dec = pcb.PolarDecoder(N, L, fz, kind)
+        sub = code[:frames]
+        bits = ((sub.unsqueeze(-1) >> torch.arange(7, -1, -1, device="cuda", dtype=torch.uint8)) & 1).reshape(frames, N)
+        llr8 = (100 - 200 * bits.to(torch.int16)).to(torch.int8)
+        llr = llr8 if kind in ("char", 5) else llr8.to(torch.float32)
+        out, ok = dec.decode_batch(llr, return_ok=True)
+        assert torch.equal(out, sent[:frames]) and bool((ok == 1).all())
+        del bits, llr8, llr
