@@ -104,6 +104,7 @@ static int plan_fastssc(pc_code* c, int cap_T = 1024)
     if (const char* e = getenv("PC_FASTSSC_THREADS")) force_T = atoi(e);
     if (const char* e = getenv("PC_FASTSSC_CTAS")) force_ctas = atoi(e);
     if (const char* e = getenv("PC_FASTSSC_NOTMEM")) no_tmem = atoi(e);
+    const bool no_flip = getenv("PC_FASTSSC_NOFLIP") != nullptr; // experiment knob, see DESIGN.md 3.1 (open item)
     const size_t sm_smem = 233472; // 228 KiB per SM, 1 KiB of it reserved per resident CTA
     struct Plan {
         int T = 0, per_sm = 0, smem_chunks = 0, tm_alloc = 0, tm_cols = 0, arena_chunks = 0, bits_kind = 0, bits_base = 0;
@@ -115,6 +116,7 @@ static int plan_fastssc(pc_code* c, int cap_T = 1024)
         if (force_ctas != -1 && per_sm != force_ctas) continue;
         for (int T = cap_T; T >= 32; T -= 32) {
             if (force_T != -1 ? T != force_T : (T != 32 && T != 64 && (T % 128) != 0)) continue;
+            if (T * per_sm > 1024) continue; // 64 registers per thread: more would not be resident (and the grid would run in two rounds)
             const size_t cta_budget = std::min(smem_max, sm_smem / per_sm - 1024);
             if (cta_budget < 1024 + 64 * (size_t)T) continue;
             const size_t per_thread_budget = (cta_budget - 1024) / T;
@@ -165,10 +167,11 @@ static int plan_fastssc(pc_code* c, int cap_T = 1024)
             // 1 x 1024 threads 200.9 Gbit/s, 1 x 640 192.5, 1 x 960 176.2, 2 x 512 175.8, 1 x 512 167.5, 1 x 768 155.6,
             // 1 x 896 136.4 (the 1 x 1024 and 2 x 512 plans place every stage identically). So: maximise resident
             // threads up to the register-file limit (64 regs x 1024), prefer ONE CTA per SM, and charge only a little
-            // for arena use. Long codes, whose stages live mostly in the arena, measured the other way round
-            // (N=16384: 2 x 512 82 Gbit/s, 1 x 1024 76), hence the sign flip on the CTA term.
+            // for arena use. Full grids (2 x 148 x 1024 frames per launch), forced shapes: N=4096 1 x 1024 169 Gbit/s,
+            // 2 x 512 159; N=8192 155 / 152; N=16384 143 / 140, but 1 x 1024 showed single runs at 118 (N=8192) and
+            // 113 (N=16384) on the same box, so from N=8192 on (arena chunks >= 400) two CTAs of 512 stay preferred.
             q.score = (long)std::min(resident, 1024) * 100 - (ar_used ? 1000 + 4L * std::min(ar_used, 512) : 0) -
-                      (q.bits_kind == PK_ARENA ? 4000 : 0) - (per_sm - 1) * (ar_used >= 128 ? -2000 : 2000);
+                      (q.bits_kind == PK_ARENA ? 4000 : 0) - (per_sm - 1) * ((ar_used >= 400 && !no_flip) ? -2000 : 2000);
             if (q.score > best.score) best = q;
         }
     }
@@ -176,6 +179,9 @@ static int plan_fastssc(pc_code* c, int cap_T = 1024)
         if (getenv("PC_DEBUG_OCC")) fprintf(stderr, "plan_fastssc: cap_T %d top %d smem_max %zu nbw %d\n", cap_T, top, smem_max, P.nbw);
         return fail(PC_ERR_UNSUPPORTED, "fastssc_i8: no launch configuration fits the on-chip memories");
     }
+    if (getenv("PC_DEBUG_OCC"))
+        fprintf(stderr, "plan_fastssc: N=%d cap %d -> %d x %d threads, smem %zu B, arena chunks %d, tmem cols %d, score %ld\n", c->N, cap_T,
+                best.per_sm, best.T, best.smem_bytes, best.arena_chunks, best.tm_alloc, best.score);
     P.threads = best.T;
     P.ctas_per_sm = best.per_sm;
     P.grid = sms * best.per_sm;
