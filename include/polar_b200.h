@@ -23,7 +23,18 @@
  * h_* are host pointers. `stream` is a cudaStream_t passed as void* (NULL = default stream).
  * Bit order is the reference's: code/info bit i lives in byte i/8, bit 7-(i%8) (MSB first).
  * LLR >= 0 decodes to bit 0. Frames are rows: llr[B][N], info[B][ceil(K/8)], code[B][N/8].
- * There is no CPU fallback: every compute entry point fails with PC_ERR_CUDA when no GPU is usable. */
+ * There is no CPU fallback: every compute entry point fails with PC_ERR_CUDA when no GPU is usable.
+ *
+ * Devices, streams, alignment:
+ *  - A pc_code belongs to the CUDA device that was current at pc_code_create (tables, constant-pool slice, scratch
+ *    arenas and streams live there). Every entry point taking a pc_code returns PC_ERR_ARG when another device is
+ *    current; a host process that drives several GPUs creates one code object per device. The detector batch calls
+ *    without a code object keep one table per (device, kind).
+ *  - One pc_code may be in flight on ONE stream at a time: the calls share per-code scratch (quantiser output,
+ *    int8 -> float copy, failed-frame list, decoder arenas). Calls on the same stream serialise by stream order;
+ *    for concurrency create one code object per stream.
+ *  - d_llr / d_llr_out must be 16-byte aligned (rows of 16 bytes or more), d_info 4-byte aligned when ceil(K/8) is a multiple of 4, d_code
+ *    4-byte aligned for N >= 32 (PC_ERR_ARG otherwise; cudaMalloc'd bases and whole rows of them always qualify). */
 #ifndef POLAR_B200_H
 #define POLAR_B200_H
 #include <stddef.h>

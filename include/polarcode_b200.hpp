@@ -184,15 +184,16 @@ public:
     {
         return pc_crc_calculate(mKind, static_cast<const uint8_t*>(data), bits);
     }
-    /// appends the check bytes after `bytes` bytes of payload
+    /// errordetector.h:52-57: `bytes` is the block size INCLUDING the checksum; the last crcBytes() bytes of the block
+    /// are replaced (crc8.cpp:59-64). Nothing outside [data, data + bytes) is touched.
     virtual void generate(void* data, int bytes)
     {
         if (mKind == PC_CRC_NONE) return;
-        const size_t total = (size_t)bytes + crcBytes();
-        DeviceRow row(total);
+        if (bytes < (int)crcBytes()) throw std::invalid_argument("Detector::generate: block shorter than the checksum");
+        DeviceRow row((size_t)bytes);
         detail::check(pc_memcpy_h2d(row.d, data, (size_t)bytes));
-        detail::check(pc_crc_generate_batch(mKind, row.d, (int)total, 1, nullptr));
-        detail::check(pc_memcpy_d2h(data, row.d, total));
+        detail::check(pc_crc_generate_batch(mKind, row.d, bytes, 1, nullptr));
+        detail::check(pc_memcpy_d2h(data, row.d, (size_t)bytes));
     }
     /// CRC over the first bytes-c bytes against the trailing c bytes
     virtual bool check(void* data, int bytes)
@@ -213,10 +214,10 @@ public:
             if (check(data[i], nBytes)) return i;
         return -1;
     }
-    /// B rows of `bytes` payload bytes followed by room for the check bytes, DEVICE memory
+    /// B rows of `bytes` bytes each (checksum included, like generate()), DEVICE memory
     void generate_batch_device(uint8_t* d_rows, int bytes, size_t B, void* stream = nullptr)
     {
-        detail::check(pc_crc_generate_batch(mKind, d_rows, bytes + (int)crcBytes(), B, stream));
+        detail::check(pc_crc_generate_batch(mKind, d_rows, bytes, B, stream));
     }
     void check_batch_device(const uint8_t* d_rows, int bytes, uint8_t* d_ok, size_t B, void* stream = nullptr)
     {

@@ -15,6 +15,23 @@ PC_DEC_FASTSSC_I8, PC_DEC_FASTSSC_F32, PC_DEC_SCL_I8, PC_DEC_SCL_F32, PC_DEC_ADA
     PC_DEC_ADAPTIVE_MIXED = range(7)
 PC_OK, PC_ERR_ARG, PC_ERR_CUDA, PC_ERR_UNSUPPORTED = range(4)
 
+FLOAT_LLR_KINDS = (PC_DEC_FASTSSC_F32, PC_DEC_SCL_F32, PC_DEC_ADAPTIVE_F32, PC_DEC_ADAPTIVE_MIXED)
+
+
+def kind_takes_float(kind):
+    """True for the decoder kinds pcsim feeds with float LLRs (simulator.cpp:703-765): the float decoders and
+    AdaptiveMixed, whose list pass needs the unquantised floats (adaptive_mixed.cpp:36-47)"""
+    return int(kind) in FLOAT_LLR_KINDS
+
+
+def pcsim_amplification(kind, ebn0_db, fixed=10.0):
+    """pcsim's LLR scaling (simulator.cpp:370-379, setup.cpp:58): the fixed amplification (default 10) for the int8
+    decoders and for AdaptiveMixed (-p 832), 4 * Eb/N0 (linear) for the float decoders"""
+    if kind_takes_float(kind) and int(kind) != PC_DEC_ADAPTIVE_MIXED:
+        return 4.0 * 10.0 ** (float(ebn0_db) / 10.0)
+    return float(fixed)
+
+
 _vp, _i, _sz, _u64 = ctypes.c_void_p, ctypes.c_int, ctypes.c_size_t, ctypes.c_uint64
 
 # name -> (restype, argtypes); mirrors include/polar_b200.h one to one (tests check the export list)

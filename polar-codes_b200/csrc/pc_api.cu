@@ -28,6 +28,22 @@ int cuda_fail(cudaError_t e, const char* what)
     return PC_ERR_CUDA;
 }
 void count_launch(unsigned long long n) { g_launches += n; }
+int check_code_device(const pc_code* c)
+{
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetDevice");
+    if (dev != c->device)
+        return fail(PC_ERR_ARG, "pc_code was created on CUDA device " + std::to_string(c->device) + " but device " +
+                                    std::to_string(dev) + " is current (one code object per device)");
+    return PC_OK;
+}
+int check_aligned(const void* p, size_t align, const char* what)
+{
+    if (reinterpret_cast<uintptr_t>(p) & (align - 1))
+        return fail(PC_ERR_ARG, std::string(what) + " must be " + std::to_string(align) + "-byte aligned");
+    return PC_OK;
+}
 
 // ---- constant-pool allocator (first fit over kConstWords, shared by all live codes) ---------------
 static std::mutex g_pool_mu;
@@ -401,6 +417,7 @@ int pc_code_set_crc(pc_code* c, int crc_kind)
     if (!c) return fail(PC_ERR_ARG, "null code");
     CrcSpec s;
     if (!crc_spec(crc_kind, s)) return fail(PC_ERR_ARG, "CRC INVALID SIZE!");
+    if (int ds = check_code_device(c)) return ds;
     c->crc_kind = crc_kind;
     c->plan_valid = false;
     c->plan_small_cap = 0;

@@ -52,15 +52,19 @@ __global__ void k_crc_calculate(const uint8_t* data, unsigned long long bits, Cr
     if (threadIdx.x == 0 && blockIdx.x == 0) *out = crc_calculate_bits(crc, data, (size_t)bits);
 }
 
-// shared table cache: one device copy per detector kind
+// shared table cache: one device copy per (device, detector kind)
 static std::mutex g_tab_mu;
-static uint32_t* g_tables[40] = { nullptr };
+constexpr int kMaxDevices = 64;
+static uint32_t* g_tables[kMaxDevices][40] = { { nullptr } };
 
 const uint32_t* crc_table_device(int kind)
 {
     std::lock_guard<std::mutex> lk(g_tab_mu);
     if (kind < 0 || kind >= 40) return nullptr;
-    if (g_tables[kind]) return g_tables[kind];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return nullptr;
+    uint32_t** g_tab = g_tables[dev];
+    if (g_tab[kind]) return g_tab[kind];
     CrcSpec s;
     if (!crc_spec(kind, s)) return nullptr;
     uint32_t h[256];
@@ -71,7 +75,7 @@ const uint32_t* crc_table_device(int kind)
         cudaFree(d);
         return nullptr;
     }
-    g_tables[kind] = d;
+    g_tab[kind] = d;
     return d;
 }
 

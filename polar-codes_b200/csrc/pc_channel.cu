@@ -160,6 +160,8 @@ int pc_awgn_generate(pc_code* c, uint64_t seed, uint64_t first_frame, float ebn0
     if (!c || !d_llr_out || !d_info_out) return fail(PC_ERR_ARG, "null argument");
     if (c->N < 8) return fail(PC_ERR_UNSUPPORTED, "channel generator needs N >= 8");
     if (B == 0) return PC_OK;
+    if (int ds = check_code_device(c)) return ds;
+    if (int ds = check_aligned(d_llr_out, 16, "d_llr_out")) return ds;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int kb = (c->K + 7) / 8, nbytes = c->N / 8;
     int s = ensure_bytes(&c->d_chan_code, &c->chan_code_bytes, (size_t)nbytes * B);

@@ -216,6 +216,9 @@ int encode_device(pc_code* c, const uint8_t* d_info, uint8_t* d_code, uint8_t* d
     if (!c || !d_info || !d_code) return fail(PC_ERR_ARG, "null argument");
     if (B == 0) return PC_OK;
     if (c->N < 8) return fail(PC_ERR_UNSUPPORTED, "encoder needs N >= 8 (the reference's packed container asserts N % 8 == 0)");
+    if (int ds = check_code_device(c)) return ds;
+    if (c->N >= 32)
+        if (int ds = check_aligned(d_code, 4, "d_code")) return ds; // code rows are stored as words
     const int kb = (c->K + 7) / 8;
     CrcSpec crc;
     crc_spec(c->crc_kind, crc);
@@ -253,6 +256,7 @@ int pc_encode_batch_host(pc_code* c, const uint8_t* h_info, uint8_t* h_code, uin
 {
     if (!c || !h_info || !h_code) return fail(PC_ERR_ARG, "null argument");
     if (B == 0) return PC_OK;
+    if (int ds = check_code_device(c)) return ds;
     const size_t kb = (size_t)(c->K + 7) / 8, nb = (size_t)(c->N >= 8 ? c->N / 8 : 1);
     // staging layout: [info B*kb | info+crc B*kb] in d_stage_in, code in d_stage_out
     int s = ensure_bytes(&c->d_stage_in, &c->stage_in_bytes, 2 * kb * B + 16);

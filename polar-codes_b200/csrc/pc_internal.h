@@ -86,6 +86,11 @@ int fail(int status, const std::string& s);
 int cuda_fail(cudaError_t e, const char* what);
 void count_launch(unsigned long long n = 1);
 int ensure_bytes(void** d, size_t* have, size_t need);
+// A pc_code lives on the device that was current at pc_code_create (its tables, constant-pool slice, arenas and
+// streams belong to it): every entry point that takes one checks that this device is current.
+int check_code_device(const pc_code* c);
+// device pointers the kernels access with vector loads / word stores: PC_ERR_ARG instead of a misaligned-address fault
+int check_aligned(const void* p, size_t align, const char* what);
 int crc_generate_rows(int crc_kind, uint8_t* d_data, int bytes, size_t B, cudaStream_t st);
 const uint32_t* crc_table_device(int kind);
 int quantize_device(int N, const float* d_in, int8_t* d_out, size_t B, cudaStream_t st);

@@ -314,7 +314,7 @@ def run_job(job, seed=0x5EED, batch=1 << 18, job_index=0, device=None):
     job.errorDetection, job.errorDetectionType = bits, typ
     dec.setErrorDetection(bits, "crc")
     dec.setSystematic(job.systematic)
-    is_float = kind in (capi.PC_DEC_FASTSSC_F32, capi.PC_DEC_ADAPTIVE_F32, capi.PC_DEC_ADAPTIVE_MIXED)
+    is_float = capi.kind_takes_float(kind)
     N, K, kb = job.N, job.K, (job.K + 7) // 8
     lo, hi = shard_range(job.BlocksToSimulate, rank, world)
     nb = max(1, min(int(batch), hi - lo))

@@ -30,8 +30,11 @@ def reduce_counts(counts):
 
 
 def amplification_for(kind, ebn0_db):
-    """pcsim's LLR scaling (simulator.cpp:370-379, setup.cpp:58): 10.0 for the int8 decoders, 4 * Eb/N0 (linear) for float"""
-    return 10.0 if "char" in kind.lower() else 4.0 * 10.0 ** (ebn0_db / 10.0)
+    """pcsim's LLR scaling for a PC_DEC_* kind (or one of the type strings 'char' / 'float' / 'mixed')"""
+    if isinstance(kind, str):
+        k = kind.lower()
+        kind = capi.PC_DEC_FASTSSC_I8 if "char" in k else capi.PC_DEC_SCL_F32
+    return capi.pcsim_amplification(kind, ebn0_db)
 
 
 def run_sweep(decoder, ebn0_points_db, frames_per_point, seed=0x5EED, batch=1 << 18, rank=0, world=1, device=None,
@@ -41,7 +44,7 @@ def run_sweep(decoder, ebn0_points_db, frames_per_point, seed=0x5EED, batch=1 <<
     dev = torch.device("cuda", torch.cuda.current_device()) if device is None else device
     N, K = decoder.blockLength(), decoder.infoLength()
     kb = (K + 7) // 8
-    is_float = decoder._kind in (capi.PC_DEC_FASTSSC_F32, capi.PC_DEC_SCL_F32, capi.PC_DEC_ADAPTIVE_F32)
+    is_float = capi.kind_takes_float(decoder._kind)
     lo, hi = shard_range(frames_per_point, rank, world)
     nb = max(1, min(batch, hi - lo))
     llr = torch.empty((nb, N), dtype=torch.float32 if is_float else torch.int8, device=dev)
@@ -52,7 +55,7 @@ def run_sweep(decoder, ebn0_points_db, frames_per_point, seed=0x5EED, batch=1 <<
     st = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
     L = lib()
     for p, ebn0 in enumerate(ebn0_points_db):
-        amp = amplification if amplification is not None else (4.0 * 10.0 ** (ebn0 / 10.0) if is_float else 10.0)
+        amp = amplification if amplification is not None else capi.pcsim_amplification(decoder._kind, ebn0)
         f = lo
         while f < hi:
             n = min(nb, hi - f)

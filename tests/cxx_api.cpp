@@ -36,14 +36,15 @@ int cxx_frozen_bits(int N, int K, float dsnr, const char* type, unsigned* out, i
     });
 }
 
-// Detector: generate into data[bytes + crc], then check; mode string out
+// Detector: `bytes` payload bytes followed by the checksum; generate(data, bytes + crc) as in the reference
+// (errordetector.h:52-57: the size includes the checksum, which replaces the last bytes), then check; mode string out
 int cxx_detector(unsigned size, const char* type, unsigned char* data, int bytes, int* check_ok, int* check_corrupt,
                  unsigned long long* calc, char* mode, int* bits)
 {
     return guarded([&] {
         std::unique_ptr<ErrorDetection::Detector> d(ErrorDetection::create(size, type));
         const int cb = (int)((d->getCheckBitCount() + 7) / 8);
-        d->generate(data, bytes);
+        d->generate(data, bytes + cb);
         *check_ok = d->check(data, bytes + cb) ? 1 : 0;
         data[0] ^= 0x10;
         *check_corrupt = d->check(data, bytes + cb) ? 1 : 0;

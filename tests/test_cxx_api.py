@@ -60,6 +60,8 @@ def test_cxx_detector_matches_reference(cxx, ref, size, typ):
         cb = (size + 7) // 8
         exp = ref.crc_generate(size, typ, data[None, :nbytes + cb].copy())[0]
         assert np.array_equal(buf[:nbytes + cb], exp)
+        # canary: generate(data, total) replaces the LAST bytes inside the block and touches nothing behind it
+        assert np.array_equal(buf[nbytes + cb:], data[nbytes + cb:])
         assert okf.value == 1 and (bad.value == 0 or size == 0)
         assert bits.value == size
     # errordetector.cpp:41: std::logic_error("CRC INVALID SIZE!")

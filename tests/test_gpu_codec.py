@@ -106,6 +106,17 @@ def test_detector_kats(pcb):
     assert D(0, "crc").check(t)
     with pytest.raises(ValueError):
         D(7, "crc")
+    # bit-granular calculate(): the 35-bit and 13-bit messages of qa_pypolar_detector.py:310-319,367-376,433-442
+    b35 = np.packbits(np.array([0, 0, 1, 0, 0, 0, 1, 0, 0, 0, 1, 0, 0, 1, 1, 1, 0, 0, 0, 1, 1, 1, 1, 0, 1, 1, 1, 1, 0, 0, 1,
+                                0, 0, 1, 0], dtype=np.uint8))
+    b13 = np.packbits(np.array([1, 0, 1, 1, 1, 1, 0, 1, 0, 0, 0, 1, 0], dtype=np.uint8))
+    assert D(24, "crcnr").calculate(b35, 35) == 0x1FB065 and D(24, "crcnr").calculate(b13, 13) == 0xF70030
+    assert D(6, "crcnr").calculate(b35, 35) == 0x02 and D(6, "crcnr").calculate(b13, 13) == 0x2F
+    assert D(11, "crcnr").calculate(b35, 35) == 0x0608 and D(11, "crcnr").calculate(b13, 13) == 0x06C8
+    # generate(): CRC-6 / CRC-11 occupy whole bytes (:334-365, :392-431)
+    m1, m2 = np.frombuffer(b"123456789", np.uint8), np.frombuffer(b"CommsIsAComplicatedMatter", np.uint8)
+    assert D(6, "crcnr").generate(m1).tolist()[-1:] == [0x15] and D(6, "crcnr").generate(m2).tolist()[-1:] == [0x04]
+    assert D(11, "crcnr").generate(m1).tolist()[-2:] == [0x05, 0xCA] and D(11, "crcnr").generate(m2).tolist()[-2:] == [0x04, 0x4E]
 
 
 @pytest.mark.parametrize("crc_bits,crc_type", CRCS[1:])
