@@ -13,6 +13,8 @@
 
 namespace pc {
 
+void encode2_forget(const pc_code* c); // pc_encode2.cu: drop the code from the encoder's constant-table cache
+
 static thread_local std::string g_err;
 static std::atomic<unsigned long long> g_launches{ 0 };
 
@@ -381,6 +383,7 @@ pc_code* pc_code_create(int N, const unsigned* frozen, int n_frozen, int kind, i
 void pc_code_destroy(pc_code* c)
 {
     if (!c) return;
+    encode2_forget(c);
     if (c->const_code >= 0) pool_free(c->const_code);
     cudaFree(c->d_code);
     cudaFree(c->d_runs);

@@ -9,6 +9,8 @@
 //   stages >= 10  across the R registers of a lane
 // I/O is coalesced: a group reads its info row through shared memory and writes N/8 contiguous bytes.
 // Bit order (reference): element i is bit 7-(i%8) of byte i/8; in registers element i is bit i%32 of word i/32.
+#include <cstdlib>
+
 #include "pc_fastssc_i8_core.h"
 #include "pc_internal.h"
 
@@ -174,8 +176,14 @@ int build_encoder_tables(pc_code* c)
     return e == cudaSuccess ? PC_OK : cuda_fail(e, "encoder tables");
 }
 
+bool encode2_supported(const pc_code* c);
+int encode2_device_raw(pc_code* c, const uint8_t* src, uint8_t* d_code, size_t B, cudaStream_t st);
+
 int encode_device_raw(pc_code* c, const uint8_t* src, uint8_t* d_code, size_t B, cudaStream_t st)
 {
+    // 32 <= N <= 16384: the register-block kernel (pc_encode2.cu); PC_ENC_OLD=1 keeps this file's kernel for measurements
+    static const bool force_old = getenv("PC_ENC_OLD") != nullptr;
+    if (!force_old && encode2_supported(c)) return encode2_device_raw(c, src, d_code, B, st);
     const int kb = (c->K + 7) / 8;
     EncParams p;
     p.info = src;

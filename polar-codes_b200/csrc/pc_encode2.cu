@@ -1,0 +1,307 @@
+// Packed polar encoder, register-block form, for sm_100a (32 <= N <= 32768). Replaces Encoding::ButterflyFipPacked::encode
+// of the reference (src/polarcode/encoding/butterfly_fip_packed.cpp:45-59) for B codewords per launch: scatter the K
+// info bits to the non-frozen positions (PackedContainer::insertPackedInformationBits, src/polarcode/bitcontainer.cpp:
+// 886-898), transform x = u F^(x)n (butterfly_fip.cpp:15-63) and, for systematic codes, zero the frozen positions
+// (resetFrozenBits, bitcontainer.cpp:1004-1010) and transform again.
+//
+// Why a second kernel: k_encode (pc_encode.cu) gives every lane ONE code word, so five of the ten stages of an
+// N = 1024 transform are warp shuffles (three instructions per word and stage) and the bit deposit is a per-lane loop
+// over the runs of the lane's own mask; it measured 8 % of HBM bandwidth for an op whose algorithmic traffic is just
+// K/8 + N/8 bytes per codeword. Here a THREAD owns R = min(N/32, 32) consecutive code words in registers:
+//   * stages 0..4 inside a word: x ^= (x << 2^d) & mask_d on MSB-first words (element i = bit 31 - i%32, i.e. the
+//     byte-swapped memory word), so the shift is a left shift (IMAD.SHL, FMA pipe) next to one LOP3 (ALU pipe);
+//   * stages 5..9 across the thread's registers: one XOR per word pair, no shuffles;
+//   * stages >= 10 (N > 1024): the 32 lanes of a warp hold 32 DIFFERENT codewords and the warps of a group hold the
+//     word blocks, so the exchange is a shared-memory transpose to a second register layout (words r * TPC + t)
+//     in which the top five stages are register XORs again; the butterfly stages commute, so the systematic form
+//     runs  A: 0..9 -> B: 10.. -> mask -> B: 10.. -> A: 0..9  with two transposes;
+//   * the deposit of a word is Hacker's-Delight "expand" with five precomputed move masks per word (five shift +
+//     bit-select pairs, no data-dependent loop); masks and offsets sit in __constant__ memory and are the same for
+//     all lanes of a warp (the word index depends on the register index and the warp only), so they are constant-
+//     bank operands, not loads;
+//   * info rows are staged coalesced into shared memory (byte-swapped on the way), code rows are stored by their
+//     owner thread as whole 32-byte sectors.
+#include <cstring>
+#include <mutex>
+
+#include "pc_fastssc_i8_core.h"
+#include "pc_internal.h"
+
+namespace pc {
+
+constexpr int kEncMaxWords = 512;                  // N <= 16384
+__constant__ uint32_t c_enc[8 * kEncMaxWords];     // per code word: mask, q1, pos, mv[0..4] (see build_table)
+
+struct Enc2Params {
+    const uint8_t* info;  // [B][kb] (check bytes already in place)
+    uint8_t* code;        // [B][N/8]
+    unsigned long long B;
+    int S, kb, kstride;   // kstride: words per staged info row (odd: conflict-free across lanes)
+    int tpc;              // threads (= warps of a group) per codeword, N / (32 R)
+    int systematic;
+    int words_in;         // info rows can be staged word-wise (kb % 4 == 0 and the base is 4-byte aligned)
+    int v8;               // code rows are 32-byte aligned: 256-bit stores
+};
+
+__device__ __forceinline__ uint32_t bswap32(uint32_t x) { return __byte_perm(x, 0, 0x0123); }
+
+// in-word stages on an MSB-first word (element i at bit 31 - i): element i takes element i + 2^d
+__device__ __forceinline__ uint32_t inword_msb(uint32_t x)
+{
+    x ^= (x << 1) & 0xAAAAAAAAu;
+    x ^= (x << 2) & 0xCCCCCCCCu;
+    x ^= (x << 4) & 0xF0F0F0F0u;
+    x ^= (x << 8) & 0xFF00FF00u;
+    x ^= (x << 16);
+    return x;
+}
+
+template <int R>
+__device__ __forceinline__ void stages_inreg(uint32_t (&x)[R], int first_bit)
+{
+    // register-index bit b pairs registers r and r | (1 << b); stages below first_bit were done in the other layout
+#pragma unroll
+    for (int b = 0; (1 << b) < R; ++b) {
+        if (b >= first_bit) {
+#pragma unroll
+            for (int r = 0; r < R; ++r)
+                if (!(r & (1 << b))) x[r] ^= x[r | (1 << b)];
+        }
+    }
+}
+
+// bit j of src goes to the j-th lowest set bit of the mask (Hacker's Delight 7-5, "expand"), move masks precomputed
+__device__ __forceinline__ uint32_t expand32(uint32_t x, const uint32_t* mv, uint32_t m)
+{
+#pragma unroll
+    for (int i = 4; i >= 0; --i) {
+        const uint32_t t = x << (1 << i);
+        x = (x & ~mv[i]) | (t & mv[i]);
+    }
+    return x & m;
+}
+
+template <int R>
+__global__ void __launch_bounds__(512, 2) k_encode2(const __grid_constant__ Enc2Params p)
+{
+    extern __shared__ __align__(16) uint32_t sm[];
+    const int T = blockDim.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int tpc = p.tpc, grp = warp / tpc, t = warp - grp * tpc; // group of tpc warps = 32 codewords; t = word block
+    const int gpc = (T >> 5) / tpc, cpc = 32 * gpc;                // codewords per CTA
+    const int W = R * tpc, Wp = W + 1;                             // words per codeword (+1: conflict-free transposes)
+    uint32_t* s_info = sm;                                         // [cpc][kstride]
+    uint32_t* s_x = sm + (size_t)cpc * p.kstride;                  // [cpc][Wp]   (tpc > 1 only)
+    const int slot = grp * 32 + lane;
+    const int nbytes = 4 * W;
+    int ltpc = 0;
+    while ((1 << ltpc) < tpc) ++ltpc;
+    for (unsigned long long base = (unsigned long long)blockIdx.x * cpc; base < p.B; base += (unsigned long long)gridDim.x * cpc) {
+        const unsigned long long left = p.B - base;
+        const int ncw = left < (unsigned long long)cpc ? (int)left : cpc;
+        const bool live = slot < ncw;
+        // ---- stage the info rows of this batch, byte-swapped so that a word is MSB-first (info bit k = bit 31 - k%32)
+        __syncthreads();
+        if (p.words_in) {
+            const int kw = p.kb >> 2;
+            const uint32_t* src = reinterpret_cast<const uint32_t*>(p.info + base * (unsigned long long)p.kb);
+            for (int i = threadIdx.x; i < ncw * kw; i += T) {
+                const int row = i / kw, q = i - row * kw;
+                s_info[row * p.kstride + q] = bswap32(__ldg(src + i));
+            }
+        } else {
+            const uint8_t* src = p.info + base * (unsigned long long)p.kb;
+            uint8_t* s8 = reinterpret_cast<uint8_t*>(s_info);
+            for (int i = threadIdx.x; i < ncw * p.kb; i += T) {
+                const int row = i / p.kb, b = i - row * p.kb;
+                s8[(size_t)row * 4 * p.kstride + (b ^ 3)] = src[i];
+            }
+        }
+        __syncthreads();
+        const uint32_t* myinfo = s_info + (size_t)(live ? slot : 0) * p.kstride;
+        // ---- deposit: code word w takes the info bits ending at stream bit e - 1, right-aligned, expanded onto its mask
+        uint32_t x[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const uint32_t* E = c_enc + 8 * (t * R + r);
+            const uint32_t m = E[0];
+            uint32_t v = 0;
+            if (m) { // uniform
+                const int q1 = (int)E[1], pos = (int)E[2];
+                const uint32_t lo = myinfo[q1], hi = q1 ? myinfo[q1 - 1] : 0u;
+                v = __funnelshift_r(lo, hi, pos);
+                if (m != 0xFFFFFFFFu) v = expand32(v, E + 3, m);
+            }
+            x[r] = v;
+        }
+        // ---- transform (the stages commute): layout A does stages 0..9, layout B (tpc > 1) stages >= 10
+#pragma unroll
+        for (int r = 0; r < R; ++r) x[r] = inword_msb(x[r]);
+        stages_inreg<R>(x, 0);
+        uint32_t* mine = s_x + (size_t)slot * Wp;
+        if (tpc > 1) {
+            // layout A (words t R + r) -> layout B (words r tpc + t). R == 32 here; register-index bit b in layout B is
+            // word-index bit ltpc + b = stage 5 + ltpc + b, of which stages < 10 (b < 5 - ltpc) were done above.
+            __syncthreads();
+#pragma unroll
+            for (int r = 0; r < R; ++r) mine[t * R + r] = x[r];
+            __syncthreads();
+#pragma unroll
+            for (int r = 0; r < R; ++r) x[r] = mine[r * tpc + t];
+            stages_inreg<R>(x, 5 - ltpc);
+        }
+        if (p.systematic) { // resetFrozenBits, then the second transform starting in the layout we are in
+            if (tpc > 1) {
+#pragma unroll
+                for (int r = 0; r < R; ++r) x[r] &= c_enc[8 * (r * tpc + t)];
+                stages_inreg<R>(x, 5 - ltpc);
+            } else {
+#pragma unroll
+                for (int r = 0; r < R; ++r) x[r] &= c_enc[8 * r];
+            }
+        }
+        if (tpc > 1) { // back to layout A (the owner of 128 contiguous output bytes)
+            __syncthreads();
+#pragma unroll
+            for (int r = 0; r < R; ++r) mine[r * tpc + t] = x[r];
+            __syncthreads();
+#pragma unroll
+            for (int r = 0; r < R; ++r) x[r] = mine[t * R + r];
+        }
+        if (p.systematic) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) x[r] = inword_msb(x[r]);
+            stages_inreg<R>(x, 0);
+        }
+        // ---- store: the thread's R consecutive code words, memory order = byte-swapped MSB-first words
+        if (live) {
+            uint32_t* out = reinterpret_cast<uint32_t*>(p.code + (base + slot) * (unsigned long long)nbytes) + t * R;
+            if (R >= 8 && p.v8) {
+#pragma unroll
+                for (int r = 0; r < R; r += 8)
+                    asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(out + r), "r"(bswap32(x[r])),
+                                 "r"(bswap32(x[r + 1])), "r"(bswap32(x[r + 2])), "r"(bswap32(x[r + 3])), "r"(bswap32(x[r + 4])),
+                                 "r"(bswap32(x[r + 5])), "r"(bswap32(x[r + 6])), "r"(bswap32(x[r + 7]))
+                                 : "memory");
+            } else {
+#pragma unroll
+                for (int r = 0; r < R; ++r) out[r] = bswap32(x[r]);
+            }
+        }
+    }
+}
+
+// ---- host side ---------------------------------------------------------------------------------------------------
+// Table of one code (8 words per code word), in the kernel's MSB-first register convention: mask bit 31 - i is set when
+// element 32 w + i is an information position; q1 / pos locate the last info bit of the word in the byte-swapped info
+// stream (word (e-1) / 32, bit 31 - (e-1) % 32); mv[0..4] are expand's move masks for that mask.
+static void build_table(const pc_code* c, std::vector<uint32_t>& tab)
+{
+    const int W = c->N / 32;
+    tab.assign((size_t)8 * W, 0u);
+    uint32_t e = 0; // info bits up to and including this word
+    for (int w = 0; w < W; ++w) {
+        const uint32_t lsb = c->prog.info_mask[w]; // bit i%32 set for info element i
+        uint32_t m = 0;
+        for (int i = 0; i < 32; ++i)
+            if (lsb & (1u << i)) m |= 1u << (31 - i);
+        e += (uint32_t)__builtin_popcount(m);
+        uint32_t* E = &tab[(size_t)8 * w];
+        E[0] = m;
+        if (!m) continue;
+        E[1] = (e - 1) >> 5;
+        E[2] = 31 - ((e - 1) & 31);
+        uint32_t mm = m, mk = ~m << 1;
+        for (int i = 0; i < 5; ++i) {
+            uint32_t mp = mk ^ (mk << 1);
+            mp ^= mp << 2;
+            mp ^= mp << 4;
+            mp ^= mp << 8;
+            mp ^= mp << 16;
+            const uint32_t mv = mp & mm;
+            E[3 + i] = mv;
+            mm = (mm ^ mv) | (mv >> (1 << i));
+            mk &= ~mp;
+        }
+    }
+}
+
+// the __constant__ table holds ONE code at a time (per device); it is re-uploaded in stream order when another code
+// object (or the same one after a change of its frozen set -- never happens -- ) encodes
+static std::mutex g_enc_mu;
+static const pc_code* g_enc_owner[64] = { nullptr };
+static unsigned long long g_enc_serial[64] = { 0 };
+
+// tpc <= 16 (a group of 16 warps = 512 threads): N <= 16384; longer codes keep k_encode
+bool encode2_supported(const pc_code* c) { return c->N >= 32 && c->N <= 16384; }
+
+void encode2_forget(const pc_code* c)
+{
+    std::lock_guard<std::mutex> lk(g_enc_mu);
+    for (auto& o : g_enc_owner)
+        if (o == c) o = nullptr;
+}
+
+template <int R>
+static cudaError_t launch2(const Enc2Params& p, int grid, int threads, size_t smem, cudaStream_t st)
+{
+    auto kern = k_encode2<R>;
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    kern<<<grid, threads, smem, st>>>(p);
+    return cudaGetLastError();
+}
+
+int encode2_device_raw(pc_code* c, const uint8_t* src, uint8_t* d_code, size_t B, cudaStream_t st)
+{
+    const int W = c->N / 32, R = W < 32 ? W : 32, tpc = W / R;
+    const int kb = (c->K + 7) / 8;
+    {
+        std::lock_guard<std::mutex> lk(g_enc_mu);
+        int dev = c->device;
+        if (dev < 0 || dev >= 64) return fail(PC_ERR_UNSUPPORTED, "device index out of range for the encoder table");
+        if (g_enc_owner[dev] != c) {
+            std::vector<uint32_t> tab;
+            build_table(c, tab);
+            // another code's encode kernels (on any stream) may still be reading the table: drain the device first.
+            // Switches are rare (a process usually encodes with one code); a code that keeps the table pays nothing.
+            cudaError_t e = cudaDeviceSynchronize();
+            if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_enc, tab.data(), tab.size() * 4, 0, cudaMemcpyHostToDevice);
+            if (e != cudaSuccess) return cuda_fail(e, "encoder table upload");
+            g_enc_owner[dev] = c;
+            g_enc_serial[dev]++;
+        }
+    }
+    Enc2Params p;
+    p.info = src;
+    p.code = d_code;
+    p.B = B;
+    p.S = c->S;
+    p.kb = kb;
+    p.kstride = ((kb + 3) / 4) | 1;
+    p.tpc = tpc;
+    p.systematic = c->systematic;
+    p.words_in = (kb % 4 == 0 && (reinterpret_cast<uintptr_t>(src) & 3u) == 0) ? 1 : 0;
+    p.v8 = ((reinterpret_cast<uintptr_t>(d_code) & 31u) == 0 && (4 * R) % 32 == 0) ? 1 : 0;
+    // CTA: whole groups of tpc warps (32 codewords each); 256 threads for short codes, 512 when a group needs them
+    int threads = tpc <= 8 ? 256 : 32 * tpc;
+    const int gpc = (threads / 32) / tpc, cpc = 32 * gpc;
+    const size_t smem = 4 * ((size_t)cpc * p.kstride + (tpc > 1 ? (size_t)cpc * (W + 1) : 0));
+    size_t ctas = (B + cpc - 1) / cpc;
+    const int grid = (int)(ctas < 148 * 8 ? ctas : 148 * 8);
+    cudaError_t e;
+    switch (R) {
+    case 1: e = launch2<1>(p, grid, threads, smem, st); break;
+    case 2: e = launch2<2>(p, grid, threads, smem, st); break;
+    case 4: e = launch2<4>(p, grid, threads, smem, st); break;
+    case 8: e = launch2<8>(p, grid, threads, smem, st); break;
+    case 16: e = launch2<16>(p, grid, threads, smem, st); break;
+    default: e = launch2<32>(p, grid, threads, smem, st); break;
+    }
+    if (e != cudaSuccess) return cuda_fail(e, "encode2 launch");
+    count_launch();
+    return PC_OK;
+}
+
+} // namespace pc

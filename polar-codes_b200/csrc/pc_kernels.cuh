@@ -56,6 +56,10 @@ struct SclParams {
     int arena_words;  // arena words per lane (LLR stages whose llr_off carries the arena flag)
     size_t arena_stride; // lanes the arena rows are laid out for (grid * threads)
     uint32_t* arena;
+    // tensor memory as private storage for the decision words of the large stages (offsets carry kTmem)
+    int tm_alloc_cols;   // tcgen05.alloc size of one CTA (0: unused)
+    int tm_cols_thread;  // columns per thread (warps sharing a lane quarter are stacked along columns)
+    int scr_off;         // smem word offset of a per-lane scratch of N/32 words for extractBestPath
 };
 
 struct SclLaunch {

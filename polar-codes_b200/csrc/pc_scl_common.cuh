@@ -15,6 +15,13 @@ namespace pc {
 // word offsets with this bit set address the lane's rows of the L2/HBM arena instead of shared memory: the largest LLR
 // stages (so that more codewords fit one SM) and, for long codes, the decision words of the largest stages
 constexpr int kArena = 1 << 30;
+// word offsets with this bit set are COLUMNS of the lane's tensor-memory slice (decision words of the large stages):
+// tcgen05.ld/st 32x32b can only reach the executing thread's own lane, so a read through the owner table is a load of
+// the same column by every lane followed by a warp shuffle from the owner. Both are warp-collective: every function
+// that touches decision words is executed by ALL lanes (dead lanes compute into their own, unreferenced buffers).
+constexpr int kTmem = 1 << 29;
+// bit modes of a kernel instantiation: which flags the decision-word accessors test
+enum : int { BM_SMEM = 0, BM_ARENA = 1, BM_TMEM = 2 };
 
 struct Tbl { // 5-bit owner lane per stage
     uint32_t w[3];
@@ -230,36 +237,35 @@ __device__ __forceinline__ void set_side(LN& c, int s, int side)
 template <class LN, class PR>
 __device__ __forceinline__ void scl_comb(LN& c, const PR& p, int s, int side)
 {
-    const bool active = c.l < c.P;
+    // executed by every lane, live or not (see kTmem): a dead lane combines whatever its tables point at into its own
+    // buffers, which no path references
     const int h = 1 << (s - 1);
     const uint32_t ol = c.own_L.get(s - 1), orr = c.own_R.get(s - 1);
     const int lo = p.bitL_off[s - 1], ro = p.bitR_off[s - 1], dst = side ? p.bitR_off[s] : p.bitL_off[s];
-    if (active) {
-        if (h >= 32) {
-            const int hw = h >> 5;
-            if (hw >= 4) {
-                for (int j = 0; j < hw; j += 4) { // loads first: the stores may alias them as far as the compiler knows
-                    uint32_t a[4], b[4];
+    if (h >= 32) {
+        const int hw = h >> 5;
+        if (hw >= 4) {
+            for (int j = 0; j < hw; j += 4) { // loads first: the stores may alias them as far as the compiler knows
+                uint32_t a[4], b[4];
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) a[u] = c.ld(lo + j + u, ol), b[u] = c.ld(ro + j + u, orr);
+                for (int u = 0; u < 4; ++u) a[u] = c.ld(lo + j + u, ol), b[u] = c.ld(ro + j + u, orr);
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) {
-                        c.st(dst + j + u, a[u] ^ b[u]);
-                        c.st(dst + hw + j + u, b[u]);
-                    }
-                }
-            } else {
-                for (int j = 0; j < hw; ++j) {
-                    const uint32_t a = c.ld(lo + j, ol), b = c.ld(ro + j, orr);
-                    c.st(dst + j, a ^ b);
-                    c.st(dst + hw + j, b);
+                for (int u = 0; u < 4; ++u) {
+                    c.st(dst + j + u, a[u] ^ b[u]);
+                    c.st(dst + hw + j + u, b[u]);
                 }
             }
         } else {
-            const uint32_t m = (1u << h) - 1u;
-            const uint32_t a = c.ld(lo, ol) & m, b = c.ld(ro, orr) & m;
-            c.st(dst, (a ^ b) | (b << h));
+            for (int j = 0; j < hw; ++j) {
+                const uint32_t a = c.ld(lo + j, ol), b = c.ld(ro + j, orr);
+                c.st(dst + j, a ^ b);
+                c.st(dst + hw + j, b);
+            }
         }
+    } else {
+        const uint32_t m = (1u << h) - 1u;
+        const uint32_t a = c.ld(lo, ol) & m, b = c.ld(ro, orr) & m;
+        c.st(dst, (a ^ b) | (b << h));
     }
     set_side(c, s, side);
 }
@@ -270,6 +276,9 @@ template <class LN, class PR>
 __device__ __forceinline__ void scl_take_bits(const LN& c, const PR& p, int s, int side, int sp, bool live, int fmask,
                                               const int (&fi)[4])
 {
+    // every lane stores (a dead lane copies path 0's words into its own unreferenced buffer): the tensor-memory store
+    // is warp-collective
+    (void)live;
     const int nb = stage_bwords(s), dst = side ? p.bitR_off[s] : p.bitL_off[s];
     for (int w = 0; w < nb; ++w) {
         uint32_t t = c.ld(dst + w, (uint32_t)sp);
@@ -277,7 +286,7 @@ __device__ __forceinline__ void scl_take_bits(const LN& c, const PR& p, int s, i
         for (int q = 0; q < 4; ++q)
             if (((fmask >> q) & 1) && (fi[q] >> 5) == w) t ^= 1u << (fi[q] & 31);
         __syncwarp();
-        if (live) c.st(dst + w, t);
+        c.st(dst + w, t);
     }
     __syncwarp();
 }

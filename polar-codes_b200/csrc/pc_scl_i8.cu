@@ -28,24 +28,35 @@
 
 namespace pc {
 
-template <bool BA> // BA: some decision words live in the arena (long codes); off = no flag tests
+template <int BM> // BM: BM_ARENA some decision words live in the arena (long codes), BM_TMEM in tensor memory; 0 = no flag tests
 struct LaneT {
     uint32_t* sm;   // smem base + tid (word w at sm[w * T])
     uint32_t* ar;   // arena base + global lane id (word w at ar[w * AS])
     size_t AS;
+    uint32_t tm;    // tensor-memory address of this thread's column 0 (lane quarter of its warp + column base)
     int T, G, l;    // threads per CTA, lanes per group, lane index inside the group
     int P;          // live paths (uniform)
     int metric;     // path metric (the reference uses long; |metric| <= 128 N fits easily)
     Tbl own_llr, own_L, own_R;
-    // decision words: shared memory, or the arena for the largest stages of long codes (flag in the offset)
+    // decision words: shared memory, tensor memory (warp-collective: called by all 32 lanes with the same word), or
+    // the arena for the largest stages of long codes (flag in the offset)
     __device__ __forceinline__ uint32_t ld(int word, uint32_t owner) const
     {
-        if (BA && (word & kArena)) return ar[(size_t)(word & (kArena - 1)) * AS + ((int)owner - l)];
+        if ((BM & BM_TMEM) && (word & kTmem)) {
+            uint32_t v;
+            tm_ld1_nowait(tm + (uint32_t)(word & 0xFFFF), v);
+            tm_wait_ld();
+            return __shfl_sync(0xFFFFFFFFu, v, (int)owner, G);
+        }
+        if ((BM & BM_ARENA) && (word & kArena)) return ar[(size_t)(word & (kArena - 1)) * AS + ((int)owner - l)];
         return sm[(size_t)word * T + ((int)owner - l)];
     }
     __device__ __forceinline__ void st(int word, uint32_t v) const
     {
-        if (BA && (word & kArena))
+        if ((BM & BM_TMEM) && (word & kTmem)) {
+            tm_st1(tm + (uint32_t)(word & 0xFFFF), v);
+            tm_wait_st();
+        } else if ((BM & BM_ARENA) && (word & kArena))
             ar[(size_t)(word & (kArena - 1)) * AS] = v;
         else
             sm[(size_t)word * T] = v;
@@ -73,6 +84,9 @@ __device__ __forceinline__ uint32_t bytemask(int nbytes) { return nbytes >= 4 ? 
 template <bool IS_G, class Lane>
 __device__ __forceinline__ void scl_fg(Lane& c, const SclParams& p, int s, const int8_t* row)
 {
+    // Every lane runs the step (the decision-word reads may be warp-collective tensor-memory loads): a dead lane
+    // reads through its (valid, copied) tables -- the same addresses as the path it was copied from, so no extra
+    // traffic -- and only its stores are suppressed.
     const bool active = c.l < c.P;
     const int h = 1 << (s - 1);
     const uint32_t* grow = reinterpret_cast<const uint32_t*>(row);
@@ -80,60 +94,62 @@ __device__ __forceinline__ void scl_fg(Lane& c, const SclParams& p, int s, const
     const uint32_t o = c.own_llr.get(s), ol = c.own_L.get(s - 1);
     const int lb = p.bitL_off[s - 1];
     const typename Lane::View src = c.view(from_row ? p.llr_off[s - 1] : p.llr_off[s], o), dst = c.view(p.llr_off[s - 1], (uint32_t)c.l);
-    if (active) {
-        if (h >= 16) {
-            // four words per step: all loads first (source and destination may alias as far as the compiler knows, so
-            // a rolled loop serialises load -> f/g -> store), the channel row as 16-byte loads
-            const int hw = h >> 2;
-            const bool row16 = from_row && ((reinterpret_cast<uintptr_t>(row) & 15u) == 0);
-            for (int j = 0; j < hw; j += 4) {
-                uint32_t a[4], b[4], r[4];
-                if (row16) {
-                    const uint4 va = __ldg(reinterpret_cast<const uint4*>(grow + j)), vb = __ldg(reinterpret_cast<const uint4*>(grow + hw + j));
-                    a[0] = va.x, a[1] = va.y, a[2] = va.z, a[3] = va.w;
-                    b[0] = vb.x, b[1] = vb.y, b[2] = vb.z, b[3] = vb.w;
-                } else {
+    if (h >= 16) {
+        // four words per step: all loads first (source and destination may alias as far as the compiler knows, so
+        // a rolled loop serialises load -> f/g -> store), the channel row as 16-byte loads
+        const int hw = h >> 2;
+        const bool row16 = from_row && ((reinterpret_cast<uintptr_t>(row) & 15u) == 0);
+        uint32_t bword = 0;
+        for (int j = 0; j < hw; j += 4) {
+            uint32_t a[4], b[4], r[4];
+            if (row16) {
+                const uint4 va = __ldg(reinterpret_cast<const uint4*>(grow + j)), vb = __ldg(reinterpret_cast<const uint4*>(grow + hw + j));
+                a[0] = va.x, a[1] = va.y, a[2] = va.z, a[3] = va.w;
+                b[0] = vb.x, b[1] = vb.y, b[2] = vb.z, b[3] = vb.w;
+            } else {
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) {
-                        a[u] = from_row ? __ldg(grow + j + u) : src[j + u];
-                        b[u] = from_row ? __ldg(grow + hw + j + u) : src[hw + j + u];
-                    }
+                for (int u = 0; u < 4; ++u) {
+                    a[u] = from_row ? __ldg(grow + j + u) : src[j + u];
+                    b[u] = from_row ? __ldg(grow + hw + j + u) : src[hw + j + u];
                 }
-                if (IS_G) {
-                    const uint32_t bw = c.ld(lb + (j >> 3), ol) >> (4 * (j & 7));
+            }
+            if (IS_G) {
+                if ((j & 7) == 0) bword = c.ld(lb + (j >> 3), ol); // one decision word covers eight LLR words
+                const uint32_t bw = bword >> (4 * (j & 7));
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) r[u] = sw_g(a[u], b[u], sw_expand4(bw >> (4 * u)));
-                } else {
+                for (int u = 0; u < 4; ++u) r[u] = sw_g(a[u], b[u], sw_expand4(bw >> (4 * u)));
+            } else {
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) r[u] = sw_f(a[u], b[u]);
-                }
+                for (int u = 0; u < 4; ++u) r[u] = sw_f(a[u], b[u]);
+            }
+            if (active) {
 #pragma unroll
                 for (int u = 0; u < 4; ++u) dst.set(j + u, r[u]);
             }
-        } else if (h >= 4) {
-            const int hw = h >> 2;
-            for (int j = 0; j < hw; ++j) {
-                const uint32_t a = from_row ? __ldg(grow + j) : src[j];
-                const uint32_t b = from_row ? __ldg(grow + hw + j) : src[hw + j];
-                uint32_t r;
-                if (IS_G) {
-                    const uint32_t bw = c.ld(lb + (j >> 3), ol);
-                    r = sw_g(a, b, sw_expand4(bw >> (4 * (j & 7))));
-                } else {
-                    r = sw_f(a, b);
-                }
-                dst.set(j, r);
-            }
-        } else {
-            const uint32_t w = from_row ? __ldg(grow) : src[0];
-            const uint32_t hi = w >> (8 * h);
+        }
+    } else if (h >= 4) {
+        const int hw = h >> 2;
+        uint32_t bword = 0;
+        if (IS_G) bword = c.ld(lb, ol); // h <= 8: at most two LLR words, one decision word
+        for (int j = 0; j < hw; ++j) {
+            const uint32_t a = from_row ? __ldg(grow + j) : src[j];
+            const uint32_t b = from_row ? __ldg(grow + hw + j) : src[hw + j];
             uint32_t r;
             if (IS_G)
-                r = sw_g(w, hi, sw_expand4(c.ld(lb, ol)));
+                r = sw_g(a, b, sw_expand4(bword >> (4 * (j & 7))));
             else
-                r = sw_f(w, hi);
-            dst.set(0, r & bytemask(h));
+                r = sw_f(a, b);
+            if (active) dst.set(j, r);
         }
+    } else {
+        const uint32_t w = from_row ? __ldg(grow) : src[0];
+        const uint32_t hi = w >> (8 * h);
+        uint32_t r;
+        if (IS_G)
+            r = sw_g(w, hi, sw_expand4(c.ld(lb, ol)));
+        else
+            r = sw_f(w, hi);
+        if (active) dst.set(0, r & bytemask(h));
     }
     c.own_llr.set(s - 1, (uint32_t)c.l);
 }
@@ -177,13 +193,11 @@ __device__ __forceinline__ void llr_sums(const Lane& c, const SclParams& p, int 
 template <class Lane>
 __device__ __forceinline__ void scl_r0(Lane& c, const SclParams& p, int s, int side)
 {
-    if (c.l < c.P) {
-        int neg, pos;
-        llr_sums(c, p, s, neg, pos);
-        c.metric += neg;
-        const int dst = side ? p.bitR_off[s] : p.bitL_off[s], nb = stage_bwords(s);
-        for (int j = 0; j < nb; ++j) c.st(dst + j, 0u);
-    }
+    int neg, pos; // every lane runs (dead lanes: garbage into their own state, replaced at the next fork)
+    llr_sums(c, p, s, neg, pos);
+    c.metric += neg;
+    const int dst = side ? p.bitR_off[s] : p.bitL_off[s], nb = stage_bwords(s);
+    for (int j = 0; j < nb; ++j) c.st(dst + j, 0u);
     set_side(c, s, side);
 }
 
@@ -310,9 +324,9 @@ template <class Lane>
 __device__ __forceinline__ void scl_rep(Lane& c, const SclParams& p, int s, int side)
 {
     int v[2] = { INT_MIN, INT_MIN };
+    int neg, pos;
+    llr_sums(c, p, s, neg, pos);
     if (c.l < c.P) {
-        int neg, pos;
-        llr_sums(c, p, s, neg, pos);
         v[0] = c.metric + neg;
         v[1] = c.metric - pos;
     }
@@ -322,11 +336,9 @@ __device__ __forceinline__ void scl_rep(Lane& c, const SclParams& p, int s, int 
     const bool live = c.l < newP;
     const int sp = live ? idx >> 1 : 0;
     scl_fork(c, sp, val, newP);
-    if (live) {
-        const int dst = side ? p.bitR_off[s] : p.bitL_off[s], nb = stage_bwords(s);
-        const uint32_t fill = (idx & 1) ? 0xFFFFFFFFu : 0u;
-        for (int j = 0; j < nb; ++j) c.st(dst + j, fill);
-    }
+    const int dst = side ? p.bitR_off[s] : p.bitL_off[s], nb = stage_bwords(s);
+    const uint32_t fill = (idx & 1) ? 0xFFFFFFFFu : 0u;
+    for (int j = 0; j < nb; ++j) c.st(dst + j, fill); // all lanes (tensor-memory stores are warp-collective)
     set_side(c, s, side);
 }
 
@@ -336,9 +348,9 @@ __device__ __forceinline__ void scl_r1(Lane& c, const SclParams& p, int s, int s
 {
     int v[4] = { INT_MIN, INT_MIN, INT_MIN, INT_MIN };
     int wi[4] = { 0, 0, 0, 0 }, wv[4];
+    scl_signs_and_abs(c, p, s, side);
+    scl_find_weak(c, p.llr_off[s], 1 << s, 2, wi, wv);
     if (c.l < c.P) {
-        scl_signs_and_abs(c, p, s, side);
-        scl_find_weak(c, p.llr_off[s], 1 << s, 2, wi, wv);
         v[0] = c.metric;
         v[1] = c.metric - wv[0];
         v[2] = c.metric - wv[1];
@@ -368,11 +380,10 @@ __device__ __forceinline__ void scl_spc(Lane& c, const SclParams& p, int s, int 
 #pragma unroll
     for (int k = 0; k < 8; ++k) v[k] = INT_MIN;
     int wi[4] = { 0, 0, 0, 0 }, wv[4];
-    int parity = 0;
+    const uint32_t par = scl_signs_and_abs(c, p, s, side);
+    const int parity = (int)parity_of_msbs(par);
+    scl_find_weak(c, p.llr_off[s], 1 << s, 4, wi, wv);
     if (c.l < c.P) {
-        const uint32_t par = scl_signs_and_abs(c, p, s, side);
-        parity = (int)parity_of_msbs(par);
-        scl_find_weak(c, p.llr_off[s], 1 << s, 4, wi, wv);
         int m = c.metric, weakest = 0;
         if (parity)
             m -= wv[0];
@@ -404,20 +415,33 @@ __device__ __forceinline__ void scl_spc(Lane& c, const SclParams& p, int s, int 
     set_side(c, s, side);
 }
 
-template <bool BA>
-__global__ void __launch_bounds__(256) k_scl_i8(const __grid_constant__ SclParams p)
+template <int BM>
+__global__ void __launch_bounds__(256, 2) k_scl_i8(const __grid_constant__ SclParams p)
 {
-    using Lane = LaneT<BA>;
+    using Lane = LaneT<BM>;
     extern __shared__ __align__(16) uint32_t smem[];
-    const int T = blockDim.x, t = threadIdx.x;
+    __shared__ uint32_t tm_base_s;
+    const int T = blockDim.x, t = threadIdx.x, warp = t >> 5;
     uint32_t* crc_table = smem; // 256 words
     if (p.crc.width)
         for (int i = t; i < 256; i += T) crc_table[i] = p.crc_table[i];
+    if (BM & BM_TMEM) {
+        if (warp == 0) {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                             (uint32_t)__cvta_generic_to_shared(&tm_base_s)),
+                         "r"((uint32_t)p.tm_alloc_cols));
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;");
+    }
     __syncthreads();
+    if (BM & BM_TMEM) asm volatile("tcgen05.fence::after_thread_sync;");
     Lane c;
     c.sm = smem + 256 + t;
     c.ar = p.arena + ((size_t)blockIdx.x * T + t);
     c.AS = p.arena_stride;
+    // a warp reaches the 32 tensor-memory lanes of its quarter (warp % 4); warps sharing a quarter are stacked along columns
+    c.tm = (BM & BM_TMEM) ? tm_base_s + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)((warp >> 2) * p.tm_cols_thread) : 0u;
     c.T = T;
     c.G = p.G;
     c.l = t & (p.G - 1);
@@ -425,8 +449,7 @@ __global__ void __launch_bounds__(256) k_scl_i8(const __grid_constant__ SclParam
     const int N = 1 << p.S, kb = (p.K + 7) >> 3;
     const unsigned gmask = (p.G == 32 ? 0xFFFFFFFFu : ((1u << p.G) - 1u)) << ((t & 31) & ~(p.G - 1));
     const unsigned long long nfr = p.count ? *p.count : p.B;
-    if (nfr == 0) return;
-    const unsigned long long nbatch = (nfr + gpc - 1) / gpc;
+    const unsigned long long nbatch = (nfr + gpc - 1) / gpc; // 0 when there is nothing to do: straight to the dealloc
     for (unsigned long long bi = blockIdx.x; bi < nbatch; bi += gridDim.x) {
         const unsigned long long fl = bi * gpc + (unsigned long long)(t / p.G);
         const bool live_frame = fl < nfr;
@@ -469,25 +492,27 @@ __global__ void __launch_bounds__(256) k_scl_i8(const __grid_constant__ SclParam
         const int top = p.bitR_off[p.S], nbw = stage_bwords(p.S);
         uint32_t owner = c.own_R.get(p.S);
         int off = top;
-        if (!p.systematic) {
-            // u = x F^(x)n on a private copy (the left buffer of the top stage is free at this point)
-            const int scr = p.bitL_off[p.S];
-            if (active) {
-                const uint32_t lim = lowmask(1 << (p.S < 5 ? p.S : 5));
-                for (int w = 0; w < nbw; ++w) {
-                    uint32_t x = c.ld(top + w, owner);
+        if (!p.systematic || (top & kTmem)) {
+            // private copy of the path's decisions in the lane's shared-memory scratch (every lane: the reads may be
+            // warp-collective); non-systematic: u = x F^(x)n on that copy
+            const int scr = p.scr_off;
+            const uint32_t lim = lowmask(1 << (p.S < 5 ? p.S : 5));
+            for (int w = 0; w < nbw; ++w) {
+                uint32_t x = c.ld(top + w, owner);
+                if (!p.systematic) {
                     x ^= (x >> 1) & 0x55555555u & lim;
                     if (p.S > 1) x ^= (x >> 2) & 0x33333333u & lim;
                     if (p.S > 2) x ^= (x >> 4) & 0x0F0F0F0Fu & lim;
                     if (p.S > 3) x ^= (x >> 8) & 0x00FF00FFu & lim;
                     if (p.S > 4) x ^= (x >> 16) & 0x0000FFFFu;
-                    c.st(scr + w, x);
                 }
+                c.st(scr + w, x);
+            }
+            if (!p.systematic)
                 for (int d = 1; d < nbw; d <<= 1)
                     for (int g = 0; g < nbw; g += 2 * d)
                         for (int i = g; i < g + d; ++i)
                             c.st(scr + i, c.ld(scr + i, (uint32_t)c.l) ^ c.ld(scr + i + d, (uint32_t)c.l));
-            }
             owner = (uint32_t)c.l;
             off = scr;
         }
@@ -503,6 +528,12 @@ __global__ void __launch_bounds__(256) k_scl_i8(const __grid_constant__ SclParam
         }
         __syncwarp();
     }
+    if (BM & BM_TMEM) {
+        asm volatile("tcgen05.fence::before_thread_sync;");
+        __syncthreads();
+        if (warp == 0)
+            asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tm_base_s), "r"((uint32_t)p.tm_alloc_cols));
+    }
 }
 
 cudaError_t launch_scl_i8(const SclLaunch& L, const int8_t* d_llr, uint8_t* d_info, uint8_t* d_ok, size_t B,
@@ -515,20 +546,26 @@ cudaError_t launch_scl_i8(const SclLaunch& L, const int8_t* d_llr, uint8_t* d_in
     p.B = B;
     p.frame_idx = d_frame_idx;
     p.count = d_count;
-    // decision words in the arena (long codes) -> the instantiation whose ld / st test the offset flag
+    // decision words in the arena (long codes) or in tensor memory -> the instantiation whose ld / st test that flag
     const bool ba = (p.bitR_off[p.S] & kArena) != 0;
-    void (*kern)(SclParams) = ba ? k_scl_i8<true> : k_scl_i8<false>;
+    void (*kern)(SclParams) = p.tm_alloc_cols ? k_scl_i8<BM_TMEM> : (ba ? k_scl_i8<BM_ARENA> : k_scl_i8<BM_SMEM>);
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes);
     // several CTAs per SM only fit when the L1/shared split is at its shared-memory maximum; a single CTA keeps the
     // default split (the rest stays L1 for the channel rows and the arena)
-    if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                 L.per_sm > 1 ? (int)cudaSharedmemCarveoutMaxShared : (int)cudaSharedmemCarveoutDefault);
+    // (the tensor-memory plan needs less shared memory: ask for what its CTAs use, the rest stays L1)
+    int carve = L.per_sm > 1 ? (int)cudaSharedmemCarveoutMaxShared : (int)cudaSharedmemCarveoutDefault;
+    if (p.tm_alloc_cols) {
+        carve = (int)(((size_t)L.per_sm * (L.smem_bytes + 1024) * 100 + 233471) / 233472) + 3;
+        if (carve > 100) carve = 100;
+    }
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
     if (e != cudaSuccess) return e;
-    if (getenv("PC_DEBUG_OCC")) {
+    static const bool debug_occ = getenv("PC_DEBUG_OCC") != nullptr;
+    if (debug_occ) {
         int occ = 0;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, L.threads, L.smem_bytes);
-        fprintf(stderr, "k_scl_i8: %d threads, %zu B smem, grid %d, occupancy %d CTAs/SM\n", L.threads, L.smem_bytes, L.grid, occ);
+        fprintf(stderr, "k_scl_i8: %d threads, %zu B smem, grid %d, tmem cols %d, occupancy %d CTAs/SM\n", L.threads, L.smem_bytes,
+                L.grid, p.tm_alloc_cols, occ);
     }
     const int gpc = L.threads / p.G;
     size_t nb = (B + gpc - 1) / gpc;
@@ -537,8 +574,8 @@ cudaError_t launch_scl_i8(const SclLaunch& L, const int8_t* d_llr, uint8_t* d_in
     return cudaGetLastError();
 }
 
-// host planner: per-lane word layout and CTA size
-int plan_scl_i8(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, SclLaunch& out, const char** msg)
+// host planner without tensor memory: per-lane word layout and CTA size
+static int plan_scl_i8_smem(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, SclLaunch& out, const char** msg)
 {
     if (L < 1 || L > 32) {
         *msg = "list size must be in [1, 32]";
@@ -633,6 +670,9 @@ int plan_scl_i8(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, S
     }
     p.words = w;
     p.arena_words = aw;
+    p.tm_alloc_cols = 0;
+    p.tm_cols_thread = 0;
+    p.scr_off = p.bitL_off[S]; // non-systematic extraction works on the (free) left buffer of the top stage
     out.threads = T;
     out.smem_bytes = 1024 + 4 * (size_t)w * T;
     out.grid = sms * per_sm;
@@ -643,6 +683,97 @@ int plan_scl_i8(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, S
         return 1;
     }
     return 0;
+}
+
+// Planner, first choice: 2 CTAs of 256 lanes per SM (16 warps; 128 registers per thread is the register file's limit)
+// with the decision words of the large stages in TENSOR MEMORY. The kernel is bound by dependent integer chains
+// (ncu r01/r02: issue slots 37 % busy with 2 warps per scheduler, top stall `wait`), so resident warps decide its
+// throughput, and shared memory alone holds only 256 lanes of path state (about 200 words per lane at N = 1024).
+// Tensor memory gives every lane 128 more columns: decision buffers descending from the top stage go there while
+// they fit, the rest (and the LLR stages, ascending, while they fit) to shared memory, the largest LLR stages to the
+// L2-resident arena as before. Falls back to plan_scl_i8_smem when the code is too long for this shape (decision
+// words needed in the arena) or on request (PC_SCL_NOTMEM=1, PC_SCL_LANES).
+int plan_scl_i8(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, SclLaunch& out, const char** msg)
+{
+    if (L < 1 || L > 32) {
+        *msg = "list size must be in [1, 32]";
+        return 1;
+    }
+    const bool no_tmem = getenv("PC_SCL_NOTMEM") != nullptr || getenv("PC_SCL_LANES") != nullptr;
+    int G = 1;
+    while (G < L) G <<= 1;
+    const int T = 256, per_sm = 2, tm_alloc = 256, tm_cols = tm_alloc / ((T / 32 + 3) / 4); // 128 columns per thread
+    const int top_llr = root_leaf ? S : S - 1;
+    if (!no_tmem && S >= 6 && S <= 15) {
+        size_t per_cta = 233472 / (size_t)per_sm - 1024;
+        if (per_cta > smem_max) per_cta = smem_max;
+        const long budget = ((long)per_cta - 1024 - 64) / (4L * T); // shared-memory words per lane
+        SclParams& p = out.p;
+        for (int s = 0; s < 20; ++s) p.llr_off[s] = p.bitL_off[s] = p.bitR_off[s] = 0;
+        // decision buffers, top stage first, into tensor memory while they fit
+        int tcol = 0, tm_lo = S + 1;
+        for (int s = S; s >= 6; --s) {
+            const int bw = 1 << (s - 5);
+            if (tcol + 2 * bw > tm_cols) break;
+            p.bitL_off[s] = kTmem | tcol;
+            tcol += bw;
+            p.bitR_off[s] = kTmem | tcol;
+            tcol += bw;
+            tm_lo = s;
+        }
+        int w = 0;
+        for (int s = 0; s < tm_lo; ++s) {
+            const int bw = s >= 5 ? (1 << (s - 5)) : 1;
+            p.bitL_off[s] = w;
+            w += bw;
+            p.bitR_off[s] = w;
+            w += bw;
+        }
+        int aw = 0, smem_top = -1;
+        bool open = true;
+        for (int s = 0; s <= top_llr; ++s) {
+            const int sw = s >= 2 ? (1 << (s - 2)) : 1;
+            if (open && w + sw <= budget) {
+                p.llr_off[s] = w;
+                w += sw;
+                smem_top = s;
+            } else {
+                open = false;
+                p.llr_off[s] = kArena | aw;
+                aw += sw;
+            }
+        }
+        // scratch of N/32 words for extractBestPath: the (dead by then) LLR stage S-3 has exactly that size
+        const int nbw = 1 << (S - 5);
+        int scr = -1;
+        if (S - 3 >= 2 && S - 3 <= smem_top) {
+            scr = p.llr_off[S - 3];
+        } else if (w + nbw <= budget) {
+            scr = w;
+            w += nbw;
+        }
+        const bool fits = w <= budget && tm_lo <= S && scr >= 0 && smem_top >= (top_llr < 6 ? top_llr : 6) &&
+                          (unsigned long long)aw * ((unsigned long long)sms * per_sm * T) < (1ull << 32);
+        if (fits) {
+            p.S = S;
+            p.K = K;
+            p.L = L;
+            p.G = G;
+            p.root_leaf = root_leaf ? 1 : 0;
+            p.words = w;
+            p.arena_words = aw;
+            p.tm_alloc_cols = tm_alloc;
+            p.tm_cols_thread = tm_cols;
+            p.scr_off = scr;
+            out.threads = T;
+            out.smem_bytes = 1024 + 4 * (size_t)w * T;
+            out.grid = sms * per_sm;
+            out.per_sm = per_sm;
+            p.arena_stride = (size_t)out.grid * T;
+            return 0;
+        }
+    }
+    return plan_scl_i8_smem(S, K, L, root_leaf, smem_max, sms, out, msg);
 }
 
 } // namespace pc
