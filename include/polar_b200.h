@@ -82,8 +82,10 @@ const char* pc_version(void);
 
 /* host-only: frozen set for (N, K) by "BB" (Bhattacharyya, design SNR in dB) or "BE" (beta expansion), the
  * substring match of Construction::frozen_bits (constructor.cpp:41-63); writes N-K sorted indices to out
- * (capacity N), returns N-K or a negative status. "5G" (FiveGList, the 3GPP reliability table) is recognised and
- * refused with PC_ERR_UNSUPPORTED: the table is not vendored into this library. */
+ * (capacity N), returns N-K or a negative status. "5G" (FiveGList, fiveGList.cpp:30-43): the N-K least reliable
+ * positions of the 3GPP TS 38.212 polar sequence restricted to indices < N -- identical to the reference for N = 1024;
+ * for N < 1024 the reference's unfiltered table prefix returns indices >= N, here the standard's filtered sequence
+ * (what the reference's python/polar_5g_parameters.py computes) is used. N > 1024 is PC_ERR_ARG as in the reference. */
 int pc_frozen_bits(int N, int K, float design_snr_db, const char* type, unsigned* out);
 
 /* error detector id from the reference's (size, type) pair; negative on the sizes create() rejects */

@@ -60,11 +60,27 @@ static void beta_expansion(int N, int K, std::vector<unsigned>& frozen)
     std::sort(frozen.begin(), frozen.end());
 }
 
+#include "pc_5g_table.inc"
+
+// FiveGList (reference src/polarcode/construction/fiveGList.cpp:30-43): the N - K least reliable positions of the 3GPP
+// polar sequence. The reference takes the first N - K entries of the Nmax = 1024 table UNFILTERED, which is the
+// standard's rule only for N = 1024; for N < 1024 it returns indices >= N (82 of the 384 at N = 512, K = 128). Here the
+// sequence is first restricted to the indices below N, as TS 38.212 section 5.3.1.2 prescribes (Q_0^{N-1} is the
+// subsequence of Q_0^{Nmax-1} with values less than N), so N = 1024 is value-identical to the reference and shorter
+// codes are the NR construction the reference's python/polar_5g_parameters.py computes.
+static void five_g(int N, int K, std::vector<unsigned>& frozen)
+{
+    frozen.clear();
+    for (int i = 0; i < 1024 && (int)frozen.size() < N - K; ++i)
+        if ((int)k5gSequence[i] < N) frozen.push_back(k5gSequence[i]);
+    std::sort(frozen.begin(), frozen.end());
+}
+
 int frozen_bits(int N, int K, float design_snr_db, const char* type, std::vector<unsigned>& frozen, const char** msg)
 {
     static const char* e_n = "new blockLength is not a power of 2!";
     static const char* e_k = "Invalid polar code(N, K)";
-    static const char* e_5g = "5G reliability-table construction is not part of this build";
+    static const char* e_5g = "5G standard does not allow for block size N > 1024!";
     std::string t(type ? type : "BB");
     std::transform(t.begin(), t.end(), t.begin(), [](unsigned char c) { return (char)std::tolower(c); });
     if (!pow2(N)) {
@@ -78,8 +94,11 @@ int frozen_bits(int N, int K, float design_snr_db, const char* type, std::vector
     if (t.find("be") != std::string::npos) {
         beta_expansion(N, K, frozen);
     } else if (t.find("5g") != std::string::npos) {
-        if (msg) *msg = e_5g;
-        return 3;
+        if (N > 1024) { // fiveGList.cpp:22-25 std::invalid_argument
+            if (msg) *msg = e_5g;
+            return 1;
+        }
+        five_g(N, K, frozen);
     } else {
         bhattacharyya(N, K, design_snr_db, frozen);
     }
