@@ -36,10 +36,10 @@ struct Enc2Params {
     const uint8_t* info;  // [B][kb] (check bytes already in place)
     uint8_t* code;        // [B][N/8]
     unsigned long long B;
-    int S, kb, kstride;   // kstride: words per staged info row (odd: conflict-free across lanes)
+    int S, kb, kw;        // kw: words per info row, ceil(kb / 4)
     int tpc;              // threads (= warps of a group) per codeword, N / (32 R)
     int systematic;
-    int words_in;         // info rows can be staged word-wise (kb % 4 == 0 and the base is 4-byte aligned)
+    int vec_in;           // info rows are 16-byte aligned and every thread's share is whole 16-byte pieces
     int v8;               // code rows are 32-byte aligned: 256-bit stores
 };
 
@@ -81,43 +81,61 @@ __device__ __forceinline__ uint32_t expand32(uint32_t x, const uint32_t* mv, uin
     return x & m;
 }
 
-template <int R>
+template <int R, bool MULTI> // MULTI: several warps per codeword (N > 1024); otherwise the word block index is 0
 __global__ void __launch_bounds__(512, 2) k_encode2(const __grid_constant__ Enc2Params p)
 {
     extern __shared__ __align__(16) uint32_t sm[];
     const int T = blockDim.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int tpc = p.tpc, grp = warp / tpc, t = warp - grp * tpc; // group of tpc warps = 32 codewords; t = word block
+    const int tpc = MULTI ? p.tpc : 1, grp = warp / tpc, t = MULTI ? warp - grp * tpc : 0; // group of tpc warps = 32 codewords
     const int gpc = (T >> 5) / tpc, cpc = 32 * gpc;                // codewords per CTA
     const int W = R * tpc, Wp = W + 1;                             // words per codeword (+1: conflict-free transposes)
-    uint32_t* s_info = sm;                                         // [cpc][kstride]
-    uint32_t* s_x = sm + (size_t)cpc * p.kstride;                  // [cpc][Wp]   (tpc > 1 only)
+    uint32_t* s_info = sm;                                         // [kw][cpc]: word q of codeword slot at q * cpc + slot
+    uint32_t* s_x = sm + (size_t)cpc * p.kw;                       // [cpc][Wp]   (MULTI only)
     const int slot = grp * 32 + lane;
     const int nbytes = 4 * W;
     int ltpc = 0;
     while ((1 << ltpc) < tpc) ++ltpc;
+    const int share = (p.kw + tpc - 1) / tpc; // info words of its row that one thread stages
     for (unsigned long long base = (unsigned long long)blockIdx.x * cpc; base < p.B; base += (unsigned long long)gridDim.x * cpc) {
         const unsigned long long left = p.B - base;
         const int ncw = left < (unsigned long long)cpc ? (int)left : cpc;
         const bool live = slot < ncw;
-        // ---- stage the info rows of this batch, byte-swapped so that a word is MSB-first (info bit k = bit 31 - k%32)
+        // ---- stage the info rows: thread (slot, t) loads words [t share, (t+1) share) of ITS row -- a warp's 16-byte
+        // loads cover whole 32-byte sectors between them -- byte-swaps them so that a word is MSB-first (info bit k =
+        // bit 31 - k % 32) and stores them word-interleaved (conflict-free for the stores and for the reads below)
         __syncthreads();
-        if (p.words_in) {
-            const int kw = p.kb >> 2;
-            const uint32_t* src = reinterpret_cast<const uint32_t*>(p.info + base * (unsigned long long)p.kb);
-            for (int i = threadIdx.x; i < ncw * kw; i += T) {
-                const int row = i / kw, q = i - row * kw;
-                s_info[row * p.kstride + q] = bswap32(__ldg(src + i));
-            }
-        } else {
-            const uint8_t* src = p.info + base * (unsigned long long)p.kb;
-            uint8_t* s8 = reinterpret_cast<uint8_t*>(s_info);
-            for (int i = threadIdx.x; i < ncw * p.kb; i += T) {
-                const int row = i / p.kb, b = i - row * p.kb;
-                s8[(size_t)row * 4 * p.kstride + (b ^ 3)] = src[i];
+        {
+            const uint8_t* rowp = p.info + (base + (live ? slot : 0)) * (unsigned long long)p.kb;
+            uint32_t* dst = s_info + slot;
+            const int q0 = t * share, q1e = q0 + share < p.kw ? q0 + share : p.kw;
+            if (p.vec_in) {
+                const uint4* r4 = reinterpret_cast<const uint4*>(rowp) + (q0 >> 2);
+                for (int q = q0; q < q1e; q += 16) { // up to four 16-byte loads in flight
+                    uint4 v[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        if (q + 4 * u < q1e) v[u] = __ldg(r4 + ((q - q0) >> 2) + u);
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        if (q + 4 * u < q1e) {
+                            dst[(q + 4 * u) * cpc] = bswap32(v[u].x);
+                            dst[(q + 4 * u + 1) * cpc] = bswap32(v[u].y);
+                            dst[(q + 4 * u + 2) * cpc] = bswap32(v[u].z);
+                            dst[(q + 4 * u + 3) * cpc] = bswap32(v[u].w);
+                        }
+                }
+            } else {
+                for (int q = q0; q < q1e; ++q) {
+                    uint32_t w = 0;
+#pragma unroll
+                    for (int b = 0; b < 4; ++b)
+                        if (4 * q + b < p.kb) w |= (uint32_t)rowp[4 * q + b] << (24 - 8 * b);
+                    dst[q * cpc] = w;
+                }
             }
         }
         __syncthreads();
-        const uint32_t* myinfo = s_info + (size_t)(live ? slot : 0) * p.kstride;
+        const uint32_t* myinfo = s_info + slot;
         // ---- deposit: code word w takes the info bits ending at stream bit e - 1, right-aligned, expanded onto its mask
         uint32_t x[R];
 #pragma unroll
@@ -127,7 +145,7 @@ __global__ void __launch_bounds__(512, 2) k_encode2(const __grid_constant__ Enc2
             uint32_t v = 0;
             if (m) { // uniform
                 const int q1 = (int)E[1], pos = (int)E[2];
-                const uint32_t lo = myinfo[q1], hi = q1 ? myinfo[q1 - 1] : 0u;
+                const uint32_t lo = myinfo[q1 * cpc], hi = q1 ? myinfo[(q1 - 1) * cpc] : 0u;
                 v = __funnelshift_r(lo, hi, pos);
                 if (m != 0xFFFFFFFFu) v = expand32(v, E + 3, m);
             }
@@ -241,10 +259,10 @@ void encode2_forget(const pc_code* c)
         if (o == c) o = nullptr;
 }
 
-template <int R>
+template <int R, bool MULTI>
 static cudaError_t launch2(const Enc2Params& p, int grid, int threads, size_t smem, cudaStream_t st)
 {
-    auto kern = k_encode2<R>;
+    auto kern = k_encode2<R, MULTI>;
     if (smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
@@ -279,25 +297,26 @@ int encode2_device_raw(pc_code* c, const uint8_t* src, uint8_t* d_code, size_t B
     p.B = B;
     p.S = c->S;
     p.kb = kb;
-    p.kstride = ((kb + 3) / 4) | 1;
+    p.kw = (kb + 3) / 4;
     p.tpc = tpc;
     p.systematic = c->systematic;
-    p.words_in = (kb % 4 == 0 && (reinterpret_cast<uintptr_t>(src) & 3u) == 0) ? 1 : 0;
+    // every thread stages kw / tpc words of its own row: 16-byte loads when rows and shares are whole 16-byte pieces
+    p.vec_in = (kb % 16 == 0 && (reinterpret_cast<uintptr_t>(src) & 15u) == 0 && ((kb / 4) % (4 * tpc)) == 0) ? 1 : 0;
     p.v8 = ((reinterpret_cast<uintptr_t>(d_code) & 31u) == 0 && (4 * R) % 32 == 0) ? 1 : 0;
     // CTA: whole groups of tpc warps (32 codewords each); 256 threads for short codes, 512 when a group needs them
     int threads = tpc <= 8 ? 256 : 32 * tpc;
     const int gpc = (threads / 32) / tpc, cpc = 32 * gpc;
-    const size_t smem = 4 * ((size_t)cpc * p.kstride + (tpc > 1 ? (size_t)cpc * (W + 1) : 0));
+    const size_t smem = 4 * ((size_t)cpc * p.kw + (tpc > 1 ? (size_t)cpc * (W + 1) : 0));
     size_t ctas = (B + cpc - 1) / cpc;
     const int grid = (int)(ctas < 148 * 8 ? ctas : 148 * 8);
     cudaError_t e;
     switch (R) {
-    case 1: e = launch2<1>(p, grid, threads, smem, st); break;
-    case 2: e = launch2<2>(p, grid, threads, smem, st); break;
-    case 4: e = launch2<4>(p, grid, threads, smem, st); break;
-    case 8: e = launch2<8>(p, grid, threads, smem, st); break;
-    case 16: e = launch2<16>(p, grid, threads, smem, st); break;
-    default: e = launch2<32>(p, grid, threads, smem, st); break;
+    case 1: e = launch2<1, false>(p, grid, threads, smem, st); break;
+    case 2: e = launch2<2, false>(p, grid, threads, smem, st); break;
+    case 4: e = launch2<4, false>(p, grid, threads, smem, st); break;
+    case 8: e = launch2<8, false>(p, grid, threads, smem, st); break;
+    case 16: e = launch2<16, false>(p, grid, threads, smem, st); break;
+    default: e = tpc > 1 ? launch2<32, true>(p, grid, threads, smem, st) : launch2<32, false>(p, grid, threads, smem, st); break;
     }
     if (e != cudaSuccess) return cuda_fail(e, "encode2 launch");
     count_launch();

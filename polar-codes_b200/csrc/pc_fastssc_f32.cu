@@ -42,6 +42,179 @@ __global__ void __launch_bounds__(256) k_fastssc_f32(const __grid_constant__ F32
     }
 }
 
+// ---- group-of-8 form: EIGHT LANES per codeword, the whole float tree in shared memory ---------------------------------
+// The thread-per-codeword kernel above is DRAM-bound on its 4 N-byte-per-thread arena (11x the algorithmic traffic).
+// Here a codeword's LLR stages (4 N bytes) and decision words sit in shared memory and the 8 lanes of a group -- the
+// width of the reference's AVX vectors -- share the element-wise steps: lane k handles elements k, k + 8, ... of every
+// f / g / g0 / g1 / combine step with at least 8 elements per half, which is where 88 % of the element operations of a
+// (1024, 512) tree are. Leaves and the steps of nodes with fewer than 16 elements run on lane 0 of the group with
+// the SAME core functions as the other kernel (their 8-lane summation / tie orders are already restated on arrays),
+// so results are identical by construction. Codeword stride = 8 mod 32 words: the four groups of a warp use
+// disjoint banks. About 48 codewords are resident per SM (12 warps).
+template <class Op>
+__device__ __forceinline__ void g8_map(const FCtx& c, const FView& in, int s, int g, const Op& op)
+{
+    const int h = 1 << (s - 1);
+    float* dst = c.llr + c.llr_off[s - 1];
+    for (int i0 = 0; i0 < h; i0 += 32) {
+        float a[4], b[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int i = i0 + 8 * u + g;
+            if (i < h) a[u] = in[i], b[u] = in[i + h];
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int i = i0 + 8 * u + g;
+            if (i < h) dst[i] = op(a[u], b[u], i);
+        }
+    }
+}
+
+__device__ __forceinline__ uint32_t g8_or(uint32_t v)
+{
+    v |= __shfl_xor_sync(0xFFFFFFFFu, v, 1);
+    v |= __shfl_xor_sync(0xFFFFFFFFu, v, 2);
+    v |= __shfl_xor_sync(0xFFFFFFFFu, v, 4);
+    return v;
+}
+
+// ROneNode::rightDecode with the 8 lanes computing the signs of g (same element-wise operations as fop_g1)
+__device__ __forceinline__ void g8_g1(const FCtx& c, const FView& in, int s, int off, int g)
+{
+    const int h = 1 << (s - 1);
+    if (h >= 32) {
+        for (int w = 0; w < (h >> 5); ++w) {
+            const uint32_t left = c.bld((off >> 5) + w);
+            uint32_t r = 0;
+            float a[4], b[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) a[u] = in[32 * w + 8 * u + g], b[u] = in[32 * w + 8 * u + g + h];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) r |= fsign(g_f32(a[u], b[u], (left >> (8 * u + g)) & 1u)) << (8 * u + g);
+            r = g8_or(r);
+            if (g == 0) {
+                c.bst((off >> 5) + w, left ^ r);
+                c.bst(((off + h) >> 5) + w, r);
+            }
+        }
+    } else { // h = 8 or 16: one word holds both halves
+        const int sh = off & 31;
+        uint32_t word = c.bld(off >> 5);
+        uint32_t r = 0;
+        for (int k = g; k < h; k += 8) r |= fsign(g_f32(in[k], in[k + h], (word >> (sh + k)) & 1u)) << k;
+        r = g8_or(r);
+        if (g == 0) {
+            word ^= r << sh;
+            word = (word & ~(lowmask(h) << (sh + h))) | (r << (sh + h));
+            c.bst(off >> 5, word);
+        }
+    }
+}
+
+__device__ __forceinline__ void fastssc_f32_run_g8(const FCtx& c, int g, const uint32_t* code, const float* row, bool staged_root)
+{
+    const int S = c.S;
+    if (staged_root) {
+        for (int i = g; i < (1 << S); i += 8) c.st(S, i, row[i]);
+        __syncwarp();
+    }
+    for (int pc = 0;; ++pc) {
+        const uint32_t ins = __ldg(code + pc);
+        const uint32_t op = instr_op(ins);
+        const int s = (int)instr_s(ins), off = (int)instr_off(ins);
+        if (op == FOP_END) break;
+        const FView in = (s == S && !staged_root) ? FView{ row, 1 } : c.stage(s);
+        const int h = 1 << (s - 1);
+        if (op <= FOP_COMB0 && h >= 8 && (op < FOP_COMB || h >= 32)) {
+            switch (op) {
+            case FOP_F: g8_map(c, in, s, g, [](float a, float b, int) { return f_f32(a, b); }); break;
+            case FOP_G0: g8_map(c, in, s, g, [](float a, float b, int) { return fadd(a, b); }); break;
+            case FOP_G: {
+                const uint32_t* bits = c.bits;
+                g8_map(c, in, s, g, [bits, off](float a, float b, int i) { return g_f32(a, b, (bits[(off + i) >> 5] >> ((off + i) & 31)) & 1u); });
+                break;
+            }
+            case FOP_G1: g8_g1(c, in, s, off, g); break;
+            default: // FOP_COMB / FOP_COMB0 with whole words per half
+                for (int w = g; w < (h >> 5); w += 8) {
+                    const uint32_t r = c.bld(((off + h) >> 5) + w);
+                    c.bst((off >> 5) + w, op == FOP_COMB0 ? r : (c.bld((off >> 5) + w) ^ r));
+                }
+                break;
+            }
+        } else if (g == 0) {
+            switch (op) {
+            case FOP_F: fop_f(c, in, s); break;
+            case FOP_G: fop_g(c, in, s, off); break;
+            case FOP_G0: fop_g0(c, in, s); break;
+            case FOP_G1: fop_g1(c, in, s, off); break;
+            case FOP_COMB: fop_comb(c, s, off, false); break;
+            case FOP_COMB0: fop_comb(c, s, off, true); break;
+            case FOP_R0: fleaf_const(c, s, off, 0u); break;
+            case FOP_R1: fleaf_r1(c, in, s, off); break;
+            case FOP_REP: fleaf_rep(c, in, s, off); break;
+            case FOP_SPC: fleaf_spc(c, in, s, off); break;
+            case FOP_DREP: fleaf_drep(c, in, s, off); break;
+            case FOP_DSPC: fleaf_dspc(c, in, s, off); break;
+            case FOP_DSPC8: fleaf_dspc8(c, in, off); break;
+            case FOP_ZSPC: fleaf_zspc(c, in, s, off); break;
+            default: {
+                float v[8];
+                if (op == FOP_ZSPC8 || op == FOP_REPONE8) {
+                    for (int k = 0; k < 8; ++k) v[k] = in[k];
+                } else {
+                    accumulate8(in, 1 << s, v);
+                }
+                if (op == FOP_ZSPC8 || op == FOP_TREP)
+                    fleaf_sum4_spc(c, v, s, off);
+                else
+                    fleaf_rep_then(c, v, s, off, op == FOP_T5);
+                break;
+            }
+            }
+        }
+        __syncwarp(); // the next step reads what other lanes of the group wrote
+    }
+}
+
+__global__ void __launch_bounds__(128) k_fastssc_f32_g8(const __grid_constant__ F32Params p)
+{
+    extern __shared__ __align__(16) uint32_t smem_g8[];
+    const int T = blockDim.x, t = threadIdx.x, g = t & 7, slot = t >> 3, cpc = T >> 3;
+    uint32_t* crc_table = smem_g8; // 256 words
+    if (p.crc.width)
+        for (int i = t; i < 256; i += T) crc_table[i] = p.crc_table[i];
+    __syncthreads();
+    float* mine = reinterpret_cast<float*>(smem_g8 + 256) + (size_t)slot * p.g8_cw_words;
+    FCtx c;
+    c.S = p.S;
+    c.llr_off = p.llr_off;
+    c.llr = mine;
+    c.ls = 1;
+    c.bits = reinterpret_cast<uint32_t*>(mine + p.elems);
+    c.bs = 1;
+    Ctx ic; // the int8 core's decision-word helpers (transform, gather) on the same words
+    ic.S = p.S;
+    ic.bits_kind = PK_SMEM;
+    ic.bits = c.bits;
+    ic.bws = 1;
+    const int N = 1 << p.S, kb = (p.K + 7) >> 3;
+    const unsigned long long nbatch = (p.B + cpc - 1) / cpc;
+    for (unsigned long long bi = blockIdx.x; bi < nbatch; bi += gridDim.x) {
+        const unsigned long long fl = bi * cpc + slot;
+        const bool live = fl < p.B;
+        const unsigned long long f = live ? fl : p.B - 1;
+        fastssc_f32_run_g8(c, g, p.code, p.llr + f * N, p.staged_root != 0);
+        if (g == 0) {
+            if (!p.systematic) transform_bits_inplace(ic);
+            const bool res = extract_info(ic, p.runs, p.nruns, p.K, p.info + f * kb, p.crc, crc_table, live);
+            if (p.ok && live) p.ok[f] = res ? 1 : 0;
+        }
+        __syncwarp();
+    }
+}
+
 // FloatContainer::insertLlr(const char*) (reference src/polarcode/bitcontainer.cpp:202-207): int8 -> float
 __global__ void __launch_bounds__(256) k_i8_to_f32(const int8_t* __restrict__ in, float* __restrict__ out, unsigned long long n)
 {
@@ -65,6 +238,17 @@ cudaError_t launch_fastssc_f32(const F32Launch& L, const float* d_llr, uint8_t* 
     p.info = d_info;
     p.ok = d_ok;
     p.B = B;
+    if (L.g8) {
+        const int cpc = L.g8_threads / 8;
+        size_t nb = (B + cpc - 1) / cpc;
+        const int grid = (int)(nb < (size_t)L.g8_grid ? nb : (size_t)L.g8_grid);
+        cudaError_t e = cudaFuncSetAttribute(k_fastssc_f32_g8, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.g8_smem);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(k_fastssc_f32_g8, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
+        if (e != cudaSuccess) return e;
+        k_fastssc_f32_g8<<<grid, L.g8_threads, L.g8_smem, st>>>(p);
+        return cudaGetLastError();
+    }
     size_t ctas = (B + L.threads - 1) / L.threads;
     const int grid = (int)(ctas < (size_t)L.grid ? ctas : (size_t)L.grid);
     // the arena is laid out for L.grid * L.threads threads; a smaller grid only uses a prefix of every row

@@ -154,7 +154,7 @@ cudaError_t launch_fastssc_i8(const FastSscLaunch& L, const int8_t* d_llr, uint8
     // memory hints (default on; PC_FASTSSC_HINTS=0..3 for measurements): bit 0 needs 32-byte aligned rows
     static const int env_hints = getenv("PC_FASTSSC_HINTS") ? atoi(getenv("PC_FASTSSC_HINTS")) : 3;
     kp.hints = (uint32_t)env_hints;
-    if ((reinterpret_cast<uintptr_t>(d_llr) & 31u) || L.S < 6) kp.hints &= ~1u;
+    if ((reinterpret_cast<uintptr_t>(d_llr) & 31u) || L.S < 6) kp.hints &= ~5u;
     const bool cp = L.const_code >= 0 && L.const_runs >= 0;
     return cp ? launch_t<true>(L, kp, st) : launch_t<false>(L, kp, st);
 }

@@ -69,6 +69,13 @@ __device__ __forceinline__ void ldg256_stream(const uint32_t* p, u4& a, u4& b)
                  : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)
                  : "l"(p));
 }
+// the same 32-byte access without cache hints (measurement variant: load width and policy separately)
+__device__ __forceinline__ void ldg256_plain(const uint32_t* p, u4& a, u4& b)
+{
+    asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)
+                 : "l"(p));
+}
 // Arena chunks (the per-thread LLR stages that do not fit on chip): kept in L2 with an evict-last policy so that the
 // streaming rows do not push them out to HBM.
 __device__ __forceinline__ u4 ldg128_keep(const uint32_t* p)
@@ -96,6 +103,7 @@ inline void ldg256_stream(const uint32_t* p, u4& a, u4& b)
     a = *reinterpret_cast<const u4*>(p);
     b = *reinterpret_cast<const u4*>(p + 4);
 }
+inline void ldg256_plain(const uint32_t* p, u4& a, u4& b) { ldg256_stream(p, a, b); }
 inline u4 ldg128_keep(const uint32_t* p) { return *reinterpret_cast<const u4*>(p); }
 inline void stg128_keep(uint32_t* p, const u4& v) { *reinterpret_cast<u4*>(p) = v; }
 // host emulation (tests/host_emul.cpp): "tensor memory" is a plain array of columns, the address its index
@@ -114,7 +122,7 @@ inline void tm_wait_ld() {}
 inline void tm_wait_st() {}
 #endif
 
-enum : uint8_t { MH_NONE = 0, MH_ROW = 1, MH_ARENA = 2 };
+enum : uint8_t { MH_NONE = 0, MH_ROW = 1, MH_ARENA = 2, MH_ROW_PLAIN = 3 };
 // One stage (or the channel row) as seen by one thread
 struct Mem {
     uint32_t* p;   // generic address of chunk 0 (shared, arena or channel row); unused for tensor memory
@@ -161,7 +169,8 @@ struct Ctx {
     uint32_t* bits;    // word 0 (shared or arena), stride bws
     size_t bws;
     uint32_t tbits;    // tensor-memory address of word 0
-    uint32_t hints;    // launch option: bit 0 stream the channel row (ldg256_stream), bit 1 keep the arena in L2
+    uint32_t hints;    // launch option: bit 0 stream the channel row (ldg256_stream), bit 1 keep the arena in L2,
+                       // bit 2 32-byte row loads without cache hints
 
     PC_HD Mem stage(int s) const
     {
@@ -261,6 +270,9 @@ PC_HD void big_loop(const Ctx& c, const Mem& src, const Mem& dst, int s, int off
             if (src.hint == MH_ROW) { // chunks 2j and 2j+1 of a row are 32 contiguous bytes
                 ldg256_stream(p, a0, a1);
                 ldg256_stream(p + (size_t)half * 4, b0, b1);
+            } else if (src.hint == MH_ROW_PLAIN) {
+                ldg256_plain(p, a0, a1);
+                ldg256_plain(p + (size_t)half * 4, b0, b1);
             } else if (src.hint == MH_ARENA) {
                 a0 = ldg128_keep(p);
                 a1 = ldg128_keep(p + src.stride);
@@ -764,7 +776,7 @@ PC_HD void fastssc_i8_run(Ctx& c, const uint32_t* code, const int8_t* row, bool 
     groot.stride = 4;
     groot.tcol = 0;
     groot.tm = false;
-    groot.hint = (c.hints & 1u) ? MH_ROW : MH_NONE;
+    groot.hint = (c.hints & 1u) ? MH_ROW : ((c.hints & 4u) ? MH_ROW_PLAIN : MH_NONE);
     for (int pc = 0;; ++pc) {
         const uint32_t ins = code[pc];
         const uint32_t op = instr_op(ins);

@@ -60,6 +60,7 @@ struct SclParams {
     int tm_alloc_cols;   // tcgen05.alloc size of one CTA (0: unused)
     int tm_cols_thread;  // columns per thread (warps sharing a lane quarter are stacked along columns)
     int scr_off;         // smem word offset of a per-lane scratch of N/32 words for extractBestPath
+    int lockstep;        // CTA barrier after every node-program step (keeps the warps on the same instruction lines)
 };
 
 struct SclLaunch {
@@ -121,11 +122,14 @@ struct F32Params {
     size_t arena_stride; // threads the arena rows are laid out for
     float* arena;  // [elems][arena_stride]
     uint32_t* bits_arena; // [nbw][grid*threads]
+    int g8_cw_words; // group-of-8 kernel: shared-memory words per codeword (elems + nbw, padded to 8 mod 32)
 };
 
 struct F32Launch {
     F32Params p;
     int threads, grid;
+    int g8, g8_threads, g8_grid; // group-of-8 kernel (tree in shared memory) chosen for this code
+    size_t g8_smem;
 };
 cudaError_t launch_fastssc_f32(const F32Launch& L, const float* d_llr, uint8_t* d_info, uint8_t* d_ok, size_t B, cudaStream_t st);
 cudaError_t launch_i8_to_f32(const int8_t* d_in, float* d_out, size_t n, cudaStream_t st);

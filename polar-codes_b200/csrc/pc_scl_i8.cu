@@ -416,7 +416,7 @@ __device__ __forceinline__ void scl_spc(Lane& c, const SclParams& p, int s, int 
 }
 
 template <int BM>
-__global__ void __launch_bounds__(256, 2) k_scl_i8(const __grid_constant__ SclParams p)
+__global__ void __launch_bounds__(512, 1) k_scl_i8(const __grid_constant__ SclParams p)
 {
     using Lane = LaneT<BM>;
     extern __shared__ __align__(16) uint32_t smem[];
@@ -485,7 +485,13 @@ __global__ void __launch_bounds__(256, 2) k_scl_i8(const __grid_constant__ SclPa
             case SCL_REP: scl_rep(c, p, s, side); break;
             default: scl_spc(c, p, s, side); break;
             }
-            __syncwarp(); // other lanes' buffers are read by the next step
+            // other lanes' buffers are read by the next step. With `lockstep` the whole CTA meets here: the kernel is
+            // 130 KB of SASS, and warps spread over the program (ncu r02_scl_i8_v0: `no_instruction` 5.3 cycles per
+            // issue with 16 free-running warps) thrash the instruction caches; in step, a fetched line serves all warps.
+            if (p.lockstep)
+                __syncthreads();
+            else
+                __syncwarp();
         }
         // extractBestPath (scl_fip_char.cpp:816-855)
         const bool active = c.l < c.P;
@@ -672,6 +678,7 @@ static int plan_scl_i8_smem(int S, int K, int L, bool root_leaf, size_t smem_max
     p.arena_words = aw;
     p.tm_alloc_cols = 0;
     p.tm_cols_thread = 0;
+    p.lockstep = getenv("PC_SCL_LOCKSTEP") ? atoi(getenv("PC_SCL_LOCKSTEP")) != 0 : 0;
     p.scr_off = p.bitL_off[S]; // non-systematic extraction works on the (free) left buffer of the top stage
     out.threads = T;
     out.smem_bytes = 1024 + 4 * (size_t)w * T;
@@ -702,7 +709,11 @@ int plan_scl_i8(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, S
     const bool no_tmem = getenv("PC_SCL_NOTMEM") != nullptr || getenv("PC_SCL_LANES") != nullptr;
     int G = 1;
     while (G < L) G <<= 1;
-    const int T = 256, per_sm = 2, tm_alloc = 256, tm_cols = tm_alloc / ((T / 32 + 3) / 4); // 128 columns per thread
+    // shape: ONE CTA of 512 lanes whose warps stay in step (default), or PC_SCL_T=256: two CTAs of 256
+    int T = 512;
+    if (const char* e = getenv("PC_SCL_T")) T = atoi(e) == 256 ? 256 : (atoi(e) == 128 ? 128 : 512);
+    const int per_sm = 512 / T, tm_alloc = 512 / per_sm, tm_cols = tm_alloc / ((T / 32 + 3) / 4); // 128 columns per thread
+    const bool lockstep = getenv("PC_SCL_LOCKSTEP") ? atoi(getenv("PC_SCL_LOCKSTEP")) != 0 : true;
     const int top_llr = root_leaf ? S : S - 1;
     if (!no_tmem && S >= 6 && S <= 15) {
         size_t per_cta = 233472 / (size_t)per_sm - 1024;
@@ -765,6 +776,7 @@ int plan_scl_i8(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, S
             p.tm_alloc_cols = tm_alloc;
             p.tm_cols_thread = tm_cols;
             p.scr_off = scr;
+            p.lockstep = lockstep ? 1 : 0;
             out.threads = T;
             out.smem_bytes = 1024 + 4 * (size_t)w * T;
             out.grid = sms * per_sm;

@@ -197,13 +197,19 @@ class PolarEncoder(_Code):
         return (code, icrc) if return_info else code
 
     def encode_vector(self, array):
-        """encoder_python.cc:45-61: uint8[K/8] -> uint8[N/8]"""
+        """encoder_python.cc:45-61: uint8[K/8] -> uint8[N/8]. Like the reference, a detector's check bytes are written
+        INTO the caller's array (ButterflyFipPacked::encode runs Detector::generate on the input buffer,
+        butterfly_fip_packed.cpp:47-49; the binding hands it the numpy buffer itself): qa_pypolar_decoder.py compares
+        the decoder's output with the array it passed in."""
         a = np.asarray(array, dtype=np.uint8)
         if a.ndim != 1:
             raise RuntimeError("Only ONE-dimensional vectors allowed!")
         if a.size != self._K // 8:
             raise RuntimeError("Input vector size != infoLength // 8!")
-        return self.encode_batch(a.reshape(1, -1))[0]
+        code, icrc = self.encode_batch(a.reshape(1, -1), return_info=True)
+        if self._crc != 0 and isinstance(array, np.ndarray) and array.dtype == np.uint8 and array.flags.writeable:
+            array[...] = icrc[0]
+        return code[0]
 
 
 class Detector:
