@@ -392,6 +392,7 @@ void pc_code_destroy(pc_code* c)
     cudaFree(c->d_info_mask);
     cudaFree(c->d_enc_runs);
     cudaFree(c->d_enc_first);
+    cudaFree(c->d_enc_tab);
     cudaFree(c->d_enc_info);
     cudaFree(c->d_chan_code);
     cudaFree(c->d_quant);

@@ -177,13 +177,14 @@ int build_encoder_tables(pc_code* c)
 }
 
 bool encode2_supported(const pc_code* c);
-int encode2_device_raw(pc_code* c, const uint8_t* src, uint8_t* d_code, size_t B, cudaStream_t st);
+bool encode2_fuses_crc(const pc_code* c);
+int encode2_device_raw(pc_code* c, const uint8_t* src, uint8_t* d_code, size_t B, cudaStream_t st, bool fuse_crc);
+static const bool g_force_old_encoder = getenv("PC_ENC_OLD") != nullptr; // measurements: keep this file's kernel
 
 int encode_device_raw(pc_code* c, const uint8_t* src, uint8_t* d_code, size_t B, cudaStream_t st)
 {
     // 32 <= N <= 16384: the register-block kernel (pc_encode2.cu); PC_ENC_OLD=1 keeps this file's kernel for measurements
-    static const bool force_old = getenv("PC_ENC_OLD") != nullptr;
-    if (!force_old && encode2_supported(c)) return encode2_device_raw(c, src, d_code, B, st);
+    if (!g_force_old_encoder && encode2_supported(c)) return encode2_device_raw(c, src, d_code, B, st, false);
     const int kb = (c->K + 7) / 8;
     EncParams p;
     p.info = src;
@@ -231,6 +232,10 @@ int encode_device(pc_code* c, const uint8_t* d_info, uint8_t* d_code, uint8_t* d
     CrcSpec crc;
     crc_spec(c->crc_kind, crc);
     const uint8_t* src = d_info;
+    // nobody wants the info blocks with their check bytes back and the code is short enough for one thread per
+    // codeword: the detector runs inside the encoder kernel on the staged rows (no copy, no extra pass over HBM)
+    if (crc.width && !d_info_crc && !g_force_old_encoder && encode2_fuses_crc(c) && !getenv("PC_ENC_NOFUSE"))
+        return encode2_device_raw(c, d_info, d_code, B, st, true);
     if (crc.width || d_info_crc) {
         // the reference writes the check bytes into the caller's buffer (butterfly_fip_packed.cpp:47-49); here they go
         // into a device-side copy

@@ -41,6 +41,10 @@ struct Enc2Params {
     int systematic;
     int vec_in;           // info rows are 16-byte aligned and every thread's share is whole 16-byte pieces
     int v8;               // code rows are 32-byte aligned: 256-bit stores
+    const uint32_t* tab;  // the code's table in HBM (multi-warp codewords read it through L1: 16 warps walking 16 KB of
+                          // __constant__ memory with different offsets miss the constant cache on every access)
+    CrcSpec crc;          // fused Detector::generate (single-thread codewords only; width 0 = none / done before)
+    const uint32_t* crc_table;
 };
 
 __device__ __forceinline__ uint32_t bswap32(uint32_t x) { return __byte_perm(x, 0, 0x0123); }
@@ -91,6 +95,9 @@ __global__ void __launch_bounds__(512, 2) k_encode2(const __grid_constant__ Enc2
     const int W = R * tpc, Wp = W + 1;                             // words per codeword (+1: conflict-free transposes)
     uint32_t* s_info = sm;                                         // [kw][cpc]: word q of codeword slot at q * cpc + slot
     uint32_t* s_x = sm + (size_t)cpc * p.kw;                       // [cpc][Wp]   (MULTI only)
+    uint32_t* s_crc = s_x + (MULTI ? (size_t)cpc * Wp : 0);        // 256 words (fused detector only)
+    if (!MULTI && p.crc.width)
+        for (int i = threadIdx.x; i < 256; i += T) s_crc[i] = p.crc_table[i];
     const int slot = grp * 32 + lane;
     const int nbytes = 4 * W;
     int ltpc = 0;
@@ -135,19 +142,50 @@ __global__ void __launch_bounds__(512, 2) k_encode2(const __grid_constant__ Enc2
             }
         }
         __syncthreads();
-        const uint32_t* myinfo = s_info + slot;
+        uint32_t* myinfo = s_info + slot;
+        if (!MULTI && p.crc.width) {
+            // Detector::generate fused (ButterflyFipPacked::encode runs it on the info block first,
+            // butterfly_fip_packed.cpp:47-49): the row's own thread runs the table-driven CRC over its staged words
+            // (MSB-first, so byte b of the row is bits 31-8(b%4).. of word b/4) and writes the check bytes into them
+            CrcStream cs;
+            cs.begin(p.crc);
+            const int payload = p.crc.reflected ? 4 * ((p.kb >> 2) - 1) : p.kb - p.crc.bytes;
+            for (int q = 0; 4 * q < payload; ++q) {
+                const uint32_t w = myinfo[q * cpc];
+#pragma unroll
+                for (int b = 0; b < 4; ++b)
+                    if (4 * q + b < payload) cs.payload_byte(p.crc, s_crc, (w >> (24 - 8 * b)) & 0xFFu);
+            }
+            const uint32_t val = cs.value(p.crc);
+            for (int i = 0; i < p.crc.bytes; ++i) {
+                const uint32_t byte = p.crc.reflected ? (val >> (8 * i)) & 0xFFu : (val >> (8 * (p.crc.bytes - 1 - i))) & 0xFFu;
+                const int pos = payload + i, sh = 24 - 8 * (pos & 3);
+                uint32_t* wp = myinfo + (pos >> 2) * cpc;
+                *wp = (*wp & ~(0xFFu << sh)) | (byte << sh);
+            }
+        }
         // ---- deposit: code word w takes the info bits ending at stream bit e - 1, right-aligned, expanded onto its mask
         uint32_t x[R];
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            const uint32_t* E = c_enc + 8 * (t * R + r);
-            const uint32_t m = E[0];
+            // table entry of code word t R + r: __constant__ operands for single-thread codewords, L1-cached loads otherwise
+            const uint32_t* Eg = p.tab + 8 * (t * R + r);
+            const uint32_t* Ec = c_enc + 8 * r;
+            const uint32_t m = MULTI ? __ldg(Eg) : Ec[0];
             uint32_t v = 0;
             if (m) { // uniform
-                const int q1 = (int)E[1], pos = (int)E[2];
+                const int q1 = (int)(MULTI ? __ldg(Eg + 1) : Ec[1]), pos = (int)(MULTI ? __ldg(Eg + 2) : Ec[2]);
                 const uint32_t lo = myinfo[q1 * cpc], hi = q1 ? myinfo[(q1 - 1) * cpc] : 0u;
                 v = __funnelshift_r(lo, hi, pos);
-                if (m != 0xFFFFFFFFu) v = expand32(v, E + 3, m);
+                if (m != 0xFFFFFFFFu) {
+#pragma unroll
+                    for (int i = 4; i >= 0; --i) {
+                        const uint32_t mv = MULTI ? __ldg(Eg + 3 + i) : Ec[3 + i];
+                        const uint32_t sh = v << (1 << i);
+                        v = (v & ~mv) | (sh & mv);
+                    }
+                    v &= m;
+                }
             }
             x[r] = v;
         }
@@ -170,7 +208,7 @@ __global__ void __launch_bounds__(512, 2) k_encode2(const __grid_constant__ Enc2
         if (p.systematic) { // resetFrozenBits, then the second transform starting in the layout we are in
             if (tpc > 1) {
 #pragma unroll
-                for (int r = 0; r < R; ++r) x[r] &= c_enc[8 * (r * tpc + t)];
+                for (int r = 0; r < R; ++r) x[r] &= __ldg(p.tab + 8 * (r * tpc + t));
                 stages_inreg<R>(x, 5 - ltpc);
             } else {
 #pragma unroll
@@ -271,7 +309,10 @@ static cudaError_t launch2(const Enc2Params& p, int grid, int threads, size_t sm
     return cudaGetLastError();
 }
 
-int encode2_device_raw(pc_code* c, const uint8_t* src, uint8_t* d_code, size_t B, cudaStream_t st)
+bool encode2_fuses_crc(const pc_code* c) { return encode2_supported(c) && c->N <= 1024; }
+
+// fuse_crc: run the code's detector on the staged info rows inside the kernel (only where encode2_fuses_crc)
+int encode2_device_raw(pc_code* c, const uint8_t* src, uint8_t* d_code, size_t B, cudaStream_t st, bool fuse_crc)
 {
     const int W = c->N / 32, R = W < 32 ? W : 32, tpc = W / R;
     const int kb = (c->K + 7) / 8;
@@ -290,6 +331,13 @@ int encode2_device_raw(pc_code* c, const uint8_t* src, uint8_t* d_code, size_t B
             g_enc_owner[dev] = c;
             g_enc_serial[dev]++;
         }
+        if (tpc > 1 && !c->d_enc_tab) { // the same table in HBM for the multi-warp kernel
+            std::vector<uint32_t> tab;
+            build_table(c, tab);
+            cudaError_t e = cudaMalloc(&c->d_enc_tab, tab.size() * 4);
+            if (e == cudaSuccess) e = cudaMemcpy(c->d_enc_tab, tab.data(), tab.size() * 4, cudaMemcpyHostToDevice);
+            if (e != cudaSuccess) return cuda_fail(e, "encoder table (HBM)");
+        }
     }
     Enc2Params p;
     p.info = src;
@@ -303,10 +351,13 @@ int encode2_device_raw(pc_code* c, const uint8_t* src, uint8_t* d_code, size_t B
     // every thread stages kw / tpc words of its own row: 16-byte loads when rows and shares are whole 16-byte pieces
     p.vec_in = (kb % 16 == 0 && (reinterpret_cast<uintptr_t>(src) & 15u) == 0 && ((kb / 4) % (4 * tpc)) == 0) ? 1 : 0;
     p.v8 = ((reinterpret_cast<uintptr_t>(d_code) & 31u) == 0 && (4 * R) % 32 == 0) ? 1 : 0;
+    p.tab = c->d_enc_tab;
+    crc_spec(fuse_crc && tpc == 1 ? c->crc_kind : 0, p.crc);
+    p.crc_table = c->d_crc_table;
     // CTA: whole groups of tpc warps (32 codewords each); 256 threads for short codes, 512 when a group needs them
     int threads = tpc <= 8 ? 256 : 32 * tpc;
     const int gpc = (threads / 32) / tpc, cpc = 32 * gpc;
-    const size_t smem = 4 * ((size_t)cpc * p.kw + (tpc > 1 ? (size_t)cpc * (W + 1) : 0));
+    const size_t smem = 4 * ((size_t)cpc * p.kw + (tpc > 1 ? (size_t)cpc * (W + 1) : 256));
     size_t ctas = (B + cpc - 1) / cpc;
     const int grid = (int)(ctas < 148 * 8 ? ctas : 148 * 8);
     cudaError_t e;

@@ -10,7 +10,6 @@
 // data-dependent SPC flip. Throughput is then bounded by the integer pipes, not by lane utilisation; the number
 // of resident warps is bounded by on-chip bytes per codeword (about N + N/8), hence shared + tensor memory.
 #include <climits>
-#include <cstdlib>
 
 #include "pc_fastssc_i8_core.h"
 #include "pc_kernels.cuh"
@@ -39,7 +38,6 @@ struct KParams {
     uint32_t place[24];
     int smem_chunks, tmem_alloc_cols, tmem_cols_thread, arena_chunks, bits_kind, bits_base, nbw;
     uint32_t* arena;
-    uint32_t hints; // Ctx::hints
 };
 
 template <bool CONSTPROG>
@@ -80,7 +78,6 @@ __global__ void __launch_bounds__(1024) k_fastssc_i8(const __grid_constant__ KPa
     // a warp reaches the 32 tensor-memory lanes of its quarter (warp % 4); warps sharing a quarter are stacked along columns
     c.tm = p.tmem_alloc_cols ? tm_base_s + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)((warp >> 2) * p.tmem_cols_thread)
                              : 0u;
-    c.hints = p.hints;
     c.bits_kind = (uint32_t)p.bits_kind;
     c.tbits = c.tm + (uint32_t)p.bits_base;
     if (p.bits_kind == PK_ARENA) {
@@ -151,10 +148,6 @@ cudaError_t launch_fastssc_i8(const FastSscLaunch& L, const int8_t* d_llr, uint8
     kp.bits_base = L.bits_base;
     kp.nbw = L.nbw;
     kp.arena = L.arena;
-    // memory hints (default on; PC_FASTSSC_HINTS=0..3 for measurements): bit 0 needs 32-byte aligned rows
-    static const int env_hints = getenv("PC_FASTSSC_HINTS") ? atoi(getenv("PC_FASTSSC_HINTS")) : 3;
-    kp.hints = (uint32_t)env_hints;
-    if ((reinterpret_cast<uintptr_t>(d_llr) & 31u) || L.S < 6) kp.hints &= ~5u;
     const bool cp = L.const_code >= 0 && L.const_runs >= 0;
     return cp ? launch_t<true>(L, kp, st) : launch_t<false>(L, kp, st);
 }

@@ -60,52 +60,7 @@ __device__ __forceinline__ void tm_ld1_nowait(uint32_t taddr, uint32_t& v)
 }
 __device__ __forceinline__ void tm_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tm_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
-// Channel row: the two adjacent 16-byte chunks of a batch as ONE 32-byte access (LDG.E.256), so that a thread consumes
-// whole 32-byte sectors and the row can be streamed past L1 and marked evict-first in L2 without costing the second
-// half-sector its hit. The row is read twice per frame (f at the root, g after the left half) and never again.
-__device__ __forceinline__ void ldg256_stream(const uint32_t* p, u4& a, u4& b)
-{
-    asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                 : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)
-                 : "l"(p));
-}
-// the same 32-byte access without cache hints (measurement variant: load width and policy separately)
-__device__ __forceinline__ void ldg256_plain(const uint32_t* p, u4& a, u4& b)
-{
-    asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                 : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)
-                 : "l"(p));
-}
-// Arena chunks (the per-thread LLR stages that do not fit on chip): kept in L2 with an evict-last policy so that the
-// streaming rows do not push them out to HBM.
-__device__ __forceinline__ u4 ldg128_keep(const uint32_t* p)
-{
-    u4 v;
-    unsigned long long pol;
-    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
-    asm volatile("ld.global.L2::cache_hint.v4.b32 {%0,%1,%2,%3}, [%4], %5;"
-                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
-                 : "l"(p), "l"(pol)
-                 : "memory");
-    return v;
-}
-__device__ __forceinline__ void stg128_keep(uint32_t* p, const u4& v)
-{
-    unsigned long long pol;
-    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
-    asm volatile("st.global.L2::cache_hint.v4.b32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w),
-                 "l"(pol)
-                 : "memory");
-}
 #else
-inline void ldg256_stream(const uint32_t* p, u4& a, u4& b)
-{
-    a = *reinterpret_cast<const u4*>(p);
-    b = *reinterpret_cast<const u4*>(p + 4);
-}
-inline void ldg256_plain(const uint32_t* p, u4& a, u4& b) { ldg256_stream(p, a, b); }
-inline u4 ldg128_keep(const uint32_t* p) { return *reinterpret_cast<const u4*>(p); }
-inline void stg128_keep(uint32_t* p, const u4& v) { *reinterpret_cast<u4*>(p) = v; }
 // host emulation (tests/host_emul.cpp): "tensor memory" is a plain array of columns, the address its index
 extern thread_local uint32_t* g_tm_emul;
 inline void tm_st4(uint32_t taddr, const u4& v)
@@ -122,14 +77,12 @@ inline void tm_wait_ld() {}
 inline void tm_wait_st() {}
 #endif
 
-enum : uint8_t { MH_NONE = 0, MH_ROW = 1, MH_ARENA = 2, MH_ROW_PLAIN = 3 };
 // One stage (or the channel row) as seen by one thread
 struct Mem {
     uint32_t* p;   // generic address of chunk 0 (shared, arena or channel row); unused for tensor memory
     int stride;    // words between consecutive chunks
     uint32_t tcol; // tensor-memory address of chunk 0
     bool tm;
-    uint8_t hint;  // MH_ROW: channel row, streamed with 32-byte loads; MH_ARENA: arena chunks, kept in L2; 0: plain
     PC_HD u4 ld4(int i) const
     { // general accessor (leaves); the hot loops below use the templated forms
         u4 v;
@@ -169,8 +122,6 @@ struct Ctx {
     uint32_t* bits;    // word 0 (shared or arena), stride bws
     size_t bws;
     uint32_t tbits;    // tensor-memory address of word 0
-    uint32_t hints;    // launch option: bit 0 stream the channel row (ldg256_stream), bit 1 keep the arena in L2,
-                       // bit 2 32-byte row loads without cache hints
 
     PC_HD Mem stage(int s) const
     {
@@ -179,11 +130,9 @@ struct Ctx {
         Mem m;
         m.tm = kind == PK_TMEM;
         m.tcol = tm + base;
-        m.hint = MH_NONE;
         if (kind == PK_ARENA) {
             m.p = ar + (size_t)base * acs;
             m.stride = (int)acs;
-            if (hints & 2u) m.hint = MH_ARENA;
         } else {
             m.p = sm + (size_t)base * scs;
             m.stride = scs;
@@ -245,6 +194,11 @@ PC_HD u4 ld_s5(const Ctx& c, int i) { return *reinterpret_cast<const u4*>(c.sm +
 //   BIG_G1  right child rate-1: decisions = sign(g), combine fused    ROneNode :427-449
 enum { BIG_F = 0, BIG_G = 1, BIG_G0 = 2, BIG_G1 = 3 };
 
+// Measured and NOT adopted (round 2, profiles/r02_fastssc_hints.txt): reading the two adjacent chunks of a channel-row
+// batch as one 32-byte LDG.E.256 (212 Gbit/s against 213 with the extra code path compiled in), the same with
+// L1::no_allocate + L2::evict_first (179: DRAM reads grow from 3.9 to 6.1 GB per 2^20 frames, because the second pass
+// over a row -- g after the left half -- otherwise still finds most of it in L2), and an L2 evict-last policy on the arena
+// chunks (212); merely compiling the three variants into this loop cost 8 % (231 -> 213) through instruction fetch.
 // ST / DT (source / destination in tensor memory) are warp-uniform RUN-TIME flags on purpose: one copy of the
 // arithmetic per OP keeps the hot code small. With the 16 specialised bodies (60-70 KB of hot SASS) the kernel's top
 // stall was instruction fetch (profiles/r01_fastssc_i8_full_v3.txt); this alone took N=1024 from 201 to 233 Gbit/s.
@@ -267,23 +221,10 @@ PC_HD void big_loop(const Ctx& c, const Mem& src, const Mem& dst, int s, int off
             tm_wait_ld();
         } else {
             const uint32_t* p = src.p + (size_t)(2 * j) * src.stride;
-            if (src.hint == MH_ROW) { // chunks 2j and 2j+1 of a row are 32 contiguous bytes
-                ldg256_stream(p, a0, a1);
-                ldg256_stream(p + (size_t)half * 4, b0, b1);
-            } else if (src.hint == MH_ROW_PLAIN) {
-                ldg256_plain(p, a0, a1);
-                ldg256_plain(p + (size_t)half * 4, b0, b1);
-            } else if (src.hint == MH_ARENA) {
-                a0 = ldg128_keep(p);
-                a1 = ldg128_keep(p + src.stride);
-                b0 = ldg128_keep(p + (size_t)half * src.stride);
-                b1 = ldg128_keep(p + (size_t)(half + 1) * src.stride);
-            } else {
-                a0 = *reinterpret_cast<const u4*>(p);
-                a1 = *reinterpret_cast<const u4*>(p + src.stride);
-                b0 = *reinterpret_cast<const u4*>(p + (size_t)half * src.stride);
-                b1 = *reinterpret_cast<const u4*>(p + (size_t)(half + 1) * src.stride);
-            }
+            a0 = *reinterpret_cast<const u4*>(p);
+            a1 = *reinterpret_cast<const u4*>(p + src.stride);
+            b0 = *reinterpret_cast<const u4*>(p + (size_t)half * src.stride);
+            b1 = *reinterpret_cast<const u4*>(p + (size_t)(half + 1) * src.stride);
         }
         u4 r0, r1;
         if (OP == BIG_F) {
@@ -306,13 +247,8 @@ PC_HD void big_loop(const Ctx& c, const Mem& src, const Mem& dst, int s, int off
             tm_st4(t + 4u, r1);
         } else {
             uint32_t* q = dst.p + (size_t)(2 * j) * dst.stride;
-            if (dst.hint == MH_ARENA) {
-                stg128_keep(q, r0);
-                stg128_keep(q + dst.stride, r1);
-            } else {
-                *reinterpret_cast<u4*>(q) = r0;
-                *reinterpret_cast<u4*>(q + dst.stride) = r1;
-            }
+            *reinterpret_cast<u4*>(q) = r0;
+            *reinterpret_cast<u4*>(q + dst.stride) = r1;
         }
     }
     if (DT && OP != BIG_G1) tm_wait_st();
@@ -776,7 +712,6 @@ PC_HD void fastssc_i8_run(Ctx& c, const uint32_t* code, const int8_t* row, bool 
     groot.stride = 4;
     groot.tcol = 0;
     groot.tm = false;
-    groot.hint = (c.hints & 1u) ? MH_ROW : ((c.hints & 4u) ? MH_ROW_PLAIN : MH_NONE);
     for (int pc = 0;; ++pc) {
         const uint32_t ins = code[pc];
         const uint32_t op = instr_op(ins);

@@ -28,6 +28,7 @@ struct pc_code {
     // encoder tables: info-bit scatter runs grouped by code word (pc_encode.cu)
     uint2* d_enc_runs = nullptr;      // unused since the encoder deposits bits from (mask, prefix count)
     uint32_t* d_enc_first = nullptr;  // number of info positions below each code word, N/32 + 1 entries
+    uint32_t* d_enc_tab = nullptr;    // pc_encode2.cu table (8 words per code word) for multi-warp codewords
     uint8_t* d_enc_info = nullptr;    // scratch copy of the info blocks when the detector writes check bytes
     size_t enc_info_bytes = 0;
     void* d_quant = nullptr;          // int8 LLRs quantised from a float batch

@@ -94,6 +94,9 @@ struct SclFParams {
     int arena_elems;  // arena floats per lane
     size_t arena_stride; // lanes the arena rows are laid out for (grid * threads)
     float* arena;     // [arena_elems][arena_stride]
+    // tensor memory for the decision words (offsets carry kTmem), see SclParams
+    int tm_alloc_cols, tm_cols_thread, scr_off, lockstep;
+    int virt_top;     // LLR stage S-1 is not stored: its consumers recompute it from the channel row (pc_scl_f32.cu FgSrc)
 };
 struct SclFLaunch {
     SclFParams p;
@@ -103,7 +106,8 @@ struct SclFLaunch {
 cudaError_t launch_scl_f32(const SclFLaunch& L, const float* d_llr, uint8_t* d_info, uint8_t* d_ok, size_t B,
                            const unsigned* d_frame_idx, const unsigned long long* d_count, cudaStream_t st);
 cudaError_t launch_compact_failed(const uint8_t* d_ok, size_t B, unsigned* d_idx, unsigned long long* d_count, cudaStream_t st);
-int plan_scl_f32(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, SclFLaunch& out, const char** msg);
+// virt_ok: no leaf of the node program sits at stage S-1, so that stage may be virtual
+int plan_scl_f32(int S, int K, int L, bool root_leaf, bool virt_ok, size_t smem_max, int sms, SclFLaunch& out, const char** msg);
 
 // ---- fp32 Fast-SSC (pc_fastssc_f32.cu) ----
 struct F32Params {

@@ -12,6 +12,7 @@
 //   ([element][lane], the lanes of a group are adjacent, so a step of all lanes is one coalesced transaction).
 // * Optional indirection (frame_idx / count) lets the adaptive decoder run this kernel over the frames whose first
 //   pass failed, without a host round trip (AdaptiveFloat::decode adaptive_float.cpp:33-45).
+#include <cstdio>
 #include <cstdlib>
 
 #include "pc_fastssc_f32_core.h"
@@ -20,25 +21,37 @@
 
 namespace pc {
 
-template <bool BA> // BA: some decision words live in the arena (long codes); off = no flag tests
+template <int BM> // BM_ARENA: some decision words live in the arena (long codes); BM_TMEM: in tensor memory; 0 = no flag tests
 struct FLaneT {
     uint32_t* sm;   // smem base + tid (word w at sm[w * T])
     float* ar;      // arena base + global lane id (element e at ar[e * AS])
     size_t AS;
+    uint32_t tm;    // tensor-memory address of this thread's column 0
     int T, G, l;    // threads per CTA, lanes per group, lane index inside the group
     int P;          // live paths (uniform)
     int smem_top;
+    int root_right; // virtual top stage: 0 while the left half of the root is decoded, 1 after the root's g step
     float metric;
     Tbl own_llr, own_L, own_R;
-    // decision words: shared memory, or the arena for the largest stages of long codes (flag in the offset)
+    // decision words: shared memory, tensor memory (warp-collective, see pc_scl_common.cuh kTmem), or the arena for the
+    // largest stages of long codes (flag in the offset)
     __device__ __forceinline__ uint32_t ld(int word, uint32_t owner) const
     {
-        if (BA && (word & kArena)) return reinterpret_cast<const uint32_t*>(ar)[(size_t)(word & (kArena - 1)) * AS + ((int)owner - l)];
+        if ((BM & BM_TMEM) && (word & kTmem)) {
+            uint32_t v;
+            tm_ld1_nowait(tm + (uint32_t)(word & 0xFFFF), v);
+            tm_wait_ld();
+            return __shfl_sync(0xFFFFFFFFu, v, (int)owner, G);
+        }
+        if ((BM & BM_ARENA) && (word & kArena)) return reinterpret_cast<const uint32_t*>(ar)[(size_t)(word & (kArena - 1)) * AS + ((int)owner - l)];
         return sm[(size_t)word * T + ((int)owner - l)];
     }
     __device__ __forceinline__ void st(int word, uint32_t v) const
     {
-        if (BA && (word & kArena))
+        if ((BM & BM_TMEM) && (word & kTmem)) {
+            tm_st1(tm + (uint32_t)(word & 0xFFFF), v);
+            tm_wait_st();
+        } else if ((BM & BM_ARENA) && (word & kArena))
             reinterpret_cast<uint32_t*>(ar)[(size_t)(word & (kArena - 1)) * AS] = v;
         else
             sm[(size_t)word * T] = v;
@@ -75,26 +88,84 @@ struct FLaneT {
 // _mm256_max_ps lane: returns the second operand unless a > b
 __device__ __forceinline__ float fmax_ps(float a, float b) { return a > b ? a : b; }
 
+// Source of an f / g step: a stored stage (view), the channel row (the root's own step), or -- with the VIRTUAL top
+// stage -- stage S-1 recomputed from the channel row on the fly: element i of stage S-1 is f(row[i], row[i + N/2]) while
+// the left half of the root is decoded and g(row[i], row[i + N/2], root-left decision i) afterwards. Stage S-1 is the
+// largest LLR buffer of a path (2 N bytes of the 4 N); not storing it halves the arena, which is what lets the arena
+// stay L2-resident (ncu r01/r02: 58x the algorithmic DRAM traffic with all stages >= 4 in a 233 MB arena).
+template <class FLane>
+struct FgSrc {
+    const FLane& c;
+    typename FLane::View v;
+    const float* row;
+    int mode;   // 0 view, 1 row, 2 virtual/left (f), 3 virtual/right (g)
+    int half;   // N / 2 (virtual modes)
+    int lbv;    // root-left decision words (virtual/right)
+    uint32_t olv;
+    uint32_t cache_w[2];
+    int cache_i[2];
+    __device__ __forceinline__ float get(int i, int which)
+    {
+        if (mode == 0) return v[i];
+        if (mode == 1) return __ldg(row + i);
+        const float a = __ldg(row + i), b = __ldg(row + i + half);
+        if (mode == 2) return f_f32(a, b);
+        return g_f32(a, b, (cache_w[which] >> (i & 31)) & 1u);
+    }
+    // warp-collective: fetch the root-left decision word that covers elements [i, i + 32) for stream `which`
+    __device__ __forceinline__ void bits_for(int i, int which)
+    {
+        if (mode == 3 && (i >> 5) != cache_i[which]) {
+            cache_i[which] = i >> 5;
+            cache_w[which] = c.ld(lbv + (i >> 5), olv);
+        }
+    }
+};
+
 template <bool IS_G, int UNR, class FLane>
-__device__ __forceinline__ void fg_block(const FLane& c, const float* row, const typename FLane::View& src, const typename FLane::View& dst, bool from_row,
-                                         int h, int lb, uint32_t ol)
+__device__ __forceinline__ void fg_block(const FLane& c, FgSrc<FLane>& src, const typename FLane::View& dst, bool active, int h, int lb, uint32_t ol)
 {
-    const bool row16 = from_row && ((reinterpret_cast<uintptr_t>(row) & 15u) == 0);
+    const bool row16 = src.mode == 1 && ((reinterpret_cast<uintptr_t>(src.row) & 15u) == 0);
     uint32_t bw = 0;
     for (int j = 0; j < h; j += UNR) {
         float a[UNR], b[UNR], r[UNR];
         if (row16) {
 #pragma unroll
             for (int u = 0; u < UNR; u += 4) {
-                const float4 va = __ldg(reinterpret_cast<const float4*>(row + j + u)), vb = __ldg(reinterpret_cast<const float4*>(row + h + j + u));
+                const float4 va = __ldg(reinterpret_cast<const float4*>(src.row + j + u)), vb = __ldg(reinterpret_cast<const float4*>(src.row + h + j + u));
                 a[u] = va.x, a[u + 1] = va.y, a[u + 2] = va.z, a[u + 3] = va.w;
                 b[u] = vb.x, b[u + 1] = vb.y, b[u + 2] = vb.z, b[u + 3] = vb.w;
             }
+        } else if (src.mode >= 2 && ((reinterpret_cast<uintptr_t>(src.row) & 15u) == 0)) {
+            // virtual stage S-1: four 16-byte row loads per four elements of each stream, then the root's f / g
+            src.bits_for(j, 0); // (uniform; no-ops before the root's g step)
+            src.bits_for(h + j, 1);
+#pragma unroll
+            for (int u = 0; u < UNR; u += 4) {
+                const float4 x0 = __ldg(reinterpret_cast<const float4*>(src.row + j + u));
+                const float4 x1 = __ldg(reinterpret_cast<const float4*>(src.row + j + u + src.half));
+                const float4 y0 = __ldg(reinterpret_cast<const float4*>(src.row + h + j + u));
+                const float4 y1 = __ldg(reinterpret_cast<const float4*>(src.row + h + j + u + src.half));
+                const float xa[4] = { x0.x, x0.y, x0.z, x0.w }, xb[4] = { x1.x, x1.y, x1.z, x1.w };
+                const float ya[4] = { y0.x, y0.y, y0.z, y0.w }, yb[4] = { y1.x, y1.y, y1.z, y1.w };
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    if (src.mode == 2) {
+                        a[u + k] = f_f32(xa[k], xb[k]);
+                        b[u + k] = f_f32(ya[k], yb[k]);
+                    } else {
+                        a[u + k] = g_f32(xa[k], xb[k], (src.cache_w[0] >> ((j + u + k) & 31)) & 1u);
+                        b[u + k] = g_f32(ya[k], yb[k], (src.cache_w[1] >> ((h + j + u + k) & 31)) & 1u);
+                    }
+                }
+            }
         } else {
+            src.bits_for(j, 0);
+            src.bits_for(h + j, 1);
 #pragma unroll
             for (int u = 0; u < UNR; ++u) {
-                a[u] = from_row ? __ldg(row + j + u) : src[j + u];
-                b[u] = from_row ? __ldg(row + h + j + u) : src[h + j + u];
+                a[u] = src.get(j + u, 0);
+                b[u] = src.get(h + j + u, 1);
             }
         }
         if (IS_G) {
@@ -105,44 +176,50 @@ __device__ __forceinline__ void fg_block(const FLane& c, const float* row, const
 #pragma unroll
             for (int u = 0; u < UNR; ++u) r[u] = f_f32(a[u], b[u]);
         }
+        if (active) {
 #pragma unroll
-        for (int u = 0; u < UNR; ++u) dst.set(j + u, r[u]);
+            for (int u = 0; u < UNR; ++u) dst.set(j + u, r[u]);
+        }
     }
 }
 
-// f / g step of a node of size 2^s (RateRNode::decode scl_avx_float.cpp:238-262)
+// f / g step of a node of size 2^s (RateRNode::decode scl_avx_float.cpp:238-262). Every lane runs the step (decision
+// words may sit in tensor memory, whose loads are warp-collective); dead lanes only skip their stores.
 template <bool IS_G, class FLane>
 __device__ __forceinline__ void sclf_fg(FLane& c, const SclFParams& p, int s, const float* row)
 {
     const bool active = c.l < c.P;
     const int h = 1 << (s - 1);
     const bool from_row = (s == p.S) && !p.root_leaf;
+    if (from_row && p.virt_top) { // the root's f / g results are never stored: their consumers recompute them
+        c.root_right = IS_G ? 1 : 0;
+        c.own_llr.set(s - 1, (uint32_t)c.l);
+        return;
+    }
     const uint32_t o = c.own_llr.get(s), ol = c.own_L.get(s - 1);
     const int lb = p.bitL_off[s - 1];
-    const typename FLane::View src = from_row ? c.view(s - 1, p.llr_off[s - 1], (uint32_t)c.l) : c.view(s, p.llr_off[s], o);
+    const bool virt = p.virt_top && s == p.S - 1;
+    FgSrc<FLane> src{ c, (from_row || virt) ? c.view(s - 1, p.llr_off[s - 1], (uint32_t)c.l) : c.view(s, p.llr_off[s], o), row,
+                      from_row ? 1 : (virt ? 2 + c.root_right : 0), 1 << (p.S - 1), p.bitL_off[p.S - 1], c.own_L.get(p.S - 1),
+                      { 0u, 0u }, { -1, -1 } };
     const typename FLane::View dst = c.view(s - 1, p.llr_off[s - 1], (uint32_t)c.l);
-    if (active) {
+    if (h >= 4) {
+        // UNR elements per step, all loads first (source and destination may alias as far as the compiler knows, so
+        // a rolled loop serialises load -> f/g -> store; the big stages live in the L2 arena and want many loads in
+        // flight); the channel row as 16-byte loads
+        if (h >= 8)
+            fg_block<IS_G, 8>(c, src, dst, active, h, lb, ol);
+        else
+            fg_block<IS_G, 4>(c, src, dst, active, h, lb, ol);
+    } else {
         uint32_t bw = 0;
-        if (h >= 4) {
-            // UNR elements per step, all loads first (source and destination may alias as far as the compiler knows, so
-            // a rolled loop serialises load -> f/g -> store; the big stages live in the L2 arena and want many loads in
-            // flight); the channel row as 16-byte loads
-            if (h >= 8)
-                fg_block<IS_G, 8>(c, row, src, dst, from_row, h, lb, ol);
-            else
-                fg_block<IS_G, 4>(c, row, src, dst, from_row, h, lb, ol);
-        } else
+        if (IS_G) bw = c.ld(lb, ol);
         for (int j = 0; j < h; ++j) {
-            const float a = from_row ? __ldg(row + j) : src[j];
-            const float b = from_row ? __ldg(row + h + j) : src[h + j];
-            float r;
-            if (IS_G) {
-                if ((j & 31) == 0) bw = c.ld(lb + (j >> 5), ol);
-                r = g_f32(a, b, (bw >> (j & 31)) & 1u);
-            } else {
-                r = f_f32(a, b);
-            }
-            dst.set(j, r);
+            src.bits_for(j, 0);
+            src.bits_for(h + j, 1);
+            const float a = src.get(j, 0), b = src.get(h + j, 1);
+            const float r = IS_G ? g_f32(a, b, (bw >> (j & 31)) & 1u) : f_f32(a, b);
+            if (active) dst.set(j, r);
         }
     }
     c.own_llr.set(s - 1, (uint32_t)c.l);
@@ -179,13 +256,11 @@ __device__ __forceinline__ void sclf_sums(const FLane& c, const SclFParams& p, i
 template <class FLane>
 __device__ __forceinline__ void sclf_r0(FLane& c, const SclFParams& p, int s, int side)
 {
-    if (c.l < c.P) {
-        float neg, pos, all;
-        sclf_sums<false>(c, p, s, neg, pos, all);
-        c.metric = fadd(c.metric, neg);
-        const int dst = side ? p.bitR_off[s] : p.bitL_off[s], nb = stage_bwords(s);
-        for (int j = 0; j < nb; ++j) c.st(dst + j, 0u);
-    }
+    float neg, pos, all; // every lane runs (dead lanes: garbage into their own state, replaced at the next fork)
+    sclf_sums<false>(c, p, s, neg, pos, all);
+    c.metric = fadd(c.metric, neg);
+    const int dst = side ? p.bitR_off[s] : p.bitL_off[s], nb = stage_bwords(s);
+    for (int j = 0; j < nb; ++j) c.st(dst + j, 0u);
     set_side(c, s, side);
 }
 
@@ -269,9 +344,9 @@ template <class FLane>
 __device__ __forceinline__ void sclf_rep(FLane& c, const SclFParams& p, int s, int side)
 {
     float v[2] = { -INFINITY, -INFINITY };
+    float neg, pos, all;
+    sclf_sums<true>(c, p, s, neg, pos, all);
     if (c.l < c.P) {
-        float neg, pos, all;
-        sclf_sums<true>(c, p, s, neg, pos, all);
         v[0] = fadd(c.metric, neg);
         v[1] = fadd(c.metric, -pos);
     }
@@ -282,12 +357,10 @@ __device__ __forceinline__ void sclf_rep(FLane& c, const SclFParams& p, int s, i
     const bool live = c.l < newP;
     const int sp = live ? idx >> 1 : 0;
     scl_fork(c, sp, val, newP);
-    if (live) {
-        // decisions: +|sum| for candidate 0, -|sum| for candidate 1 -> the sign is the candidate's parity
-        const int dst = side ? p.bitR_off[s] : p.bitL_off[s], nb = stage_bwords(s);
-        const uint32_t fill = (idx & 1) ? 0xFFFFFFFFu : 0u;
-        for (int j = 0; j < nb; ++j) c.st(dst + j, fill);
-    }
+    // decisions: +|sum| for candidate 0, -|sum| for candidate 1 -> the sign is the candidate's parity (all lanes store)
+    const int dst = side ? p.bitR_off[s] : p.bitL_off[s], nb = stage_bwords(s);
+    const uint32_t fill = (idx & 1) ? 0xFFFFFFFFu : 0u;
+    for (int j = 0; j < nb; ++j) c.st(dst + j, fill);
     set_side(c, s, side);
 }
 
@@ -298,9 +371,9 @@ __device__ __forceinline__ void sclf_r1(FLane& c, const SclFParams& p, int s, in
     float v[4] = { -INFINITY, -INFINITY, -INFINITY, -INFINITY };
     int wi[4] = { 0, 0, 0, 0 };
     float wv[4];
+    sclf_signs_and_abs(c, p, s, side);
+    sclf_find_weak(c, s, p.llr_off[s], 2, wi, wv);
     if (c.l < c.P) {
-        sclf_signs_and_abs(c, p, s, side);
-        sclf_find_weak(c, s, p.llr_off[s], 2, wi, wv);
         v[0] = c.metric;
         v[1] = fadd(c.metric, -wv[0]);
         v[2] = fadd(c.metric, -wv[1]);
@@ -332,10 +405,9 @@ __device__ __forceinline__ void sclf_spc(FLane& c, const SclFParams& p, int s, i
     for (int k = 0; k < 8; ++k) v[k] = -INFINITY;
     int wi[4] = { 0, 0, 0, 0 };
     float wv[4];
-    int parity = 0;
+    const int parity = (int)sclf_signs_and_abs(c, p, s, side);
+    sclf_find_weak(c, s, p.llr_off[s], 4, wi, wv);
     if (c.l < c.P) {
-        parity = (int)sclf_signs_and_abs(c, p, s, side);
-        sclf_find_weak(c, s, p.llr_off[s], 4, wi, wv);
         // odd parity: the weakest bit is flipped in every candidate's base and its cost is already in `m`
         const float m = parity ? fadd(c.metric, -wv[0]) : c.metric;
         const float w = parity ? 0.0f : wv[0];
@@ -367,20 +439,32 @@ __device__ __forceinline__ void sclf_spc(FLane& c, const SclFParams& p, int s, i
     set_side(c, s, side);
 }
 
-template <bool BA>
-__global__ void __launch_bounds__(128) k_scl_f32(const __grid_constant__ SclFParams p)
+template <int BM>
+__global__ void __launch_bounds__(384, 1) k_scl_f32(const __grid_constant__ SclFParams p)
 {
-    using FLane = FLaneT<BA>;
+    using FLane = FLaneT<BM>;
     extern __shared__ __align__(16) uint32_t smem[];
-    const int T = blockDim.x, t = threadIdx.x;
+    __shared__ uint32_t tm_base_s;
+    const int T = blockDim.x, t = threadIdx.x, warp = t >> 5;
     uint32_t* crc_table = smem; // 256 words
     if (p.crc.width)
         for (int i = t; i < 256; i += T) crc_table[i] = p.crc_table[i];
+    if (BM & BM_TMEM) {
+        if (warp == 0) {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                             (uint32_t)__cvta_generic_to_shared(&tm_base_s)),
+                         "r"((uint32_t)p.tm_alloc_cols));
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;");
+    }
     __syncthreads();
+    if (BM & BM_TMEM) asm volatile("tcgen05.fence::after_thread_sync;");
     FLane c;
     c.sm = smem + 256 + t;
     c.ar = p.arena + ((size_t)blockIdx.x * T + t);
     c.AS = p.arena_stride;
+    c.tm = (BM & BM_TMEM) ? tm_base_s + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)((warp >> 2) * p.tm_cols_thread) : 0u;
     c.T = T;
     c.G = p.G;
     c.l = t & (p.G - 1);
@@ -389,8 +473,7 @@ __global__ void __launch_bounds__(128) k_scl_f32(const __grid_constant__ SclFPar
     const int N = 1 << p.S, kb = (p.K + 7) >> 3;
     const unsigned gmask = (p.G == 32 ? 0xFFFFFFFFu : ((1u << p.G) - 1u)) << ((t & 31) & ~(p.G - 1));
     const unsigned long long B = p.count ? *p.count : p.B;
-    if (B == 0) return;
-    const unsigned long long nbatch = (B + gpc - 1) / gpc;
+    const unsigned long long nbatch = (B + gpc - 1) / gpc; // 0 when there is nothing to do: straight to the dealloc
     for (unsigned long long bi = blockIdx.x; bi < nbatch; bi += gridDim.x) {
         const unsigned long long fl = bi * gpc + (unsigned long long)(t / p.G);
         const bool live_frame = fl < B;
@@ -399,6 +482,7 @@ __global__ void __launch_bounds__(128) k_scl_f32(const __grid_constant__ SclFPar
         const float* row = p.llr + f * N;
         c.P = 1;
         c.metric = 0.0f;
+        c.root_right = 0;
         c.own_llr = Tbl{ { 0u, 0u, 0u } };
         c.own_L = c.own_llr;
         c.own_R = c.own_llr;
@@ -419,32 +503,39 @@ __global__ void __launch_bounds__(128) k_scl_f32(const __grid_constant__ SclFPar
             case SCL_REP: sclf_rep(c, p, s, side); break;
             default: sclf_spc(c, p, s, side); break;
             }
-            __syncwarp(); // other lanes' buffers are read by the next step
+            // other lanes' buffers are read by the next step; `lockstep` keeps the CTA's warps on the same program step
+            // (the kernel is ~90 KB of SASS; free-running warps thrash the instruction caches, see pc_scl_i8.cu)
+            if (p.lockstep)
+                __syncthreads();
+            else
+                __syncwarp();
         }
         // extractBestPath (scl_avx_float.cpp:706-748)
         const bool active = c.l < c.P;
         const int top = p.bitR_off[p.S], nbw = stage_bwords(p.S);
         uint32_t owner = c.own_R.get(p.S);
         int off = top;
-        if (!p.systematic) {
-            // u = x F^(x)n on a private copy (the left buffer of the top stage is free at this point)
-            const int scr = p.bitL_off[p.S];
-            if (active) {
-                const uint32_t lim = lowmask(1 << (p.S < 5 ? p.S : 5));
-                for (int w = 0; w < nbw; ++w) {
-                    uint32_t x = c.ld(top + w, owner);
+        if (!p.systematic || (top & kTmem)) {
+            // private copy of the path's decisions in the lane's shared-memory scratch (every lane: the reads may be
+            // warp-collective); non-systematic: u = x F^(x)n on that copy
+            const int scr = p.scr_off;
+            const uint32_t lim = lowmask(1 << (p.S < 5 ? p.S : 5));
+            for (int w = 0; w < nbw; ++w) {
+                uint32_t x = c.ld(top + w, owner);
+                if (!p.systematic) {
                     x ^= (x >> 1) & 0x55555555u & lim;
                     if (p.S > 1) x ^= (x >> 2) & 0x33333333u & lim;
                     if (p.S > 2) x ^= (x >> 4) & 0x0F0F0F0Fu & lim;
                     if (p.S > 3) x ^= (x >> 8) & 0x00FF00FFu & lim;
                     if (p.S > 4) x ^= (x >> 16) & 0x0000FFFFu;
-                    c.st(scr + w, x);
                 }
+                c.st(scr + w, x);
+            }
+            if (!p.systematic)
                 for (int d = 1; d < nbw; d <<= 1)
                     for (int g = 0; g < nbw; g += 2 * d)
                         for (int i = g; i < g + d; ++i)
                             c.st(scr + i, c.ld(scr + i, (uint32_t)c.l) ^ c.ld(scr + i + d, (uint32_t)c.l));
-            }
             owner = (uint32_t)c.l;
             off = scr;
         }
@@ -460,6 +551,12 @@ __global__ void __launch_bounds__(128) k_scl_f32(const __grid_constant__ SclFPar
         }
         __syncwarp();
     }
+    if (BM & BM_TMEM) {
+        asm volatile("tcgen05.fence::before_thread_sync;");
+        __syncthreads();
+        if (warp == 0)
+            asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tm_base_s), "r"((uint32_t)p.tm_alloc_cols));
+    }
 }
 
 cudaError_t launch_scl_f32(const SclFLaunch& L, const float* d_llr, uint8_t* d_info, uint8_t* d_ok, size_t B,
@@ -472,9 +569,9 @@ cudaError_t launch_scl_f32(const SclFLaunch& L, const float* d_llr, uint8_t* d_i
     p.B = B;
     p.frame_idx = d_frame_idx;
     p.count = d_count;
-    // decision words in the arena (long codes) -> the instantiation whose ld / st test the offset flag
+    // decision words in the arena (long codes) or in tensor memory -> the instantiation whose ld / st test that flag
     const bool ba = (p.bitR_off[p.S] & kArena) != 0;
-    void (*kern)(SclFParams) = ba ? k_scl_f32<true> : k_scl_f32<false>;
+    void (*kern)(SclFParams) = p.tm_alloc_cols ? k_scl_f32<BM_TMEM> : (ba ? k_scl_f32<BM_ARENA> : k_scl_f32<BM_SMEM>);
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes);
     // several CTAs per SM only fit when the L1/shared split is at its shared-memory maximum; a single CTA keeps the
     // default split (the rest stays L1 for the channel rows and the arena)
@@ -482,6 +579,13 @@ cudaError_t launch_scl_f32(const SclFLaunch& L, const float* d_llr, uint8_t* d_i
         e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout,
                                  L.per_sm > 1 ? (int)cudaSharedmemCarveoutMaxShared : (int)cudaSharedmemCarveoutDefault);
     if (e != cudaSuccess) return e;
+    static const bool debug_occ = getenv("PC_DEBUG_OCC") != nullptr;
+    if (debug_occ) {
+        int occ = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, L.threads, L.smem_bytes);
+        fprintf(stderr, "k_scl_f32: %d threads, %zu B smem, grid %d, tmem cols %d, virt_top %d, smem_top %d, arena elems %d, occupancy %d\n",
+                L.threads, L.smem_bytes, L.grid, p.tm_alloc_cols, p.virt_top, p.smem_top, p.arena_elems, occ);
+    }
     const int gpc = L.threads / p.G;
     size_t nb = (B + gpc - 1) / gpc;
     const int grid = (int)(nb < (size_t)L.grid ? nb : (size_t)L.grid);
@@ -490,7 +594,7 @@ cudaError_t launch_scl_f32(const SclFLaunch& L, const float* d_llr, uint8_t* d_i
 }
 
 // host planner: which LLR stages fit shared memory, CTA size and CTAs per SM
-int plan_scl_f32(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, SclFLaunch& out, const char** msg)
+static int plan_scl_f32_smem(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, SclFLaunch& out, const char** msg)
 {
     if (L < 1 || L > 32) {
         *msg = "list size must be in [1, 32]";
@@ -583,6 +687,11 @@ int plan_scl_f32(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, 
     p.words = w;
     p.smem_top = smem_top;
     p.arena_elems = e;
+    p.tm_alloc_cols = 0;
+    p.tm_cols_thread = 0;
+    p.scr_off = p.bitL_off[S]; // non-systematic extraction works on the (free) left buffer of the top stage
+    p.lockstep = getenv("PC_SCL_LOCKSTEP") ? atoi(getenv("PC_SCL_LOCKSTEP")) != 0 : 0;
+    p.virt_top = 0;
     out.threads = T;
     out.smem_bytes = 1024 + 4 * (size_t)w * T;
     out.grid = sms * per_sm;
@@ -591,6 +700,103 @@ int plan_scl_f32(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, 
     while (out.grid > sms && (size_t)4 * e * out.grid * T > ((size_t)1 << 30)) out.grid -= sms;
     p.arena_stride = (size_t)out.grid * T;
     return 0;
+}
+
+// Planner, first choice: ONE CTA of T lanes per SM whose warps stay in step, all decision words in TENSOR MEMORY (which
+// frees 136 shared-memory words per lane at N = 1024 for LLR stages), LLR stage S-1 virtual (recomputed from the channel
+// row) and only the stage(s) that still do not fit in an arena small enough to stay in L2:
+//   N = 1024, T = 256: stages <= 6 in shared memory, stages 7 and 8 in a 58 MB arena (was: stages >= 4, 233 MB);
+//   T = 224: stages <= 7 in shared memory, 34 MB arena.
+// PC_SCLF_T picks T (multiple of 32 and of the group size), PC_SCLF_VIRT=0 stores stage S-1, PC_SCL_NOTMEM=1 or
+// PC_SCLF_THREADS / PC_SCLF_CTAS fall back to the shared-memory planner above.
+int plan_scl_f32(int S, int K, int L, bool root_leaf, bool virt_ok, size_t smem_max, int sms, SclFLaunch& out, const char** msg)
+{
+    if (L < 1 || L > 32) {
+        *msg = "list size must be in [1, 32]";
+        return 1;
+    }
+    const bool no_tmem = getenv("PC_SCL_NOTMEM") != nullptr || getenv("PC_SCLF_THREADS") != nullptr || getenv("PC_SCLF_CTAS") != nullptr;
+    int G = 1;
+    while (G < L) G <<= 1;
+    int T = 256;
+    if (const char* e = getenv("PC_SCLF_T")) T = atoi(e);
+    if (T < 32 || T > 384 || (T % 32) != 0 || (T % G) != 0) T = 256;
+    const bool lockstep = getenv("PC_SCL_LOCKSTEP") ? atoi(getenv("PC_SCL_LOCKSTEP")) != 0 : true;
+    bool virt = virt_ok && !root_leaf && S >= 7;
+    if (const char* e = getenv("PC_SCLF_VIRT")) virt = virt && atoi(e) != 0;
+    const int top_llr = root_leaf ? S : S - 1;
+    // (short codes keep their whole tree in shared memory with up to 1024 lanes per SM: the planner above)
+    if (!no_tmem && S >= 9 && S <= 13) {
+        const int tm_alloc = 512, tm_cols = tm_alloc / ((T / 32 + 3) / 4);
+        size_t per_cta = 233472 - 1024;
+        if (per_cta > smem_max) per_cta = smem_max;
+        const long budget = ((long)per_cta - 1024 - 64) / (4L * T); // shared-memory words per lane
+        SclFParams& p = out.p;
+        for (int s = 0; s < 20; ++s) p.llr_off[s] = p.bitL_off[s] = p.bitR_off[s] = 0;
+        int tcol = 0, tm_lo = S + 1;
+        for (int s = S; s >= 0; --s) { // decision buffers, top stage first, into tensor memory while they fit
+            const int bw = s >= 5 ? (1 << (s - 5)) : 1;
+            if (tcol + 2 * bw > tm_cols) break;
+            p.bitL_off[s] = kTmem | tcol;
+            tcol += bw;
+            p.bitR_off[s] = kTmem | tcol;
+            tcol += bw;
+            tm_lo = s;
+        }
+        int w = 0;
+        for (int s = 0; s < tm_lo; ++s) {
+            const int bw = s >= 5 ? (1 << (s - 5)) : 1;
+            p.bitL_off[s] = w;
+            w += bw;
+            p.bitR_off[s] = w;
+            w += bw;
+        }
+        int e = 0, smem_top = -1;
+        bool open = true;
+        for (int s = 0; s <= top_llr; ++s) {
+            if (virt && s == S - 1) continue; // never stored
+            if (open && w + (1 << s) <= budget) {
+                p.llr_off[s] = w;
+                w += 1 << s;
+                smem_top = s;
+            } else {
+                open = false;
+                p.llr_off[s] = e;
+                e += 1 << s;
+            }
+        }
+        // scratch of N/32 words for extractBestPath: LLR stage S-5 has exactly that size and is dead by then
+        const int nbw = S >= 5 ? (1 << (S - 5)) : 1;
+        int scr = -1;
+        if (S - 5 >= 0 && S - 5 <= smem_top) {
+            scr = p.llr_off[S - 5];
+        } else if (w + nbw <= budget) {
+            scr = w;
+            w += nbw;
+        }
+        if (w <= budget && tm_lo <= S && scr >= 0 && smem_top >= (top_llr < 4 ? top_llr : 4)) {
+            p.S = S;
+            p.K = K;
+            p.L = L;
+            p.G = G;
+            p.root_leaf = root_leaf ? 1 : 0;
+            p.words = w;
+            p.smem_top = smem_top;
+            p.arena_elems = e;
+            p.tm_alloc_cols = tm_alloc;
+            p.tm_cols_thread = tm_cols;
+            p.scr_off = scr;
+            p.lockstep = lockstep ? 1 : 0;
+            p.virt_top = virt ? 1 : 0;
+            out.threads = T;
+            out.smem_bytes = 1024 + 4 * (size_t)w * T;
+            out.grid = sms;
+            out.per_sm = 1;
+            p.arena_stride = (size_t)out.grid * T;
+            return 0;
+        }
+    }
+    return plan_scl_f32_smem(S, K, L, root_leaf, smem_max, sms, out, msg);
 }
 
 } // namespace pc

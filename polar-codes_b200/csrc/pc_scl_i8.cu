@@ -715,7 +715,7 @@ int plan_scl_i8(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, S
     const int per_sm = 512 / T, tm_alloc = 512 / per_sm, tm_cols = tm_alloc / ((T / 32 + 3) / 4); // 128 columns per thread
     const bool lockstep = getenv("PC_SCL_LOCKSTEP") ? atoi(getenv("PC_SCL_LOCKSTEP")) != 0 : true;
     const int top_llr = root_leaf ? S : S - 1;
-    if (!no_tmem && S >= 6 && S <= 15) {
+    if (!no_tmem && S >= 8 && S <= 15) { // shorter codes fit shared memory whole (planner above)
         size_t per_cta = 233472 / (size_t)per_sm - 1024;
         if (per_cta > smem_max) per_cta = smem_max;
         const long budget = ((long)per_cta - 1024 - 64) / (4L * T); // shared-memory words per lane

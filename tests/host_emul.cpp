@@ -67,7 +67,6 @@ int emul_fastssc_i8_decode_mode(int N, const unsigned* frozen, int nf, int syste
         c.bits = bits.data();
         c.bws = 1;
         c.tbits = (uint32_t)(4 * nchunks);
-        c.hints = 3u; // exercise the streamed-row and kept-arena paths (plain loads on the host)
         fastssc_i8_run(c, p.code.data(), reinterpret_cast<const int8_t*>(rowbuf.data()), p.staged_root);
         if (!systematic) transform_bits_inplace(c);
         bool res = extract_info(c, p.runs.data(), (int)p.runs.size(), p.K, outrow.data(), crc, table);

@@ -106,3 +106,34 @@ def test_encoder_at_scale(pcb, ref, N, K, rows, crc, systematic):
     exp, _ = ref.encode_batch(N, np.array(fz, np.uint32), info, crc_bits=crc, systematic=systematic,
                               threads=os.cpu_count() or 1)
     assert np.array_equal(got, exp), f"{int((got != exp).any(axis=1).sum())} code words differ"
+
+
+@pytest.mark.parametrize("crc,typ", [(6, "crcnr"), (8, "crc"), (11, "crcnr"), (16, "crc"), (16, "crcnr"), (24, "crc"), (32, "crc")])
+@pytest.mark.parametrize("N,K", [(1024, 512), (256, 128), (64, 40), (512, 264), (32, 16)])
+def test_encoder_fused_detector(pcb, ref, crc, typ, N, K):
+    """pc_encode_batch without the info-copy output: for N <= 1024 the detector's generate runs INSIDE the encoder kernel
+    on the staged rows (pc_encode2.cu). Same code words as the reference's generate-then-encode."""
+    import torch
+    kb = (K + 7) // 8
+    cb = {6: 1, 8: 1, 11: 2, 16: 2, 24: 3, 32: 4}[crc]
+    if crc == 32 and kb % 4:
+        pytest.skip("CRC-32C needs whole words (crc32.cpp)")
+    if kb <= cb:
+        pytest.skip("block shorter than the checksum")
+    rng = np.random.default_rng(N + crc)
+    fz = pcb.frozen_bits(N, K, 0.0)
+    B = 3000
+    info = rng.integers(0, 256, (B, kb), dtype=np.uint8)
+    for systematic in (True, False):
+        enc = pcb.PolarEncoder(N, fz)
+        enc.setErrorDetection(crc, typ)
+        enc.setSystematic(systematic)
+        d_info = torch.from_numpy(info).cuda()
+        d_code = torch.empty((B, N // 8), dtype=torch.uint8, device="cuda")
+        L_, ptr, check = pcb.capi.lib(), pcb.capi.ptr, pcb.capi.check
+        check(L_.pc_encode_batch(enc._h, ptr(d_info), ptr(d_code), None, B, None))
+        torch.cuda.synchronize()
+        exp, _ = ref.encode_batch(N, np.array(fz, np.uint32), info, crc_bits=crc, crc_type=typ, systematic=systematic,
+                                  threads=os.cpu_count() or 1)
+        assert np.array_equal(d_code.cpu().numpy(), exp), f"systematic={systematic}"
+        assert np.array_equal(d_info.cpu().numpy(), info)  # the caller's blocks stay untouched

@@ -1,8 +1,9 @@
 """The reference's own python QA suites, run UNCHANGED against the mirror ("they become the first
 acceptance tests of the replacement"): qa_pypolar_{decoder,encoder,detector,puncturer}.py are copied by oracle/Makefile
 from the reference tree into oracle/_ref/qa/ (git-ignored, travels to the GPU box); here `pypolar` resolves to the B200
-mirror (the top-level pypolar/ package) and every test case must pass. The one expected failure is
-test_007_scan_decoder: the 'scan' kind is out of scope and rejected like an unknown kind (no CPU fallback).
+mirror (the top-level pypolar/ package) and every test case must pass. Expected failures, all out-of-scope kinds that
+are refused with an error instead of falling back to the CPU: test_007_scan_decoder ('scan' decoder) and the two
+detector cases that construct a CMAC (test_001_init, test_006_cmac).
 """
 import importlib
 import os
@@ -35,7 +36,8 @@ def _run(module_name):
 
 
 def _names(items):
-    return sorted(str(t).split()[0] for t, _ in items)
+    """names of the failing test METHODS (a method that fails in several subTests counts once)"""
+    return sorted({str(t).split()[0] for t, _ in items})
 
 
 def test_qa_pypolar_decoder_unchanged():
@@ -56,7 +58,9 @@ def test_qa_pypolar_encoder_unchanged():
 def test_qa_pypolar_detector_unchanged():
     """python/qa_pypolar_detector.py:51-442: every CRC literal incl. CRC-6 0x15/0x02/0x2f, CRC-11 0x06c8, 35-bit 0x1fb065"""
     res = _run("qa_pypolar_detector")
-    assert _names(res.failures + res.errors) == []
+    # the two cases that construct a CMAC detector (AES-CMAC through OpenSSL: host-side crypto, out of scope per SURVEY.md
+    # section 2 row 9b, refused with an error) are the only expected failures; all thirteen CRC cases must pass
+    assert _names(res.failures + res.errors) == ["test_001_init", "test_006_cmac"]
     assert res.testsRun >= 15
 
 
