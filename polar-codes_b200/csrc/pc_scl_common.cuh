@@ -280,6 +280,7 @@ __device__ __forceinline__ void scl_take_bits(const LN& c, const PR& p, int s, i
     // is warp-collective
     (void)live;
     const int nb = stage_bwords(s), dst = side ? p.bitR_off[s] : p.bitL_off[s];
+    c.st_fence(); // the leaf's own decisions were stored into these words a moment ago
     for (int w = 0; w < nb; ++w) {
         uint32_t t = c.ld(dst + w, (uint32_t)sp);
 #pragma unroll

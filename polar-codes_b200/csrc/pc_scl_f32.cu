@@ -21,8 +21,20 @@
 
 namespace pc {
 
-template <int BM> // BM_ARENA: some decision words live in the arena (long codes); BM_TMEM: in tensor memory; 0 = no flag tests
+__device__ __forceinline__ float lds_f32(uint32_t a)
+{
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ void sts_f32(uint32_t a, float v) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v) : "memory"); }
+
+// BM_ARENA: some decision words live in the arena (long codes); BM_TMEM: in tensor memory; 0 = no flag tests.
+// TT: threads per CTA as a compile-time constant (0 = run-time): the lane-interleaved shared-memory layout puts element i
+// of a stage at byte offset 4 TT i of the lane's column, which is an immediate of the load when i and TT are known
+template <int BM, int TT>
 struct FLaneT {
+    static constexpr int kTT = TT;
     uint32_t* sm;   // smem base + tid (word w at sm[w * T])
     float* ar;      // arena base + global lane id (element e at ar[e * AS])
     size_t AS;
@@ -49,12 +61,17 @@ struct FLaneT {
     __device__ __forceinline__ void st(int word, uint32_t v) const
     {
         if ((BM & BM_TMEM) && (word & kTmem)) {
-            tm_st1(tm + (uint32_t)(word & 0xFFFF), v);
-            tm_wait_st();
+            tm_st1(tm + (uint32_t)(word & 0xFFFF), v); // completion is awaited by st_fence(), once per step
         } else if ((BM & BM_ARENA) && (word & kArena))
             reinterpret_cast<uint32_t*>(ar)[(size_t)(word & (kArena - 1)) * AS] = v;
         else
             sm[(size_t)word * T] = v;
+    }
+    // tensor-memory stores complete: called before a step re-reads columns it wrote (scl_take_bits after the leaf's own
+    // decisions) and at the end of every node-program step
+    __device__ __forceinline__ void st_fence() const
+    {
+        if (BM & BM_TMEM) tm_wait_st();
     }
     // LLR stage s (off = p.llr_off[s]) in lane `owner`'s space, resolved once per node step
     struct View {
@@ -203,7 +220,34 @@ __device__ __forceinline__ void sclf_fg(FLane& c, const SclFParams& p, int s, co
                       from_row ? 1 : (virt ? 2 + c.root_right : 0), 1 << (p.S - 1), p.bitL_off[p.S - 1], c.own_L.get(p.S - 1),
                       { 0u, 0u }, { -1, -1 } };
     const typename FLane::View dst = c.view(s - 1, p.llr_off[s - 1], (uint32_t)c.l);
-    if (h >= 4) {
+    if (FLane::kTT && h >= 8 && src.mode == 0 && s <= c.smem_top) {
+        // both stages in shared memory and the CTA size known at compile time: 32-bit shared addresses whose element
+        // offsets are immediates (the generic path below spends a 64-bit multiply-add and a generic load per element:
+        // a third of all executed instructions in ncu r02_scl_f32_v1)
+        constexpr uint32_t ES = 4u * (uint32_t)FLane::kTT;
+        const uint32_t sa = (uint32_t)__cvta_generic_to_shared(c.sm) + ES * (uint32_t)p.llr_off[s] + 4u * (uint32_t)((int)o - c.l);
+        const uint32_t da = (uint32_t)__cvta_generic_to_shared(c.sm) + ES * (uint32_t)p.llr_off[s - 1];
+        uint32_t bw = 0;
+        for (int j = 0; j < h; j += 8) {
+            float a[8], b[8], r[8];
+            const uint32_t ja = sa + ES * (uint32_t)j, jb = ja + ES * (uint32_t)h;
+#pragma unroll
+            for (int u = 0; u < 8; ++u) a[u] = lds_f32(ja + ES * u), b[u] = lds_f32(jb + ES * u);
+            if (IS_G) {
+                if ((j & 31) == 0) bw = c.ld(lb + (j >> 5), ol);
+#pragma unroll
+                for (int u = 0; u < 8; ++u) r[u] = g_f32(a[u], b[u], (bw >> ((j & 31) + u)) & 1u);
+            } else {
+#pragma unroll
+                for (int u = 0; u < 8; ++u) r[u] = f_f32(a[u], b[u]);
+            }
+            if (active) {
+                const uint32_t jd = da + ES * (uint32_t)j;
+#pragma unroll
+                for (int u = 0; u < 8; ++u) sts_f32(jd + ES * u, r[u]);
+            }
+        }
+    } else if (h >= 4) {
         // UNR elements per step, all loads first (source and destination may alias as far as the compiler knows, so
         // a rolled loop serialises load -> f/g -> store; the big stages live in the L2 arena and want many loads in
         // flight); the channel row as 16-byte loads
@@ -439,10 +483,10 @@ __device__ __forceinline__ void sclf_spc(FLane& c, const SclFParams& p, int s, i
     set_side(c, s, side);
 }
 
-template <int BM>
-__global__ void __launch_bounds__(384, 1) k_scl_f32(const __grid_constant__ SclFParams p)
+template <int BM, int TT>
+__global__ void __launch_bounds__(TT ? TT : 384, 1) k_scl_f32(const __grid_constant__ SclFParams p)
 {
-    using FLane = FLaneT<BM>;
+    using FLane = FLaneT<BM, TT>;
     extern __shared__ __align__(16) uint32_t smem[];
     __shared__ uint32_t tm_base_s;
     const int T = blockDim.x, t = threadIdx.x, warp = t >> 5;
@@ -505,6 +549,7 @@ __global__ void __launch_bounds__(384, 1) k_scl_f32(const __grid_constant__ SclF
             }
             // other lanes' buffers are read by the next step; `lockstep` keeps the CTA's warps on the same program step
             // (the kernel is ~90 KB of SASS; free-running warps thrash the instruction caches, see pc_scl_i8.cu)
+            c.st_fence();
             if (p.lockstep)
                 __syncthreads();
             else
@@ -571,7 +616,15 @@ cudaError_t launch_scl_f32(const SclFLaunch& L, const float* d_llr, uint8_t* d_i
     p.count = d_count;
     // decision words in the arena (long codes) or in tensor memory -> the instantiation whose ld / st test that flag
     const bool ba = (p.bitR_off[p.S] & kArena) != 0;
-    void (*kern)(SclFParams) = p.tm_alloc_cols ? k_scl_f32<BM_TMEM> : (ba ? k_scl_f32<BM_ARENA> : k_scl_f32<BM_SMEM>);
+    void (*kern)(SclFParams) = ba ? k_scl_f32<BM_ARENA, 0> : k_scl_f32<BM_SMEM, 0>;
+    if (p.tm_alloc_cols) {
+        switch (L.threads) { // the CTA sizes the tensor-memory planner picks get their own instantiation
+        case 512: kern = k_scl_f32<BM_TMEM, 512>; break;
+        case 384: kern = k_scl_f32<BM_TMEM, 384>; break;
+        case 256: kern = k_scl_f32<BM_TMEM, 256>; break;
+        default: kern = k_scl_f32<BM_TMEM, 0>; break;
+        }
+    }
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes);
     // several CTAs per SM only fit when the L1/shared split is at its shared-memory maximum; a single CTA keeps the
     // default split (the rest stays L1 for the channel rows and the arena)
@@ -720,7 +773,7 @@ int plan_scl_f32(int S, int K, int L, bool root_leaf, bool virt_ok, size_t smem_
     while (G < L) G <<= 1;
     int T = 256;
     if (const char* e = getenv("PC_SCLF_T")) T = atoi(e);
-    if (T < 32 || T > 384 || (T % 32) != 0 || (T % G) != 0) T = 256;
+    if (T < 32 || T > 512 || (T % 32) != 0 || (T % G) != 0) T = 256;
     const bool lockstep = getenv("PC_SCL_LOCKSTEP") ? atoi(getenv("PC_SCL_LOCKSTEP")) != 0 : true;
     bool virt = virt_ok && !root_leaf && S >= 7;
     if (const char* e = getenv("PC_SCLF_VIRT")) virt = virt && atoi(e) != 0;

@@ -28,8 +28,20 @@
 
 namespace pc {
 
-template <int BM> // BM: BM_ARENA some decision words live in the arena (long codes), BM_TMEM in tensor memory; 0 = no flag tests
+__device__ __forceinline__ uint32_t lds_u32(uint32_t a)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ void sts_u32(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+
+// BM: BM_ARENA some decision words live in the arena (long codes), BM_TMEM in tensor memory; 0 = no flag tests.
+// TT: threads per CTA as a compile-time constant (0 = run-time): word w of a lane's shared-memory column sits at byte
+// offset 4 TT w, an immediate of the load when w and TT are known
+template <int BM, int TT>
 struct LaneT {
+    static constexpr int kTT = TT;
     uint32_t* sm;   // smem base + tid (word w at sm[w * T])
     uint32_t* ar;   // arena base + global lane id (word w at ar[w * AS])
     size_t AS;
@@ -54,12 +66,17 @@ struct LaneT {
     __device__ __forceinline__ void st(int word, uint32_t v) const
     {
         if ((BM & BM_TMEM) && (word & kTmem)) {
-            tm_st1(tm + (uint32_t)(word & 0xFFFF), v);
-            tm_wait_st();
+            tm_st1(tm + (uint32_t)(word & 0xFFFF), v); // completion is awaited by st_fence(), once per step
         } else if ((BM & BM_ARENA) && (word & kArena))
             ar[(size_t)(word & (kArena - 1)) * AS] = v;
         else
             sm[(size_t)word * T] = v;
+    }
+    // tensor-memory stores complete: called before a step re-reads columns it wrote (scl_take_bits after the leaf's own
+    // decisions) and at the end of every node-program step
+    __device__ __forceinline__ void st_fence() const
+    {
+        if (BM & BM_TMEM) tm_wait_st();
     }
     // LLR stage starting at word offset `off` (p.llr_off[s]) in lane `owner`'s space, resolved once per node step
     struct View {
@@ -94,7 +111,36 @@ __device__ __forceinline__ void scl_fg(Lane& c, const SclParams& p, int s, const
     const uint32_t o = c.own_llr.get(s), ol = c.own_L.get(s - 1);
     const int lb = p.bitL_off[s - 1];
     const typename Lane::View src = c.view(from_row ? p.llr_off[s - 1] : p.llr_off[s], o), dst = c.view(p.llr_off[s - 1], (uint32_t)c.l);
-    if (h >= 16) {
+    if (Lane::kTT && h >= 16 && !from_row && !((p.llr_off[s] | p.llr_off[s - 1]) & kArena)) {
+        // both stages in shared memory and the CTA size known at compile time: 32-bit shared addresses whose word
+        // offsets are immediates (the view path below pays a multiply-add per access, 12 % of the executed
+        // instructions in ncu r02_scl_i8_v1)
+        constexpr uint32_t ES = 4u * (uint32_t)Lane::kTT;
+        const uint32_t smb = (uint32_t)__cvta_generic_to_shared(c.sm);
+        const uint32_t sa = smb + ES * (uint32_t)p.llr_off[s] + 4u * (uint32_t)((int)o - c.l), da = smb + ES * (uint32_t)p.llr_off[s - 1];
+        const int hw = h >> 2;
+        uint32_t bword = 0;
+        for (int j = 0; j < hw; j += 4) {
+            uint32_t a[4], b[4], r[4];
+            const uint32_t ja = sa + ES * (uint32_t)j, jb = ja + ES * (uint32_t)hw;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) a[u] = lds_u32(ja + ES * u), b[u] = lds_u32(jb + ES * u);
+            if (IS_G) {
+                if ((j & 7) == 0) bword = c.ld(lb + (j >> 3), ol); // one decision word covers eight LLR words
+                const uint32_t bw = bword >> (4 * (j & 7));
+#pragma unroll
+                for (int u = 0; u < 4; ++u) r[u] = sw_g(a[u], b[u], sw_expand4(bw >> (4 * u)));
+            } else {
+#pragma unroll
+                for (int u = 0; u < 4; ++u) r[u] = sw_f(a[u], b[u]);
+            }
+            if (active) {
+                const uint32_t jd = da + ES * (uint32_t)j;
+#pragma unroll
+                for (int u = 0; u < 4; ++u) sts_u32(jd + ES * u, r[u]);
+            }
+        }
+    } else if (h >= 16) {
         // four words per step: all loads first (source and destination may alias as far as the compiler knows, so
         // a rolled loop serialises load -> f/g -> store), the channel row as 16-byte loads
         const int hw = h >> 2;
@@ -415,10 +461,10 @@ __device__ __forceinline__ void scl_spc(Lane& c, const SclParams& p, int s, int 
     set_side(c, s, side);
 }
 
-template <int BM>
+template <int BM, int TT>
 __global__ void __launch_bounds__(512, 1) k_scl_i8(const __grid_constant__ SclParams p)
 {
-    using Lane = LaneT<BM>;
+    using Lane = LaneT<BM, TT>;
     extern __shared__ __align__(16) uint32_t smem[];
     __shared__ uint32_t tm_base_s;
     const int T = blockDim.x, t = threadIdx.x, warp = t >> 5;
@@ -488,6 +534,7 @@ __global__ void __launch_bounds__(512, 1) k_scl_i8(const __grid_constant__ SclPa
             // other lanes' buffers are read by the next step. With `lockstep` the whole CTA meets here: the kernel is
             // 130 KB of SASS, and warps spread over the program (ncu r02_scl_i8_v0: `no_instruction` 5.3 cycles per
             // issue with 16 free-running warps) thrash the instruction caches; in step, a fetched line serves all warps.
+            c.st_fence();
             if (p.lockstep)
                 __syncthreads();
             else
@@ -554,7 +601,8 @@ cudaError_t launch_scl_i8(const SclLaunch& L, const int8_t* d_llr, uint8_t* d_in
     p.count = d_count;
     // decision words in the arena (long codes) or in tensor memory -> the instantiation whose ld / st test that flag
     const bool ba = (p.bitR_off[p.S] & kArena) != 0;
-    void (*kern)(SclParams) = p.tm_alloc_cols ? k_scl_i8<BM_TMEM> : (ba ? k_scl_i8<BM_ARENA> : k_scl_i8<BM_SMEM>);
+    void (*kern)(SclParams) = ba ? k_scl_i8<BM_ARENA, 0> : k_scl_i8<BM_SMEM, 0>;
+    if (p.tm_alloc_cols) kern = L.threads == 512 ? k_scl_i8<BM_TMEM, 512> : (L.threads == 256 ? k_scl_i8<BM_TMEM, 256> : k_scl_i8<BM_TMEM, 0>);
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes);
     // several CTAs per SM only fit when the L1/shared split is at its shared-memory maximum; a single CTA keeps the
     // default split (the rest stays L1 for the channel rows and the arena)
