@@ -10,6 +10,7 @@
  *   pc_code_set_crc         Decoder/Encoder::setErrorDetection              decoder.cpp:133-136, src/polarcode/encoding/encoder.cpp
  *   pc_code_set_systematic  Decoder/Encoder::setSystematic                  decoder.h:118, encoder.h
  *   pc_decode_batch         Decoder::decode_vector(const char* | const float*, void*)   decoder.cpp:154-181   (B codewords per call)
+ *   pc_decode_soft_batch    Decoder::getSoftCodeword / getSoftInformation   decoder.cpp:147-152 (int8 Fast-SSC)
  *   pc_encode_batch         Encoder::encode_vector(void*, void*)            src/polarcode/encoding/encoder.cpp:79-90
  *   pc_crc_generate_batch   ErrorDetection::Detector::generate              include/polarcode/errordetection/errordetector.h:57-63
  *   pc_crc_check_batch      Detector::check                                 errordetector.h:65-70
@@ -116,6 +117,16 @@ int pc_decode_batch(pc_code* c, const void* d_llr, int llr_is_float, uint8_t* d_
  * path the per-codeword decode_vector() wrappers use (B = 1) and bench.py's e2e leg. */
 int pc_decode_batch_host(pc_code* c, const void* h_llr, int llr_is_float, uint8_t* h_info, uint8_t* h_ok,
                          size_t B);
+
+/* Soft outputs of the int8 Fast-SSC decoder ('char', L = 1), Decoder::getSoftCodeword / getSoftInformation
+ * (src/polarcode/decoding/decoder.cpp:147-152) after decode(): the decoder's bit container as BYTES, byte for byte what
+ * the reference holds (leaves write LLR-valued bytes, combine steps XOR whole bytes; only the sign is a decision).
+ * d_soft_code[B][N] int8 and / or d_soft_info[B][K] int8 (the container bytes at the information positions,
+ * CharContainer::getSoftInformation bitcontainer.cpp:582-590); either may be NULL. Other decoder kinds: PC_ERR_UNSUPPORTED. */
+int pc_decode_soft_batch(pc_code* c, const void* d_llr, int llr_is_float, int8_t* d_soft_code, int8_t* d_soft_info, size_t B,
+                         void* stream);
+int pc_decode_soft_batch_host(pc_code* c, const void* h_llr, int llr_is_float, int8_t* h_soft_code, int8_t* h_soft_info,
+                              size_t B);
 
 /* Encode B info blocks of ceil(K/8) bytes. The detector's check bytes are generated into the tail of a
  * device-side copy of each block (the reference writes them into the caller's buffer,

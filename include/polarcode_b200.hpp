@@ -14,8 +14,9 @@
 // (correctness path, not the performance path). There is no CPU fallback: constructing an encoder or decoder without
 // a usable GPU throws std::runtime_error.
 //
-// Not carried over: soft outputs (getSoftCodeword / getSoftInformation; the kernels keep hard decisions as one bit
-// per element), the BitContainer accessors (inputContainer / outputContainer), Encoder::setCodeword / setCharCodeword /
+// Soft outputs: getSoftCodeword / getSoftInformation are served for the 'char' Fast-SSC decoder by a second kernel that
+// keeps the bit container as bytes (pc_fastssc_i8_soft.cu); the float and list decoders' containers are not kept.
+// Not carried over: the BitContainer accessors (inputContainer / outputContainer), Encoder::setCodeword / setCharCodeword /
 // setFloatCodeword / clearFrozenBits (hooks the reference's own decoders use for non-systematic output; the kernels do
 // that step on the device), the 'scan' kind and CMAC detectors.
 #ifndef POLARCODE_B200_HPP
@@ -402,6 +403,14 @@ protected:
     std::vector<char> mCharLlr;
     bool mSignalIsFloat = false;
 
+    void soft(int8_t* code, int8_t* info)
+    {
+        if (mKind != PC_DEC_FASTSSC_I8) throw std::logic_error("soft outputs are available for the 'char' Fast-SSC decoder only");
+        const void* llr = mSignalIsFloat ? static_cast<const void*>(mFloatLlr.data()) : static_cast<const void*>(mCharLlr.data());
+        if ((mSignalIsFloat ? mFloatLlr.size() : mCharLlr.size()) != mBlockLength) throw std::logic_error("no signal set");
+        detail::check(pc_decode_soft_batch_host(mCode, llr, mSignalIsFloat ? 1 : 0, code, info, 1));
+    }
+
 public:
     Decoder() {}
     Decoder(size_t blockLength, size_t listSize, const std::vector<unsigned>& frozenBits, int kind)
@@ -460,6 +469,17 @@ public:
     void decode_batch_device(const void* d_llr, bool llrIsFloat, uint8_t* d_info, uint8_t* d_ok, size_t B, void* stream = nullptr)
     {
         detail::check(pc_decode_batch(mCode, d_llr, llrIsFloat ? 1 : 0, d_info, d_ok, B, stream));
+    }
+    /// decoder.cpp:147-152: the bit container after the last decode() as bytes (N int8 values for the 'char' Fast-SSC
+    /// decoder; other kinds throw std::logic_error -- their containers hold floats / list paths the kernels do not keep).
+    /// The container is recomputed on the device from the signal of the last setSignal()/decode_vector().
+    void getSoftCodeword(void* pData) { soft(static_cast<int8_t*>(pData), nullptr); }
+    /// the container bytes at the information positions (K int8 values)
+    void getSoftInformation(void* pData) { soft(nullptr, static_cast<int8_t*>(pData)); }
+    /// batch forms, DEVICE buffers: d_soft_code[B][N], d_soft_info[B][K] (either may be null)
+    void soft_batch_device(const void* d_llr, bool llrIsFloat, int8_t* d_soft_code, int8_t* d_soft_info, size_t B, void* stream = nullptr)
+    {
+        detail::check(pc_decode_soft_batch(mCode, d_llr, llrIsFloat ? 1 : 0, d_soft_code, d_soft_info, B, stream));
     }
     size_t duration_ns() { return mDecoderDuration; }
     std::vector<unsigned> frozenBits() { return mFrozenBits; }

@@ -125,6 +125,29 @@ double ref_decode_batch2(int N, int L, const unsigned* frozen, int nf, const cha
     }
 }
 
+// Decoder::getSoftCodeword / getSoftInformation (decoder.cpp:147-152) of the 'char' Fast-SSC decoder after decode():
+// soft_code int8[B][N], soft_info int8[B][K] (either may be null). Returns 0 or -1.
+int ref_decode_soft(int N, const unsigned* frozen, int nf, int systematic, const signed char* llr, long B,
+                    signed char* soft_code, signed char* soft_info)
+{
+    try {
+        auto fz = mkfrozen(frozen, nf);
+        const int K = N - nf;
+        Decoding::Decoder* dec = Decoding::create(N, 1, fz, std::string("char"));
+        dec->setSystematic(systematic != 0);
+        std::vector<unsigned char> tmp((K + 7) / 8 + 64);
+        for (long i = 0; i < B; ++i) {
+            dec->decode_vector(reinterpret_cast<const char*>(llr) + i * N, tmp.data());
+            if (soft_code) dec->getSoftCodeword(soft_code + i * N);
+            if (soft_info) dec->getSoftInformation(soft_info + i * K);
+        }
+        delete dec;
+        return 0;
+    } catch (...) {
+        return -1;
+    }
+}
+
 // info: uint8[B][ceil(K/8)] (a private copy is made per frame because encode() writes the CRC in place,
 // butterfly_fip_packed.cpp:47-49; the copy incl. CRC is returned through info_out when non-null).
 double ref_encode_batch(int N, const unsigned* frozen, int nf, int crc_bits, const char* crc_type,

@@ -407,6 +407,7 @@ void pc_code_destroy(pc_code* c)
     cudaFree(c->f32_arena);
     cudaFree(c->d_f32_in);
     cudaFree(c->arena);
+    cudaFree(c->soft_arena);
     cudaFree(c->d_stage_in);
     cudaFree(c->d_stage_out);
     cudaFree(c->d_stage_ok);

@@ -72,6 +72,8 @@ struct pc_code {
     int plan_small_cap = 0;       // CTA size cap plan_small was made for (0 = none)
     uint32_t* arena = nullptr;
     size_t arena_bytes = 0;
+    uint32_t* soft_arena = nullptr;   // pc_fastssc_i8_soft.cu: LLR stages + N decision BYTES per thread
+    size_t soft_arena_bytes = 0;
     // staging for the *_host entry points
     void* d_stage_in = nullptr;
     void* d_stage_out = nullptr;
@@ -98,5 +100,6 @@ int quantize_device(int N, const float* d_in, int8_t* d_out, size_t B, cudaStrea
 int encode_device(pc_code* c, const uint8_t* d_info, uint8_t* d_code, uint8_t* d_info_crc, size_t B, cudaStream_t st);
 int build_encoder_tables(pc_code* c);
 int encode_device_raw(pc_code* c, const uint8_t* d_info, uint8_t* d_code, size_t B, cudaStream_t st);
+int soft_decode_device(pc_code* c, const int8_t* d_llr, int8_t* d_soft_code, int8_t* d_soft_info, size_t B, cudaStream_t st);
 } // namespace pc
 #endif

@@ -758,8 +758,8 @@ static int plan_scl_f32_smem(int S, int K, int L, bool root_leaf, size_t smem_ma
 // Planner, first choice: ONE CTA of T lanes per SM whose warps stay in step, all decision words in TENSOR MEMORY (which
 // frees 136 shared-memory words per lane at N = 1024 for LLR stages), LLR stage S-1 virtual (recomputed from the channel
 // row) and only the stage(s) that still do not fit in an arena small enough to stay in L2:
-//   N = 1024, T = 256: stages <= 6 in shared memory, stages 7 and 8 in a 58 MB arena (was: stages >= 4, 233 MB);
-//   T = 224: stages <= 7 in shared memory, 34 MB arena.
+//   N = 1024, T = 384 (default): stages <= 6 in shared memory, stages 7 and 8 in an 87 MB arena (was: stages >= 4, 233 MB);
+//   T = 256: the same stages, 58 MB arena; T = 224: stages <= 7 in shared memory, 34 MB arena.
 // PC_SCLF_T picks T (multiple of 32 and of the group size), PC_SCLF_VIRT=0 stores stage S-1, PC_SCL_NOTMEM=1 or
 // PC_SCLF_THREADS / PC_SCLF_CTAS fall back to the shared-memory planner above.
 int plan_scl_f32(int S, int K, int L, bool root_leaf, bool virt_ok, size_t smem_max, int sms, SclFLaunch& out, const char** msg)
@@ -771,9 +771,11 @@ int plan_scl_f32(int S, int K, int L, bool root_leaf, bool virt_ok, size_t smem_
     const bool no_tmem = getenv("PC_SCL_NOTMEM") != nullptr || getenv("PC_SCLF_THREADS") != nullptr || getenv("PC_SCLF_CTAS") != nullptr;
     int G = 1;
     while (G < L) G <<= 1;
-    int T = 256;
+    // measured at N = 1024, L = 8 (profiles/r02_c4_perf.txt): T = 256 2.79 Gbit/s (58 MB arena, DRAM traffic 4.3x the
+    // algorithmic bytes), 320 2.55, 384 3.32 (87 MB arena, 17x, still only 0.47 TB/s), 512 3.34 (stage 6 leaves shared memory)
+    int T = 384;
     if (const char* e = getenv("PC_SCLF_T")) T = atoi(e);
-    if (T < 32 || T > 512 || (T % 32) != 0 || (T % G) != 0) T = 256;
+    if (T < 32 || T > 512 || (T % 32) != 0 || (T % G) != 0) T = 384;
     const bool lockstep = getenv("PC_SCL_LOCKSTEP") ? atoi(getenv("PC_SCL_LOCKSTEP")) != 0 : true;
     bool virt = virt_ok && !root_leaf && S >= 7;
     if (const char* e = getenv("PC_SCLF_VIRT")) virt = virt && atoi(e) != 0;

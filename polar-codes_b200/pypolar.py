@@ -159,6 +159,31 @@ class PolarDecoder(_Code):
         check(lib().pc_decode_batch_host(self._h, ptr(a), int(a.dtype == np.float32), ptr(out), ptr(ok), B))
         return (out, ok) if return_ok else out
 
+    def decode_soft_batch(self, llrs):
+        """[B, N] int8 (or float32, quantised like decode_vector does) -> (soft codeword int8 [B, N], soft information
+        int8 [B, K]): Decoder::getSoftCodeword / getSoftInformation (decoder.cpp:147-152) after decode(), for every row.
+        int8 Fast-SSC ('char', L = 1) only. numpy in -> numpy out; torch CUDA tensor in -> CUDA tensors out."""
+        if hasattr(llrs, "is_cuda") and llrs.is_cuda:
+            import torch
+            llrs = llrs.contiguous()
+            B = llrs.shape[0]
+            sc = torch.empty((B, self._N), dtype=torch.int8, device=llrs.device)
+            si = torch.empty((B, self._K), dtype=torch.int8, device=llrs.device)
+            st = torch.cuda.current_stream(llrs.device).cuda_stream
+            check(lib().pc_decode_soft_batch(self._h, ptr(llrs), int(llrs.dtype == torch.float32), ptr(sc), ptr(si), B,
+                                             ctypes.c_void_p(st)))
+            return sc, si
+        a = np.asarray(llrs)
+        if a.ndim != 2 or a.shape[1] != self._N:
+            raise RuntimeError("Input must be [B, blockLength]")
+        if a.dtype != np.int8:
+            a = a.astype(np.float32, copy=False)
+        a = np.ascontiguousarray(a)
+        B = a.shape[0]
+        sc, si = np.empty((B, self._N), np.int8), np.empty((B, self._K), np.int8)
+        check(lib().pc_decode_soft_batch_host(self._h, ptr(a), int(a.dtype == np.float32), ptr(sc), ptr(si), B))
+        return sc, si
+
     def decode_vector(self, array):
         """decoder_python.cc:41-74: float32[N] or int8[N] -> uint8[K/8] (one codeword = a batch of one)"""
         a = np.asarray(array)

@@ -39,6 +39,9 @@ def lib():
         L.ref_crc_batch.restype = ctypes.c_int
         L.ref_crc_batch.argtypes = [ctypes.c_int, ctypes.c_char_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
                                     ctypes.c_long, ctypes.c_long, ctypes.c_void_p, ctypes.c_void_p]
+        L.ref_decode_soft.restype = ctypes.c_int
+        L.ref_decode_soft.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_long,
+                                      ctypes.c_void_p, ctypes.c_void_p]
         L.ref_quantize.restype = ctypes.c_int
         L.ref_quantize.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_long, ctypes.c_void_p]
         L.ref_puncturer.restype = ctypes.c_long
@@ -78,6 +81,17 @@ def decode_batch(N, L, frozen, kind, llr, crc_bits=-1, crc_type="crc", systemati
     if t < 0:
         raise RuntimeError("reference decode failed")
     return (out, ok, t) if return_time else (out, ok)
+
+
+def decode_soft(N, frozen, llr, systematic=True):
+    """Decoder::getSoftCodeword / getSoftInformation of the reference's 'char' Fast-SSC decoder after decode_vector"""
+    frozen = np.ascontiguousarray(frozen, dtype=np.uint32)
+    llr = np.ascontiguousarray(llr, dtype=np.int8)
+    B, K = llr.shape[0], N - len(frozen)
+    sc, si = np.zeros((B, N), np.int8), np.zeros((B, K), np.int8)
+    if lib().ref_decode_soft(N, _p(frozen), len(frozen), int(systematic), _p(llr), B, _p(sc), _p(si)) < 0:
+        raise RuntimeError("reference soft decode failed")
+    return sc, si
 
 
 def encode_batch(N, frozen, info, crc_bits=-1, crc_type="crc", systematic=True, threads=1, repeat=1,

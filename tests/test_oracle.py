@@ -64,6 +64,20 @@ def test_rep_soft_output_saturation(orc):
         assert (soft[0] == exp).all()
 
 
+@pytest.mark.parametrize("N,K", [(1024, 512), (64, 40), (8, 4), (256, 64), (2048, 1800)])
+def test_soft_codeword_matches_reference(orc, ref, N, K):
+    """Decoder::getSoftCodeword (decoder.cpp:147-152): the restatement's root bit bytes against the reference's"""
+    rng = np.random.default_rng(N)
+    fz = ref.frozen_bits(N, K, 0.0)
+    llr = np.concatenate([rng.integers(-128, 128, (64, N), dtype=np.int8),
+                          np.clip(np.rint(10 * (1 + 0.8 * rng.standard_normal((192, N)))), -128, 127).astype(np.int8)])
+    _, soft = orc.fastssc_i8_decode(N, fz, llr, soft=True)
+    esc, esi = ref.decode_soft(N, fz, llr)
+    assert np.array_equal(soft, esc)
+    info_pos = np.setdiff1d(np.arange(N), fz)
+    assert np.array_equal(esi, esc[:, info_pos])
+
+
 @pytest.mark.parametrize("N,K", [(1024, 512), (256, 128), (4096, 3072), (16384, 8192)])
 def test_encoder_golden(orc, N, K):
     fz = orc.frozen_bits(N, K, 0.0)
