@@ -93,11 +93,19 @@ __global__ void __launch_bounds__(512, 2) k_encode2(const __grid_constant__ Enc2
     const int tpc = MULTI ? p.tpc : 1, grp = warp / tpc, t = MULTI ? warp - grp * tpc : 0; // group of tpc warps = 32 codewords
     const int gpc = (T >> 5) / tpc, cpc = 32 * gpc;                // codewords per CTA
     const int W = R * tpc, Wp = W + 1;                             // words per codeword (+1: conflict-free transposes)
-    uint32_t* s_info = sm;                                         // [kw][cpc]: word q of codeword slot at q * cpc + slot
-    uint32_t* s_x = sm + (size_t)cpc * p.kw;                       // [cpc][Wp]   (MULTI only)
-    uint32_t* s_crc = s_x + (MULTI ? (size_t)cpc * Wp : 0);        // 256 words (fused detector only)
-    if (!MULTI && p.crc.width)
+    // shared memory: the staged info rows [kw][cpc] (word q of codeword slot at q * cpc + slot); MULTI: the transpose
+    // buffer [cpc][Wp] ALIASES them (the rows are dead once deposited) and the code's table (8 W words) follows;
+    // otherwise the detector table (256 words) follows the rows
+    uint32_t* s_info = sm;
+    uint32_t* s_x = sm;
+    const size_t head = MULTI ? ((size_t)cpc * Wp > (size_t)cpc * p.kw ? (size_t)cpc * Wp : (size_t)cpc * p.kw) : (size_t)cpc * p.kw;
+    uint32_t* s_tab = sm + head;                                   // MULTI: 8 * W words
+    uint32_t* s_crc = sm + head;                                   // !MULTI: 256 words (fused detector only)
+    if (MULTI) {
+        for (int i = threadIdx.x; i < 8 * W; i += T) s_tab[i] = __ldg(p.tab + i);
+    } else if (p.crc.width) {
         for (int i = threadIdx.x; i < 256; i += T) s_crc[i] = p.crc_table[i];
+    }
     const int slot = grp * 32 + lane;
     const int nbytes = 4 * W;
     int ltpc = 0;
@@ -168,19 +176,20 @@ __global__ void __launch_bounds__(512, 2) k_encode2(const __grid_constant__ Enc2
         uint32_t x[R];
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            // table entry of code word t R + r: __constant__ operands for single-thread codewords, L1-cached loads otherwise
-            const uint32_t* Eg = p.tab + 8 * (t * R + r);
+            // table entry of code word t R + r: __constant__ operands for single-thread codewords, the shared-memory copy
+            // otherwise (the same address for all lanes of a warp: one broadcast read)
+            const uint32_t* Eg = s_tab + 8 * (t * R + r);
             const uint32_t* Ec = c_enc + 8 * r;
-            const uint32_t m = MULTI ? __ldg(Eg) : Ec[0];
+            const uint32_t m = MULTI ? Eg[0] : Ec[0];
             uint32_t v = 0;
             if (m) { // uniform
-                const int q1 = (int)(MULTI ? __ldg(Eg + 1) : Ec[1]), pos = (int)(MULTI ? __ldg(Eg + 2) : Ec[2]);
+                const int q1 = (int)(MULTI ? Eg[1] : Ec[1]), pos = (int)(MULTI ? Eg[2] : Ec[2]);
                 const uint32_t lo = myinfo[q1 * cpc], hi = q1 ? myinfo[(q1 - 1) * cpc] : 0u;
                 v = __funnelshift_r(lo, hi, pos);
                 if (m != 0xFFFFFFFFu) {
 #pragma unroll
                     for (int i = 4; i >= 0; --i) {
-                        const uint32_t mv = MULTI ? __ldg(Eg + 3 + i) : Ec[3 + i];
+                        const uint32_t mv = MULTI ? Eg[3 + i] : Ec[3 + i];
                         const uint32_t sh = v << (1 << i);
                         v = (v & ~mv) | (sh & mv);
                     }
@@ -208,7 +217,7 @@ __global__ void __launch_bounds__(512, 2) k_encode2(const __grid_constant__ Enc2
         if (p.systematic) { // resetFrozenBits, then the second transform starting in the layout we are in
             if (tpc > 1) {
 #pragma unroll
-                for (int r = 0; r < R; ++r) x[r] &= __ldg(p.tab + 8 * (r * tpc + t));
+                for (int r = 0; r < R; ++r) x[r] &= s_tab[8 * (r * tpc + t)];
                 stages_inreg<R>(x, 5 - ltpc);
             } else {
 #pragma unroll
@@ -357,7 +366,8 @@ int encode2_device_raw(pc_code* c, const uint8_t* src, uint8_t* d_code, size_t B
     // CTA: whole groups of tpc warps (32 codewords each); 256 threads for short codes, 512 when a group needs them
     int threads = tpc <= 8 ? 256 : 32 * tpc;
     const int gpc = (threads / 32) / tpc, cpc = 32 * gpc;
-    const size_t smem = 4 * ((size_t)cpc * p.kw + (tpc > 1 ? (size_t)cpc * (W + 1) : 256));
+    const size_t rows_w = (size_t)cpc * p.kw, xpose_w = (size_t)cpc * (W + 1);
+    const size_t smem = 4 * (tpc > 1 ? (rows_w > xpose_w ? rows_w : xpose_w) + 8 * (size_t)W : rows_w + 256);
     size_t ctas = (B + cpc - 1) / cpc;
     const int grid = (int)(ctas < 148 * 8 ? ctas : 148 * 8);
     cudaError_t e;
