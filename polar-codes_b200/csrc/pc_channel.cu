@@ -78,11 +78,12 @@ __global__ void __launch_bounds__(256) k_awgn(const uint8_t* __restrict__ code, 
 {
     const Philox ph{ (uint32_t)seed, (uint32_t)(seed >> 32) };
     const int quads = N >> 2, nbytes = N >> 3;
+    const int lq = 31 - __clz(quads); // N is a power of two: row / column by shift and mask, not a 64-bit division
     const unsigned long long total = B * (unsigned long long)quads;
     for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
          i += (unsigned long long)gridDim.x * blockDim.x) {
-        const unsigned long long row = i / quads;
-        const int q = (int)(i % quads);
+        const unsigned long long row = i >> lq;
+        const int q = (int)(i & (unsigned long long)(quads - 1));
         const unsigned long long frame = first_frame + row;
         const uint4 r = ph((uint32_t)frame, (uint32_t)(frame >> 32), (uint32_t)q, 0xA36Eu);
         // Box-Muller on two pairs of uniforms in (0,1]

@@ -200,6 +200,51 @@ __device__ __forceinline__ void fg_block(const FLane& c, FgSrc<FLane>& src, cons
     }
 }
 
+// The same step while ONE path is alive (the frozen prefix of the tree: G - 1 lanes of a group would only watch): all G
+// lanes share path 0's step, eight elements per lane and round, reading through lane 0's tables and writing into lane
+// 0's column. Element-wise operations only, so the results are the same values.
+template <bool IS_G, class FLane>
+__device__ __forceinline__ void sclf_fg_single(FLane& c, const SclFParams& p, int s, const float* row, int mode)
+{
+    const int h = 1 << (s - 1), G = c.G, half = 1 << (p.S - 1);
+    const uint32_t o = __shfl_sync(0xFFFFFFFFu, c.own_llr.get(s), 0, G), ol = __shfl_sync(0xFFFFFFFFu, c.own_L.get(s - 1), 0, G);
+    const int lb = p.bitL_off[s - 1];
+    const typename FLane::View src = c.view(mode == 0 ? s : s - 1, mode == 0 ? p.llr_off[s] : p.llr_off[s - 1], o);
+    const typename FLane::View dst = c.view(s - 1, p.llr_off[s - 1], 0u);
+    for (int j0 = 0; j0 < h; j0 += 8 * G) {
+        const int j = j0 + 8 * c.l;
+        uint32_t bword = 0;
+        if (IS_G) { // the decision words of this round, fetched by all lanes (tensor-memory loads are warp-collective)
+            const int nq = (h - j0 + 31) >> 5 < ((8 * G + 31) >> 5) ? (h - j0 + 31) >> 5 : ((8 * G + 31) >> 5);
+            for (int q = 0; q < nq; ++q) {
+                const uint32_t w = c.ld(lb + (j0 >> 5) + q, ol);
+                if (q == ((j - j0) >> 5)) bword = w;
+            }
+        }
+        if (j < h) {
+            float a[8], b[8], r[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                if (mode == 0) {
+                    a[u] = src[j + u];
+                    b[u] = src[h + j + u];
+                } else if (mode == 1) {
+                    a[u] = __ldg(row + j + u);
+                    b[u] = __ldg(row + h + j + u);
+                } else { // virtual stage S-1 before the root's g step
+                    a[u] = f_f32(__ldg(row + j + u), __ldg(row + j + u + half));
+                    b[u] = f_f32(__ldg(row + h + j + u), __ldg(row + h + j + u + half));
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 8; ++u) r[u] = IS_G ? g_f32(a[u], b[u], (bword >> ((j & 31) + u)) & 1u) : f_f32(a[u], b[u]);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) dst.set(j + u, r[u]);
+        }
+    }
+    c.own_llr.set(s - 1, (uint32_t)c.l);
+}
+
 // f / g step of a node of size 2^s (RateRNode::decode scl_avx_float.cpp:238-262). Every lane runs the step (decision
 // words may sit in tensor memory, whose loads are warp-collective); dead lanes only skip their stores.
 template <bool IS_G, class FLane>
@@ -213,9 +258,13 @@ __device__ __forceinline__ void sclf_fg(FLane& c, const SclFParams& p, int s, co
         c.own_llr.set(s - 1, (uint32_t)c.l);
         return;
     }
+    const bool virt = p.virt_top && s == p.S - 1;
+    if (c.P == 1 && c.G >= 2 && h >= 16 && !(virt && c.root_right)) {
+        sclf_fg_single<IS_G>(c, p, s, row, from_row ? 1 : (virt ? 2 : 0));
+        return;
+    }
     const uint32_t o = c.own_llr.get(s), ol = c.own_L.get(s - 1);
     const int lb = p.bitL_off[s - 1];
-    const bool virt = p.virt_top && s == p.S - 1;
     FgSrc<FLane> src{ c, (from_row || virt) ? c.view(s - 1, p.llr_off[s - 1], (uint32_t)c.l) : c.view(s, p.llr_off[s], o), row,
                       from_row ? 1 : (virt ? 2 + c.root_right : 0), 1 << (p.S - 1), p.bitL_off[p.S - 1], c.own_L.get(p.S - 1),
                       { 0u, 0u }, { -1, -1 } };
@@ -276,6 +325,7 @@ template <bool WANT_ALL, class FLane>
 __device__ __forceinline__ void sclf_sums(const FLane& c, const SclFParams& p, int s, float& neg, float& pos, float& all)
 {
     const int n = 1 << s;
+    // (no lane sharing here even while one path is alive: the order of the float additions is part of the result)
     const typename FLane::View v = c.view(s, p.llr_off[s], (uint32_t)c.l);
     float an[8], ap[8], aa[8];
 #pragma unroll

@@ -96,11 +96,66 @@ struct LaneT {
 __device__ __forceinline__ int stage_words(int s) { return s >= 2 ? (1 << (s - 2)) : 1; }   // LLR words
 __device__ __forceinline__ uint32_t bytemask(int nbytes) { return nbytes >= 4 ? 0xFFFFFFFFu : ((1u << (8 * nbytes)) - 1u); }
 
+// The same step while ONE path is alive (the whole frozen prefix of the tree, 15 % of a (1024, 512) frame's word steps
+// in the lane-per-path form, where G - 1 lanes of a group only watch): all G lanes of the group share path 0's step,
+// four words per lane and round, reading through lane 0's tables and writing into lane 0's column.
+template <bool IS_G, class Lane>
+__device__ __forceinline__ void scl_fg_single(Lane& c, const SclParams& p, int s, const int8_t* row)
+{
+    const int h = 1 << (s - 1), hw = h >> 2, G = c.G;
+    const uint32_t* grow = reinterpret_cast<const uint32_t*>(row);
+    const bool from_row = (s == p.S) && !p.root_leaf;
+    const uint32_t o = __shfl_sync(0xFFFFFFFFu, c.own_llr.get(s), 0, G), ol = __shfl_sync(0xFFFFFFFFu, c.own_L.get(s - 1), 0, G);
+    const int lb = p.bitL_off[s - 1];
+    const typename Lane::View src = c.view(from_row ? p.llr_off[s - 1] : p.llr_off[s], o), dst = c.view(p.llr_off[s - 1], 0u);
+    const bool row16 = from_row && ((reinterpret_cast<uintptr_t>(row) & 15u) == 0);
+    for (int j0 = 0; j0 < hw; j0 += 4 * G) {
+        const int j = j0 + 4 * c.l;
+        uint32_t bword = 0;
+        if (IS_G) { // the decision words of this round, fetched by all lanes (tensor-memory loads are warp-collective)
+            const int nq = (hw - j0 + 7) >> 3 < (G >> 1) ? (hw - j0 + 7) >> 3 : (G >> 1);
+            for (int q = 0; q < nq; ++q) {
+                const uint32_t w = c.ld(lb + (j0 >> 3) + q, ol);
+                if (q == (c.l >> 1)) bword = w;
+            }
+        }
+        if (j < hw) {
+            uint32_t a[4], b[4], r[4];
+            if (row16) {
+                const uint4 va = __ldg(reinterpret_cast<const uint4*>(grow + j)), vb = __ldg(reinterpret_cast<const uint4*>(grow + hw + j));
+                a[0] = va.x, a[1] = va.y, a[2] = va.z, a[3] = va.w;
+                b[0] = vb.x, b[1] = vb.y, b[2] = vb.z, b[3] = vb.w;
+            } else {
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    a[u] = from_row ? __ldg(grow + j + u) : src[j + u];
+                    b[u] = from_row ? __ldg(grow + hw + j + u) : src[hw + j + u];
+                }
+            }
+            if (IS_G) {
+                const uint32_t bw = bword >> (4 * (j & 7));
+#pragma unroll
+                for (int u = 0; u < 4; ++u) r[u] = sw_g(a[u], b[u], sw_expand4(bw >> (4 * u)));
+            } else {
+#pragma unroll
+                for (int u = 0; u < 4; ++u) r[u] = sw_f(a[u], b[u]);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) dst.set(j + u, r[u]);
+        }
+    }
+    c.own_llr.set(s - 1, (uint32_t)c.l);
+}
+
 // f / g step of a node of size 2^s: parent LLRs (stage s, through the owner table or the channel row) -> child
 // LLRs (stage s-1, own buffer). RateRNode::decode scl_fip_char.cpp:315-349.
 template <bool IS_G, class Lane>
 __device__ __forceinline__ void scl_fg(Lane& c, const SclParams& p, int s, const int8_t* row)
 {
+    if (c.P == 1 && c.G >= 2 && (1 << (s - 1)) >= 32) { // at least eight words: two or more lanes of the group have work
+        scl_fg_single<IS_G>(c, p, s, row);
+        return;
+    }
     // Every lane runs the step (the decision-word reads may be warp-collective tensor-memory loads): a dead lane
     // reads through its (valid, copied) tables -- the same addresses as the path it was copied from, so no extra
     // traffic -- and only its stores are suppressed.
@@ -205,9 +260,23 @@ template <class Lane>
 __device__ __forceinline__ void llr_sums(const Lane& c, const SclParams& p, int s, int& neg, int& pos)
 {
     const int n = 1 << s, nw = stage_words(s);
-    const typename Lane::View v = c.view(p.llr_off[s], (uint32_t)c.l);
     neg = 0;
     pos = 0;
+    if (c.P == 1 && c.G >= 2 && nw >= 8) {
+        // one live path: the lanes of the group sum slices of ITS buffer (lane 0's column) and add up (exact integers)
+        const typename Lane::View v0 = c.view(p.llr_off[s], 0u);
+        for (int j = c.l; j < nw; j += c.G) {
+            const uint32_t w = v0[j], f = sw_signfill(w);
+            neg = __dp4a((int)(w & f), 0x01010101, neg);
+            pos = __dp4a((int)(w & ~f), 0x01010101, pos);
+        }
+        for (int off = c.G >> 1; off; off >>= 1) {
+            neg += __shfl_xor_sync(0xFFFFFFFFu, neg, off);
+            pos += __shfl_xor_sync(0xFFFFFFFFu, pos, off);
+        }
+        return;
+    }
+    const typename Lane::View v = c.view(p.llr_off[s], (uint32_t)c.l);
     if (nw >= 4) {
         int n1 = 0, p1 = 0; // two accumulator pairs, four loads in flight
         for (int j = 0; j < nw; j += 4) {
