@@ -358,9 +358,8 @@ class Puncturer:
 
     # ---- batch entry points ------------------------------------------------------------------------------------
     def _run(self, fn, x, n_in, n_out, elem=None):
-        import torch
-        is_t = hasattr(x, "is_cuda")
-        if is_t and x.is_cuda:
+        if hasattr(x, "is_cuda") and x.is_cuda:            # torch CUDA tensor: used in place, asynchronous
+            import torch
             if x.dim() != 2 or x.shape[1] != n_in:
                 raise RuntimeError("Input must be [B, %d]" % n_in)
             x = x.contiguous()
@@ -369,13 +368,29 @@ class Puncturer:
             e = x.element_size() if elem is None else elem
             check(fn(ptr(x), ptr(out), e, x.shape[0], st))
             return out
-        a = np.ascontiguousarray(x.numpy() if is_t else x)
+        # host arrays: staged through the C-ABI's own device helpers (no torch on this path)
+        a = np.ascontiguousarray(x.numpy() if hasattr(x, "numpy") else x)
         if a.ndim != 2 or a.shape[1] != n_in:
             raise RuntimeError("Input must be [B, %d]" % n_in)
         if a.dtype not in self._DTYPES:
             raise TypeError("unsupported dtype %s" % a.dtype)
-        d = torch.from_numpy(a).cuda()
-        return self._run(fn, d, n_in, n_out, elem).cpu().numpy()
+        B = a.shape[0]
+        out = np.empty((B, n_out), dtype=a.dtype)
+        if B == 0:
+            return out
+        e = a.dtype.itemsize if elem is None else elem
+        d_in, d_out = lib().pc_device_alloc(a.nbytes), lib().pc_device_alloc(out.nbytes)
+        try:
+            if not d_in or not d_out:
+                raise capi.PolarError(capi.last_error())
+            check(lib().pc_memcpy_h2d(ctypes.c_void_p(d_in), ptr(a), a.nbytes))
+            check(fn(ctypes.c_void_p(d_in), ctypes.c_void_p(d_out), e, B, None))
+            check(lib().pc_device_synchronize())
+            check(lib().pc_memcpy_d2h(ptr(out), ctypes.c_void_p(d_out), out.nbytes))
+        finally:
+            lib().pc_device_free(ctypes.c_void_p(d_in))
+            lib().pc_device_free(ctypes.c_void_p(d_out))
+        return out
 
     def puncture_batch(self, x):
         return self._run(lambda i, o, e, B, st: lib().pc_puncture_batch(self._h, i, o, e, B, st), x, self._Np, self._M)
