@@ -56,7 +56,10 @@ enum {
     /* the two wrappers pcsim builds directly (src/simulation/simulator.cpp:721-733), not reachable through
      * Decoding::create's type strings: */
     PC_DEC_ADAPTIVE_I8 = 5,   /* AdaptiveChar  (adaptive_char.cpp:35-46):  FastSscFipChar, then SclFipChar  */
-    PC_DEC_ADAPTIVE_MIXED = 6 /* AdaptiveMixed (adaptive_mixed.cpp:36-47): FastSscFipChar, then SclAvxFloat */
+    PC_DEC_ADAPTIVE_MIXED = 6, /* AdaptiveMixed (adaptive_mixed.cpp:36-47): FastSscFipChar, then SclAvxFloat */
+    /* pcsim's 'depthfirst' decoder (simulator.cpp:715-716): DepthFirst(N, trialLimit = L, frozen), SC-Flip on float LLRs
+     * (src/polarcode/decoding/depth_first.cpp:556-640); L is the trial limit (1 .. 32) */
+    PC_DEC_SCFLIP_F32 = 7
 };
 
 /* error detectors -- ErrorDetection::create(size, type) (errordetector.cpp:27-88) */

@@ -548,6 +548,7 @@ PC_B200_DECODER_CLASS_L(SclAvxFloat, PC_DEC_SCL_F32)         // scl_avx_float.h
 PC_B200_DECODER_CLASS_L(AdaptiveFloat, PC_DEC_ADAPTIVE_F32)  // adaptive_float.h
 PC_B200_DECODER_CLASS_L(AdaptiveChar, PC_DEC_ADAPTIVE_I8)    // adaptive_char.h
 PC_B200_DECODER_CLASS_L(AdaptiveMixed, PC_DEC_ADAPTIVE_MIXED) // adaptive_mixed.h
+PC_B200_DECODER_CLASS_L(DepthFirst, PC_DEC_SCFLIP_F32)        // depth_first.h: DepthFirst(N, trialLimit, frozenBits), SC-Flip
 #undef PC_B200_DECODER_CLASS_1
 #undef PC_B200_DECODER_CLASS_L
 

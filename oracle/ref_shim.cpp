@@ -14,6 +14,7 @@
 #include <polarcode/decoding/adaptive_char.h>
 #include <polarcode/decoding/adaptive_mixed.h>
 #include <polarcode/decoding/decoder.h>
+#include <polarcode/decoding/depth_first.h>
 #include <polarcode/encoding/butterfly_fip_packed.h>
 #include <polarcode/errordetection/errordetector.h>
 #include <polarcode/puncturer.h>
@@ -33,6 +34,7 @@ static Decoding::Decoder* make_decoder(int N, int L, const std::vector<unsigned>
 {
     if (kind == "adaptive_char") return new Decoding::AdaptiveChar(N, L, fz);
     if (kind == "adaptive_mixed") return new Decoding::AdaptiveMixed(N, L, fz);
+    if (kind == "depthfirst") return new Decoding::DepthFirst(N, L, fz); // pcsim's SC-Flip decoder (simulator.cpp:715-716), L = trial limit
     return Decoding::create(N, L, fz, kind);
 }
 

@@ -12,10 +12,10 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libpolar_b200.so")
 
 PC_DEC_FASTSSC_I8, PC_DEC_FASTSSC_F32, PC_DEC_SCL_I8, PC_DEC_SCL_F32, PC_DEC_ADAPTIVE_F32, PC_DEC_ADAPTIVE_I8, \
-    PC_DEC_ADAPTIVE_MIXED = range(7)
+    PC_DEC_ADAPTIVE_MIXED, PC_DEC_SCFLIP_F32 = range(8)
 PC_OK, PC_ERR_ARG, PC_ERR_CUDA, PC_ERR_UNSUPPORTED = range(4)
 
-FLOAT_LLR_KINDS = (PC_DEC_FASTSSC_F32, PC_DEC_SCL_F32, PC_DEC_ADAPTIVE_F32, PC_DEC_ADAPTIVE_MIXED)
+FLOAT_LLR_KINDS = (PC_DEC_FASTSSC_F32, PC_DEC_SCL_F32, PC_DEC_ADAPTIVE_F32, PC_DEC_ADAPTIVE_MIXED, PC_DEC_SCFLIP_F32)
 
 
 def kind_takes_float(kind):

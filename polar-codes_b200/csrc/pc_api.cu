@@ -302,7 +302,7 @@ int pc_crc_bytes(int crc_kind)
 
 pc_code* pc_code_create(int N, const unsigned* frozen, int n_frozen, int kind, int L)
 {
-    if (kind < PC_DEC_FASTSSC_I8 || kind > PC_DEC_ADAPTIVE_MIXED) {
+    if (kind < PC_DEC_FASTSSC_I8 || kind > PC_DEC_SCFLIP_F32) {
         set_error("Unknown PolarDecoder type!");
         return nullptr;
     }
@@ -408,6 +408,7 @@ void pc_code_destroy(pc_code* c)
     cudaFree(c->d_f32_in);
     cudaFree(c->arena);
     cudaFree(c->soft_arena);
+    cudaFree(c->scf_arena);
     cudaFree(c->d_stage_in);
     cudaFree(c->d_stage_out);
     cudaFree(c->d_stage_ok);

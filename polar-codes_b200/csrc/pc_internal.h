@@ -72,6 +72,8 @@ struct pc_code {
     int plan_small_cap = 0;       // CTA size cap plan_small was made for (0 = none)
     uint32_t* arena = nullptr;
     size_t arena_bytes = 0;
+    float* scf_arena = nullptr;       // pc_scflip_f32.cu: LLR stages, decision words, leaf reliabilities, flip words
+    size_t scf_arena_bytes = 0;
     uint32_t* soft_arena = nullptr;   // pc_fastssc_i8_soft.cu: LLR stages + N decision BYTES per thread
     size_t soft_arena_bytes = 0;
     // staging for the *_host entry points
@@ -100,6 +102,8 @@ int quantize_device(int N, const float* d_in, int8_t* d_out, size_t B, cudaStrea
 int encode_device(pc_code* c, const uint8_t* d_info, uint8_t* d_code, uint8_t* d_info_crc, size_t B, cudaStream_t st);
 int build_encoder_tables(pc_code* c);
 int encode_device_raw(pc_code* c, const uint8_t* d_info, uint8_t* d_code, size_t B, cudaStream_t st);
+int scflip_decode_device(pc_code* c, const float* d_llr, uint8_t* d_info, uint8_t* d_ok, size_t B, const unsigned* d_frame_idx,
+                         const unsigned long long* d_count, int trials, cudaStream_t st);
 int soft_decode_device(pc_code* c, const int8_t* d_llr, int8_t* d_soft_code, int8_t* d_soft_info, size_t B, cudaStream_t st);
 } // namespace pc
 #endif

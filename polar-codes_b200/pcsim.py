@@ -23,8 +23,9 @@ Differences, all forced by batching: timing columns are CUDA-event times of the 
 batch time / frames in the batch; min / max / deviation are over batches), "Encoder Bitrate" is measured on the fused
 generator launch (random info, detector, encode, BPSK, AWGN, scaling), `--threads` is accepted and ignored, frames are
 sharded over the ranks of an initialised torch.distributed group with one all_reduce(sum) of the counters per job.
-Out of scope (no GPU kernel, no CPU fallback): cmac detectors, the ask / fixed / depthfirst / scan / fastsscan
-simulation types, and the SCFlip / Fast-SSCAN / FFSSC rows of compareall (skipped with a note on stderr)."""
+Out of scope (no GPU kernel, no CPU fallback): cmac detectors, the ask / fixed / scan / fastsscan simulation types, and
+the Fast-SSCAN / FFSSC rows of compareall (skipped with a note on stderr). `depthfirst` (SC-Flip, DepthFirst with the list
+size as trial limit, simulator.cpp:303-321,715-716) runs on PC_DEC_SCFLIP_F32."""
 import argparse
 import ctypes
 import dataclasses
@@ -51,7 +52,8 @@ DEFAULTS = {
 }
 SIM_TYPES = ["single", "codelength", "designsnr", "listlength", "rate", "amplification", "fixed", "depthfirst", "scan",
              "fastsscan", "ask", "compareall", "getcode"]                                   # setup.cpp:77-81
-GPU_SIM_TYPES = ["single", "codelength", "designsnr", "listlength", "rate", "amplification", "compareall", "getcode"]
+GPU_SIM_TYPES = ["single", "codelength", "designsnr", "listlength", "rate", "amplification", "depthfirst", "compareall",
+                 "getcode"]
 ERROR_DETECTIONS = ["none", "crc8", "crc32", "cmac8", "cmac16", "cmac32", "cmac64", "cmac128"]  # setup.cpp:226-228
 
 # saveResults, simulator.cpp:528-533
@@ -173,6 +175,13 @@ def _configure_listlength(cfg):                                   # simulator.cp
     return jobs
 
 
+def _configure_depthfirst(cfg):                                   # simulator.cpp:303-321: the trial limit doubles from l-min to l-max
+    jobs = _configure_listlength(cfg)
+    for job in jobs:
+        job.decoderType = "depthfirst"
+    return jobs
+
+
 def _configure_rate(cfg):                                         # simulator.cpp:229-250
     jobs = []
     for r in _linspace_f32(cfg["r-min"], cfg["r-max"], int(cfg["r-count"])):
@@ -227,9 +236,9 @@ def _configure_compareall(cfg, skipped=None):                     # simulator.cp
     fixed = template.copy()
     fixed.name, fixed.decoderType, fixed.amplification = "FFSSC", "fixed", amp_hi
     jobs.append(fixed)
-    keep = [j for j in jobs if j.decoderType == "flexible"]
+    keep = [j for j in jobs if j.decoderType in ("flexible", "depthfirst")]
     if skipped is not None:
-        skipped.extend(j.name for j in jobs if j.decoderType != "flexible")
+        skipped.extend(j.name for j in jobs if j.decoderType not in ("flexible", "depthfirst"))
     return keep
 
 
@@ -259,7 +268,8 @@ def build_job_list(cfg, skipped=None):
     if st == "compareall":
         return _configure_compareall(cfg, skipped)               # "No SNR inflation"
     table = {"single": _configure_single, "codelength": _configure_codelength, "designsnr": _configure_designsnr,
-             "listlength": _configure_listlength, "rate": _configure_rate, "amplification": _configure_amplification}
+             "listlength": _configure_listlength, "rate": _configure_rate, "amplification": _configure_amplification,
+             "depthfirst": _configure_depthfirst}
     if st == "getcode":
         return []
     if st not in table:
@@ -268,7 +278,9 @@ def build_job_list(cfg, skipped=None):
 
 
 def decoder_kind(job):
-    """SimulationWorker::setCoders, simulator.cpp:703-765 (tFlexible branch)"""
+    """SimulationWorker::setCoders, simulator.cpp:703-765 (tFlexible and tDepthFirst branches)"""
+    if job.decoderType == "depthfirst":
+        return capi.PC_DEC_SCFLIP_F32                            # new DepthFirst(N, L, frozen), :715-716
     if job.decoderType != "flexible":
         raise NotImplementedError(f"decoder type '{job.decoderType}' has no GPU kernel (out of scope)")
     if job.L > 1:

@@ -31,10 +31,11 @@ def frozen_bits(blockLength, infoLength, designSNR, constructorType="BB"):
 
 
 def _kind_from_string(decoderType, listSize):
-    # extension: an int selects a PC_DEC_* kind directly (AdaptiveChar / AdaptiveMixed have no type string in the
-    # reference factory; pcsim constructs them by class, simulator.cpp:721-733)
+    # extension: an int selects a PC_DEC_* kind directly (AdaptiveChar / AdaptiveMixed / DepthFirst have no type string
+    # in the reference factory; pcsim constructs them by class, simulator.cpp:715-733). For PC_DEC_SCFLIP_F32 the list
+    # size argument is DepthFirst's trial limit.
     if isinstance(decoderType, int):
-        if not 0 <= decoderType <= capi.PC_DEC_ADAPTIVE_MIXED:
+        if not 0 <= decoderType <= capi.PC_DEC_SCFLIP_F32:
             raise RuntimeError("Unknown PolarDecoder type!")
         return decoderType
     # Decoding::create (reference src/polarcode/decoding/decoder.cpp:26-52): lower-case substring match

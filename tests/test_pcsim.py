@@ -81,19 +81,25 @@ def test_job_lists_per_simtype(sim):
     assert sorted({j.K for j in jobs}) == sorted(set(ks))
     jobs = sim.build_job_list(_cfg(sim, "amplification"))
     assert sorted({j.amplification for j in jobs}) == [float(f(1.0) + f(i) * (f(127.0) / f(5))) for i in range(6)]
-    for st in ("fixed", "depthfirst", "scan", "fastsscan", "ask"):
+    for st in ("fixed", "scan", "fastsscan", "ask"):
         with pytest.raises(NotImplementedError):
             sim.build_job_list(_cfg(sim, st))
+    # depthfirst (simulator.cpp:303-321): the trial limit doubles from l-min to l-max, every job inflated over the SNR grid
+    jobs = sim.build_job_list(_cfg(sim, "depthfirst", "--l-min", "2", "--l-max", "8"))
+    assert sorted({j.L for j in jobs}) == [2, 4, 8] and {j.decoderType for j in jobs} == {"depthfirst"}
+    assert sim.decoder_kind(jobs[0]) == sim.capi.PC_DEC_SCFLIP_F32
 
 
 def test_compareall_jobs(sim):
     """simulator.cpp:404-491: (N, K, Eb/N0) = (1024, 512, 2 dB) and (4096, 3072, 3 dB) per decoder; no SNR inflation"""
     skipped = []
     jobs = sim.build_job_list(_cfg(sim, "compareall"), skipped)
-    assert [j.name for j in jobs] == ["Fast-SSC32", "Fast-SSC32", "Fast-SSC8", "Fast-SSC8", "SCL32", "SCL32", "SCL8", "SCL8"]
-    assert skipped == ["SCFlip", "SCFlip", "Fast-SSCAN", "Fast-SSCAN", "FFSSC"]
+    assert [j.name for j in jobs] == ["Fast-SSC32", "Fast-SSC32", "Fast-SSC8", "Fast-SSC8", "SCL32", "SCL32", "SCL8", "SCL8",
+                                      "SCFlip", "SCFlip"]
+    assert skipped == ["Fast-SSCAN", "Fast-SSCAN", "FFSSC"]
     assert [(j.N, j.K, j.EbN0) for j in jobs[:2]] == [(1024, 512, 2.0), (4096, 3072, 3.0)]
-    assert [j.L for j in jobs] == [1, 1, 1, 1, 8, 8, 8, 8]
+    assert [j.L for j in jobs] == [1, 1, 1, 1, 8, 8, 8, 8, 8, 8]
+    assert [j.decoderType for j in jobs[8:]] == ["depthfirst"] * 2 and jobs[8].amplification == jobs[0].amplification
     assert jobs[0].amplification == float(np.float32(4 * 10 ** 0.2)) and jobs[1].amplification == float(np.float32(4 * 10 ** 0.3))
     assert jobs[2].amplification == 10.0 and jobs[7].amplification == 10.0
 
