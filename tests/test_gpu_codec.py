@@ -253,3 +253,47 @@ def test_full_size_properties(pcb, N, K, B):
         out, ok = dec.decode_batch(llr, return_ok=True)
         assert torch.equal(out, sent[:frames]) and bool((ok == 1).all())
         del bits, llr8, llr
+
+
+def test_code_object_is_bound_to_its_device(pcb):
+    """include/polar_b200.h "Devices, streams, alignment": a pc_code belongs to the device that was current at creation;
+    with another device current every entry point answers PC_ERR_ARG instead of faulting (needs two GPUs)."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    N, K = 256, 128
+    fz = pcb.frozen_bits(N, K, 0.0)
+    with torch.cuda.device(0):
+        dec = pcb.PolarDecoder(N, 1, fz, "char")
+        enc = pcb.PolarEncoder(N, fz)
+        llr0 = torch.zeros((8, N), dtype=torch.int8, device="cuda:0")
+        assert dec.decode_batch(llr0).shape == (8, K // 8)
+    with torch.cuda.device(1):
+        llr1 = torch.zeros((8, N), dtype=torch.int8, device="cuda:1")
+        with pytest.raises(ValueError, match="created on CUDA device 0"):
+            dec.decode_batch(llr1)
+        with pytest.raises(ValueError, match="created on CUDA device 0"):
+            enc.encode_batch(torch.zeros((8, K // 8), dtype=torch.uint8, device="cuda:1"))
+        # a second code object on the second device works, detector tables included (one table per device and kind)
+        dec1 = pcb.PolarDecoder(N, 1, fz, "char")
+        assert dec1.decode_batch(llr1).shape == (8, K // 8)
+        det = pcb.Detector(16, "crc")
+        assert det.check(det.generate(np.frombuffer(b"Test", np.uint8)))
+    with torch.cuda.device(0):
+        assert dec.decode_batch(llr0).shape == (8, K // 8)
+
+
+def test_misaligned_pointers_are_an_argument_error(pcb):
+    """16-byte aligned LLR batches, 4-byte aligned info batches: PC_ERR_ARG (ValueError), not a misaligned-address fault"""
+    import torch
+    N, K = 1024, 512
+    fz = pcb.frozen_bits(N, K, 0.0)
+    dec = pcb.PolarDecoder(N, 1, fz, "char")
+    buf = torch.zeros(4 * N + 64, dtype=torch.int8, device="cuda")
+    out = torch.empty((4, K // 8), dtype=torch.uint8, device="cuda")
+    ok = torch.empty(4, dtype=torch.uint8, device="cuda")
+    L_, ptr = pcb.capi.lib(), pcb.capi.ptr
+    with pytest.raises(ValueError, match="16-byte aligned"):
+        pcb.capi.check(L_.pc_decode_batch(dec._h, buf.data_ptr() + 4, 0, ptr(out), ptr(ok), 4, None))
+    pcb.capi.check(L_.pc_decode_batch(dec._h, buf.data_ptr() + 16, 0, ptr(out), ptr(ok), 4, None))
+    torch.cuda.synchronize()
