@@ -61,6 +61,7 @@ struct SclParams {
     int tm_cols_thread;  // columns per thread (warps sharing a lane quarter are stacked along columns)
     int scr_off;         // smem word offset of a per-lane scratch of N/32 words for extractBestPath
     int lockstep;        // CTA barrier after every node-program step (keeps the warps on the same instruction lines)
+    int sort2;           // scl_sort_packed2 (candidate index inside the sort key): groups of <= 8 lanes, N <= 4096
 };
 
 struct SclLaunch {

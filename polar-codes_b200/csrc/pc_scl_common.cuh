@@ -188,6 +188,57 @@ __device__ __forceinline__ void scl_sort_packed(const LN& c, const int (&v)[C], 
     }
 }
 
+// The same emulation for groups of at most 8 lanes (C * G <= 64 candidates) and |metric| < 2^19 (N <= 4096): the candidate's
+// ORIGINAL index rides in the key as well, key = (value << 12) | ((63 - position) << 6) | index, so the separate index
+// array, its dynamic-index selects and two of the three shuffles per pass go away (the sort was 28 % of the executed
+// instructions of k_scl_i8, profiles/r02_scl_i8_full_v2.txt). A pass: maximum of the keys (larger value wins, equal values
+// go to the lower position), the content of slot i moves to the winner's slot and takes its position bits, slot i is
+// consumed, new path i gets the winner's value and index.
+template <int C, class LN>
+__device__ __forceinline__ void scl_sort_packed2(const LN& c, const int (&v)[C], int newP, int& out_val, int& out_idx)
+{
+    static_assert((C & (C - 1)) == 0, "C must be a power of two");
+    constexpr int LOGC = C == 2 ? 1 : (C == 4 ? 2 : 3);
+    const int size = C * c.P, G = c.G;
+    int kv[C];
+#pragma unroll
+    for (int k = 0; k < C; ++k) {
+        const int pos = c.l * C + k;
+        kv[k] = pos < size ? (int)(((unsigned)v[k] << 12) | ((unsigned)(63 - pos) << 6) | (unsigned)pos) : INT_MIN;
+    }
+    const int lim = size - 1 < newP ? size - 1 : newP;
+    out_val = 0;
+    out_idx = 0;
+    for (int li = 0; li * C < lim; ++li) {
+#pragma unroll
+        for (int ki = 0; ki < C; ++ki) {
+            const int i = li * C + ki;
+            if (i < lim) { // uniform
+                int m = kv[0];
+#pragma unroll
+                for (int k = 1; k < C; ++k) m = max(m, kv[k]);
+                for (int off = G >> 1; off; off >>= 1) m = max(m, __shfl_xor_sync(0xFFFFFFFFu, m, off));
+                const int bp = 63 - ((m >> 6) & 63), lm = bp >> LOGC, km = bp & (C - 1);
+                const int vi = __shfl_sync(0xFFFFFFFFu, kv[ki], li, G);
+                if (c.l == lm) put(kv, km, (int)(((unsigned)vi & ~(63u << 6)) | ((unsigned)(63 - bp) << 6)));
+                if (c.l == li) kv[ki] = INT_MIN; // consumed (also when the maximum already sat in slot i)
+                if (c.l == i) {
+                    out_val = m >> 12;
+                    out_idx = m & 63;
+                }
+            }
+        }
+    }
+    if (lim < newP) { // size == newP: the last slot was never the target of a pass and keeps its content
+        const int lj = lim >> LOGC, kj = lim & (C - 1);
+        const int vj = __shfl_sync(0xFFFFFFFFu, sel(kv, kj), lj, G);
+        if (c.l == lim) {
+            out_val = vj >> 12;
+            out_idx = vj & 63;
+        }
+    }
+}
+
 // Indices[] bookkeeping of findWeakLlrs (arrayfuncs.h:209-231): the first four entries plus a patch list for
 // positions >= 4 (at most four swaps happen). swap(i, bp) is called once per pass with i < 4.
 struct WeakIdx {

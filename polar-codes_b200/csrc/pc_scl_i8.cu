@@ -91,6 +91,22 @@ struct LaneT {
         if (off & kArena) return View{ ar + (size_t)(off & (kArena - 1)) * AS + d, (uint32_t)AS };
         return View{ sm + (size_t)off * T + d, (uint32_t)T };
     }
+    // the lane's OWN stage in shared memory with the compile-time CTA size: 32-bit shared address, word w at + 4 TT w
+    struct SView {
+        uint32_t a;
+        __device__ __forceinline__ uint32_t operator[](int w) const { return lds_u32(a + 4u * (uint32_t)(TT ? TT : 1) * (uint32_t)w); }
+        __device__ __forceinline__ void set(int w, uint32_t v) const { sts_u32(a + 4u * (uint32_t)(TT ? TT : 1) * (uint32_t)w, v); }
+    };
+    // runs `f` on the own stage at `off`: the shared-memory form when the stage is there and TT is known (a shared load
+    // with a multiply-free address instead of a generic load behind a 64-bit multiply-add), else the general view
+    template <class F>
+    __device__ __forceinline__ void with_own_view(int off, F&& f) const
+    {
+        if (TT != 0 && !(off & kArena))
+            f(SView{ (uint32_t)__cvta_generic_to_shared(sm) + 4u * (uint32_t)(TT ? TT : 1) * (uint32_t)off });
+        else
+            f(view(off, (uint32_t)l));
+    }
 };
 
 __device__ __forceinline__ int stage_words(int s) { return s >= 2 ? (1 << (s - 2)) : 1; }   // LLR words
@@ -276,7 +292,7 @@ __device__ __forceinline__ void llr_sums(const Lane& c, const SclParams& p, int 
         }
         return;
     }
-    const typename Lane::View v = c.view(p.llr_off[s], (uint32_t)c.l);
+    c.with_own_view(p.llr_off[s], [&](const auto& v) {
     if (nw >= 4) {
         int n1 = 0, p1 = 0; // two accumulator pairs, four loads in flight
         for (int j = 0; j < nw; j += 4) {
@@ -302,6 +318,7 @@ __device__ __forceinline__ void llr_sums(const Lane& c, const SclParams& p, int 
         neg = __dp4a((int)(w & f), 0x01010101, neg);
         pos = __dp4a((int)(w & ~f), 0x01010101, pos);
     }
+    });
 }
 
 // RateZeroDecoder::decode scl_fip_char.cpp:387-421: metric += sum(min(llr, 0)), decisions 0, no fork, no re-sort
@@ -325,7 +342,7 @@ __device__ __forceinline__ void scl_find_weak(const Lane& c, int off, int n, int
 {
     int I[4] = { 0, 1, 2, 3 }, ppos[4] = { -1, -1, -1, -1 }, pidx[4] = { 0, 0, 0, 0 };
     int np = 0;
-    const typename Lane::View v = c.view(off, (uint32_t)c.l);
+    c.with_own_view(off, [&](const auto& v) {
     const int lim = n - 1 < want ? n - 1 : want;
     const int nw = (n + 3) >> 2;
     for (int i = 0; i < lim; ++i) {
@@ -394,6 +411,7 @@ __device__ __forceinline__ void scl_find_weak(const Lane& c, int off, int n, int
         const uint32_t x = v[k >> 2];
         wval[k] = (k < n) ? (int)((x >> (8 * (k & 3))) & 0xFFu) : 0;
     }
+    });
 }
 
 // first phase of RateOne / SPC leaves: decisions = signs into the own side buffer, |max(llr, -127)| in place,
@@ -402,35 +420,37 @@ template <class Lane>
 __device__ __forceinline__ uint32_t scl_signs_and_abs(const Lane& c, const SclParams& p, int s, int side)
 {
     const int n = 1 << s, nw = stage_words(s), dst = side ? p.bitR_off[s] : p.bitL_off[s];
-    const typename Lane::View v = c.view(p.llr_off[s], (uint32_t)c.l);
-    uint32_t par = 0, acc = 0;
-    if (nw >= 8) { // eight words (one decision word) per step, loads first
-        for (int j = 0; j < nw; j += 8) {
-            uint32_t w[8];
+    uint32_t par = 0;
+    c.with_own_view(p.llr_off[s], [&](const auto& v) {
+        uint32_t acc = 0;
+        if (nw >= 8) { // eight words (one decision word) per step, loads first
+            for (int j = 0; j < nw; j += 8) {
+                uint32_t w[8];
 #pragma unroll
-            for (int u = 0; u < 8; ++u) w[u] = v[j + u];
+                for (int u = 0; u < 8; ++u) w[u] = v[j + u];
 #pragma unroll
-            for (int u = 0; u < 8; ++u) {
-                par ^= w[u];
-                acc |= sw_movemask(w[u]) << (4 * u);
-                v.set(j + u, sw_abs_sat(w[u]));
+                for (int u = 0; u < 8; ++u) {
+                    par ^= w[u];
+                    acc |= sw_movemask(w[u]) << (4 * u);
+                    v.set(j + u, sw_abs_sat(w[u]));
+                }
+                c.st(dst + (j >> 3), acc);
+                acc = 0;
             }
-            c.st(dst + (j >> 3), acc);
-            acc = 0;
+            return;
         }
-        return par;
-    }
-    for (int j = 0; j < nw; ++j) {
-        uint32_t w = v[j];
-        if (n < 4) w &= bytemask(n);
-        par ^= w;
-        acc |= sw_movemask(w) << (4 * (j & 7));
-        v.set(j, sw_abs_sat(w));
-        if ((j & 7) == 7 || j == nw - 1) {
-            c.st(dst + (j >> 3), acc);
-            acc = 0;
+        for (int j = 0; j < nw; ++j) {
+            uint32_t w = v[j];
+            if (n < 4) w &= bytemask(n);
+            par ^= w;
+            acc |= sw_movemask(w) << (4 * (j & 7));
+            v.set(j, sw_abs_sat(w));
+            if ((j & 7) == 7 || j == nw - 1) {
+                c.st(dst + (j >> 3), acc);
+                acc = 0;
+            }
         }
-    }
+    });
     return par;
 }
 
@@ -447,7 +467,10 @@ __device__ __forceinline__ void scl_rep(Lane& c, const SclParams& p, int s, int 
     }
     const int newP = 2 * c.P < p.L ? 2 * c.P : p.L;
     int val, idx;
-    scl_sort_packed<2>(c, v, newP, val, idx);
+    if (p.sort2)
+        scl_sort_packed2<2>(c, v, newP, val, idx);
+    else
+        scl_sort_packed<2>(c, v, newP, val, idx);
     const bool live = c.l < newP;
     const int sp = live ? idx >> 1 : 0;
     scl_fork(c, sp, val, newP);
@@ -474,7 +497,10 @@ __device__ __forceinline__ void scl_r1(Lane& c, const SclParams& p, int s, int s
     __syncwarp();
     const int newP = 4 * c.P < p.L ? 4 * c.P : p.L;
     int val, idx;
-    scl_sort_packed<4>(c, v, newP, val, idx);
+    if (p.sort2)
+        scl_sort_packed2<4>(c, v, newP, val, idx);
+    else
+        scl_sort_packed<4>(c, v, newP, val, idx);
     const bool live = c.l < newP;
     const int sp = live ? idx >> 2 : 0;
     int fi[4];
@@ -516,7 +542,10 @@ __device__ __forceinline__ void scl_spc(Lane& c, const SclParams& p, int s, int 
     __syncwarp();
     const int newP = 8 * c.P < p.L ? 8 * c.P : p.L;
     int val, idx;
-    scl_sort_packed<8>(c, v, newP, val, idx);
+    if (p.sort2)
+        scl_sort_packed2<8>(c, v, newP, val, idx);
+    else
+        scl_sort_packed<8>(c, v, newP, val, idx);
     const bool live = c.l < newP;
     const int sp = live ? idx >> 3 : 0;
     int fi[4];
@@ -796,6 +825,7 @@ static int plan_scl_i8_smem(int S, int K, int L, bool root_leaf, size_t smem_max
     p.tm_alloc_cols = 0;
     p.tm_cols_thread = 0;
     p.lockstep = getenv("PC_SCL_LOCKSTEP") ? atoi(getenv("PC_SCL_LOCKSTEP")) != 0 : 0;
+    p.sort2 = (G <= 8 && S <= 12 && !getenv("PC_SCL_SORT1")) ? 1 : 0;
     p.scr_off = p.bitL_off[S]; // non-systematic extraction works on the (free) left buffer of the top stage
     out.threads = T;
     out.smem_bytes = 1024 + 4 * (size_t)w * T;
@@ -894,6 +924,7 @@ int plan_scl_i8(int S, int K, int L, bool root_leaf, size_t smem_max, int sms, S
             p.tm_cols_thread = tm_cols;
             p.scr_off = scr;
             p.lockstep = lockstep ? 1 : 0;
+            p.sort2 = (G <= 8 && S <= 12 && !getenv("PC_SCL_SORT1")) ? 1 : 0; // 8 G <= 64 candidates, |metric| < 2^19
             out.threads = T;
             out.smem_bytes = 1024 + 4 * (size_t)w * T;
             out.grid = sms * per_sm;
