@@ -23,30 +23,50 @@ constexpr int kTmem = 1 << 29;
 // bit modes of a kernel instantiation: which flags the decision-word accessors test
 enum : int { BM_SMEM = 0, BM_ARENA = 1, BM_TMEM = 2 };
 
-struct Tbl { // 5-bit owner lane per stage
-    uint32_t w[3];
+struct Tbl { // owner lane per stage, one byte each (stages 0 .. 15)
+    uint32_t w[4];
     __device__ __forceinline__ uint32_t get(int s) const
     {
-        const uint32_t v = s < 6 ? w[0] : (s < 12 ? w[1] : w[2]);
-        return (v >> (5 * (s % 6))) & 31u;
+        const int q = s >> 2;
+        const uint32_t v = q == 0 ? w[0] : (q == 1 ? w[1] : (q == 2 ? w[2] : w[3]));
+        return __byte_perm(v, 0u, 0x4440u | (uint32_t)(s & 3)); // byte s % 4 into the low byte, zeros above
     }
     __device__ __forceinline__ void set(int s, uint32_t lane)
     {
-        const uint32_t sh = 5u * (uint32_t)(s % 6), m = ~(31u << sh), b = lane << sh;
-        if (s < 6)
+        const int q = s >> 2;
+        const uint32_t sh = 8u * (uint32_t)(s & 3), m = ~(0xFFu << sh), b = lane << sh;
+        if (q == 0)
             w[0] = (w[0] & m) | b;
-        else if (s < 12)
+        else if (q == 1)
             w[1] = (w[1] & m) | b;
-        else
+        else if (q == 2)
             w[2] = (w[2] & m) | b;
+        else
+            w[3] = (w[3] & m) | b;
     }
     __device__ __forceinline__ void copy_from(const Tbl& o, int src, int width)
     {
         w[0] = __shfl_sync(0xFFFFFFFFu, o.w[0], src, width);
         w[1] = __shfl_sync(0xFFFFFFFFu, o.w[1], src, width);
         w[2] = __shfl_sync(0xFFFFFFFFu, o.w[2], src, width);
+        w[3] = __shfl_sync(0xFFFFFFFFu, o.w[3], src, width);
     }
 };
+
+// maximum over the G (power of two) lanes of a group, levels unrolled (the rolled loop spent as many instructions on
+// its own control as on the shuffles)
+__device__ __forceinline__ int group_max(int m, int G)
+{
+    switch (G) {
+    case 32: m = max(m, __shfl_xor_sync(0xFFFFFFFFu, m, 16)); // fall through
+    case 16: m = max(m, __shfl_xor_sync(0xFFFFFFFFu, m, 8));  // fall through
+    case 8: m = max(m, __shfl_xor_sync(0xFFFFFFFFu, m, 4));   // fall through
+    case 4: m = max(m, __shfl_xor_sync(0xFFFFFFFFu, m, 2));   // fall through
+    case 2: m = max(m, __shfl_xor_sync(0xFFFFFFFFu, m, 1));   // fall through
+    default: break;
+    }
+    return m;
+}
 
 __device__ __forceinline__ int stage_bwords(int s) { return s >= 5 ? (1 << (s - 5)) : 1; } // decision words
 
@@ -160,7 +180,7 @@ __device__ __forceinline__ void scl_sort_packed(const LN& c, const int (&v)[C], 
                 if (G == 32)
                     m = __reduce_max_sync(0xFFFFFFFFu, m);
                 else
-                    for (int off = G >> 1; off; off >>= 1) m = max(m, __shfl_xor_sync(0xFFFFFFFFu, m, off));
+                    m = group_max(m, G);
                 const int bp = 255 - (m & 255), lm = bp >> LOGC, km = bp & (C - 1);
                 const int im = __shfl_sync(0xFFFFFFFFu, sel(idx, km), lm, G);
                 const int vi = __shfl_sync(0xFFFFFFFFu, kv[ki], li, G);
@@ -217,7 +237,7 @@ __device__ __forceinline__ void scl_sort_packed2(const LN& c, const int (&v)[C],
                 int m = kv[0];
 #pragma unroll
                 for (int k = 1; k < C; ++k) m = max(m, kv[k]);
-                for (int off = G >> 1; off; off >>= 1) m = max(m, __shfl_xor_sync(0xFFFFFFFFu, m, off));
+                m = group_max(m, G);
                 const int bp = 63 - ((m >> 6) & 63), lm = bp >> LOGC, km = bp & (C - 1);
                 const int vi = __shfl_sync(0xFFFFFFFFu, kv[ki], li, G);
                 if (c.l == lm) put(kv, km, (int)(((unsigned)vi & ~(63u << 6)) | ((unsigned)(63 - bp) << 6)));

@@ -76,15 +76,29 @@ struct FLaneT {
     // LLR stage s (off = p.llr_off[s]) in lane `owner`'s space, resolved once per node step
     struct View {
         float* p;
-        size_t stride;
-        __device__ __forceinline__ float operator[](int i) const { return p[(size_t)i * stride]; }
-        __device__ __forceinline__ void set(int i, float v) const { p[(size_t)i * stride] = v; }
+        uint32_t stride; // element index * stride stays below 2^32 (the planner bounds the arena at 1 GiB)
+        __device__ __forceinline__ float operator[](int i) const { return p[(uint32_t)i * stride]; }
+        __device__ __forceinline__ void set(int i, float v) const { p[(uint32_t)i * stride] = v; }
     };
     __device__ __forceinline__ View view(int s, int off, uint32_t owner) const
     {
         const ptrdiff_t d = (int)owner - l;
-        if (s <= smem_top) return View{ reinterpret_cast<float*>(sm) + (size_t)off * T + d, (size_t)T };
-        return View{ ar + (size_t)off * AS + d, AS };
+        if (s <= smem_top) return View{ reinterpret_cast<float*>(sm) + (size_t)off * T + d, (uint32_t)T };
+        return View{ ar + (size_t)off * AS + d, (uint32_t)AS };
+    }
+    // the lane's OWN stage in shared memory with the compile-time CTA size: 32-bit shared address, element i at + 4 TT i
+    struct SView {
+        uint32_t a;
+        __device__ __forceinline__ float operator[](int i) const { return lds_f32(a + 4u * (uint32_t)(TT ? TT : 1) * (uint32_t)i); }
+        __device__ __forceinline__ void set(int i, float v) const { sts_f32(a + 4u * (uint32_t)(TT ? TT : 1) * (uint32_t)i, v); }
+    };
+    template <class F>
+    __device__ __forceinline__ void with_own_view(int s, int off, F&& f) const
+    {
+        if (TT != 0 && s <= smem_top)
+            f(SView{ (uint32_t)__cvta_generic_to_shared(sm) + 4u * (uint32_t)(TT ? TT : 1) * (uint32_t)off });
+        else
+            f(view(s, off, (uint32_t)l));
     }
     // LLR element i of stage s (off = p.llr_off[s]) in lane `owner`'s space
     __device__ __forceinline__ float lld(int s, int off, int i, uint32_t owner) const
@@ -326,7 +340,7 @@ __device__ __forceinline__ void sclf_sums(const FLane& c, const SclFParams& p, i
 {
     const int n = 1 << s;
     // (no lane sharing here even while one path is alive: the order of the float additions is part of the result)
-    const typename FLane::View v = c.view(s, p.llr_off[s], (uint32_t)c.l);
+    c.with_own_view(s, p.llr_off[s], [&](const auto& v) {
     float an[8], ap[8], aa[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) an[k] = ap[k] = aa[k] = 0.0f;
@@ -344,6 +358,7 @@ __device__ __forceinline__ void sclf_sums(const FLane& c, const SclFParams& p, i
     neg = reduce_add8(an);
     pos = WANT_ALL ? reduce_add8(ap) : 0.0f;
     all = WANT_ALL ? reduce_add8(aa) : 0.0f;
+    });
 }
 
 // RateZeroDecoder::decode scl_avx_float.cpp:316-337: metric += sum(min(llr, 0)), decisions 0, no fork, no re-sort
@@ -368,7 +383,7 @@ __device__ __forceinline__ void sclf_find_weak(const FLane& c, int s, int off, i
     WeakIdx ix;
     ix.init();
     const int lim = n - 1 < want ? n - 1 : want;
-    const typename FLane::View v = c.view(s, off, (uint32_t)c.l);
+    c.with_own_view(s, off, [&](const auto& v) {
     for (int i = 0; i < lim; ++i) {
         const float vi = v[i];
         float bv = vi;
@@ -392,6 +407,7 @@ __device__ __forceinline__ void sclf_find_weak(const FLane& c, int s, int off, i
         widx[k] = ix.I[k];
         wval[k] = (k < n) ? v[k] : INFINITY; // pads of the 8-float block hold +inf (:363-365,:517-519)
     }
+    });
 }
 
 // first phase of RateOne / SPC leaves: decisions = sign bits into the own side buffer, |llr| in place; returns the
@@ -400,37 +416,41 @@ template <class FLane>
 __device__ __forceinline__ uint32_t sclf_signs_and_abs(const FLane& c, const SclFParams& p, int s, int side)
 {
     const int n = 1 << s, dst = side ? p.bitR_off[s] : p.bitL_off[s];
-    const typename FLane::View v = c.view(s, p.llr_off[s], (uint32_t)c.l);
-    uint32_t par = 0, acc = 0;
-    if (n >= 4) { // four loads in flight, then the in-place stores
-        for (int j = 0; j < n; j += 4) {
-            const float x0 = v[j], x1 = v[j + 1], x2 = v[j + 2], x3 = v[j + 3];
-            const uint32_t s4 = fsign(x0) | (fsign(x1) << 1) | (fsign(x2) << 2) | (fsign(x3) << 3);
-            acc |= s4 << (j & 31);
-            v.set(j, fabs_(x0));
-            v.set(j + 1, fabs_(x1));
-            v.set(j + 2, fabs_(x2));
-            v.set(j + 3, fabs_(x3));
-            if ((j & 31) == 28 || j == n - 4) {
-                par ^= acc;
+    uint32_t result = 0;
+    c.with_own_view(s, p.llr_off[s], [&](const auto& v) {
+        uint32_t par = 0, acc = 0;
+        if (n >= 4) { // four loads in flight, then the in-place stores
+            for (int j = 0; j < n; j += 4) {
+                const float x0 = v[j], x1 = v[j + 1], x2 = v[j + 2], x3 = v[j + 3];
+                const uint32_t s4 = fsign(x0) | (fsign(x1) << 1) | (fsign(x2) << 2) | (fsign(x3) << 3);
+                acc |= s4 << (j & 31);
+                v.set(j, fabs_(x0));
+                v.set(j + 1, fabs_(x1));
+                v.set(j + 2, fabs_(x2));
+                v.set(j + 3, fabs_(x3));
+                if ((j & 31) == 28 || j == n - 4) {
+                    par ^= acc;
+                    c.st(dst + (j >> 5), acc);
+                    acc = 0;
+                }
+            }
+            result = __popc(par) & 1u;
+            return;
+        }
+        for (int j = 0; j < n; ++j) {
+            const float x = v[j];
+            const uint32_t sg = fsign(x);
+            par ^= sg;
+            acc |= sg << (j & 31);
+            v.set(j, fabs_(x));
+            if ((j & 31) == 31 || j == n - 1) {
                 c.st(dst + (j >> 5), acc);
                 acc = 0;
             }
         }
-        return __popc(par) & 1u;
-    }
-    for (int j = 0; j < n; ++j) {
-        const float x = v[j];
-        const uint32_t sg = fsign(x);
-        par ^= sg;
-        acc |= sg << (j & 31);
-        v.set(j, fabs_(x));
-        if ((j & 31) == 31 || j == n - 1) {
-            c.st(dst + (j >> 5), acc);
-            acc = 0;
-        }
-    }
-    return par;
+        result = par;
+    });
+    return result;
 }
 
 // RepetitionDecoder::decode scl_avx_float.cpp:428-481 (only built for n < 8)
@@ -577,7 +597,7 @@ __global__ void __launch_bounds__(TT ? TT : 384, 1) k_scl_f32(const __grid_const
         c.P = 1;
         c.metric = 0.0f;
         c.root_right = 0;
-        c.own_llr = Tbl{ { 0u, 0u, 0u } };
+        c.own_llr = Tbl{ { 0u, 0u, 0u, 0u } };
         c.own_L = c.own_llr;
         c.own_R = c.own_llr;
         if (p.root_leaf && c.l == 0) // stage the channel row (the root is a leaf), setFirstPath :103-109

@@ -602,7 +602,7 @@ __global__ void __launch_bounds__(512, 1) k_scl_i8(const __grid_constant__ SclPa
         const int8_t* row = p.llr + f * N;
         c.P = 1;
         c.metric = 0;
-        c.own_llr = Tbl{ { 0u, 0u, 0u } };
+        c.own_llr = Tbl{ { 0u, 0u, 0u, 0u } };
         c.own_L = c.own_llr;
         c.own_R = c.own_llr;
         if (p.root_leaf && c.l == 0) { // stage the channel row (the root is a leaf)
