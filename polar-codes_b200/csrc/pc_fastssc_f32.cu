@@ -215,6 +215,207 @@ __global__ void __launch_bounds__(128) k_fastssc_f32_g8(const __grid_constant__ 
     }
 }
 
+// ---- on-chip form: one thread per codeword, FEW threads per SM, the whole LLR tree in shared + tensor memory ---------
+// The arena kernel above runs at 25 % issue utilisation behind DRAM latency: 3.4 k warp instructions and 47 KB of DRAM
+// traffic per codeword. Here a codeword's tree never leaves the SM. Per thread:
+//   tensor memory  stage S-1 (N / 2 floats, one column each; tcgen05.ld/st 32x32b.x8 move eight consecutive elements per
+//                  instruction, and all lanes of a warp use the same element index, which is what the instruction wants)
+//   shared memory  stages 0 .. S-2 (N / 2 - 1 floats) and the N / 32 decision words, thread-interleaved: a warp access is
+//                  one conflict-free 128-byte row and, T being a compile-time constant, `base + immediate`
+//   channel row    read in place with 16-byte loads, 32 element pairs in flight per thread
+// Capacity decides the CTA: N = 1024 needs 512 columns + 543 words per thread -> 96 threads per SM (tensor memory has
+// 128 lanes x 512 columns, shared memory 227 KB); N = 512: 2 CTAs x 96; N = 256: 3 CTAs x 128 (plan_f32). Codes whose
+// stage S-1 does not fit 512 columns (N > 1024) stay on the arena kernel.
+// Same core functions (pc_fastssc_f32_core.h) on different views, so the results are the arena kernel's bit for bit.
+__device__ __forceinline__ float lds_f32(uint32_t a)
+{
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ void sts_f32(uint32_t a, float v) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v) : "memory"); }
+__device__ __forceinline__ uint32_t lds_w(uint32_t a)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ void sts_w(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+__device__ __forceinline__ void tm_ld8_f32(uint32_t taddr, float* a)
+{
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=f"(a[0]), "=f"(a[1]), "=f"(a[2]), "=f"(a[3]), "=f"(a[4]), "=f"(a[5]), "=f"(a[6]), "=f"(a[7])
+                 : "r"(taddr)
+                 : "memory");
+}
+__device__ __forceinline__ void tm_st8_f32(uint32_t taddr, const float* a)
+{
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr), "f"(a[0]),
+                 "f"(a[1]), "f"(a[2]), "f"(a[3]), "f"(a[4]), "f"(a[5]), "f"(a[6]), "f"(a[7])
+                 : "memory");
+}
+
+template <int T>
+struct SmView { // a stage in shared memory
+    static constexpr int kBatch = 8;
+    uint32_t a; // shared address of this thread's element 0
+    __device__ __forceinline__ float operator[](int i) const { return lds_f32(a + 4u * T * (uint32_t)i); }
+    __device__ __forceinline__ void ld8(int i, float* v) const
+    {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = lds_f32(a + 4u * T * (uint32_t)(i + k));
+    }
+    __device__ __forceinline__ void wait() const {}
+};
+struct TmView { // stage S-1 in tensor memory
+    static constexpr int kBatch = 16;
+    uint32_t t; // tensor-memory address of this warp's lane quarter, column of element 0
+    __device__ __forceinline__ float operator[](int i) const
+    {
+        uint32_t v;
+        __syncwarp(); // leaves branch on data; the load is warp-collective
+        tm_ld1_nowait(t + (uint32_t)i, v);
+        tm_wait_ld();
+        return __uint_as_float(v);
+    }
+    __device__ __forceinline__ void ld8(int i, float* v) const { tm_ld8_f32(t + (uint32_t)i, v); }
+    __device__ __forceinline__ void wait() const { tm_wait_ld(); }
+};
+struct RowView { // the channel row in global memory, contiguous and 16-byte aligned
+    static constexpr int kBatch = 32;
+    const float* p;
+    __device__ __forceinline__ float operator[](int i) const { return __ldg(p + i); }
+    __device__ __forceinline__ void ld8(int i, float* v) const
+    {
+        const float4 x = __ldg(reinterpret_cast<const float4*>(p + i)), y = __ldg(reinterpret_cast<const float4*>(p + i + 4));
+        v[0] = x.x, v[1] = x.y, v[2] = x.z, v[3] = x.w, v[4] = y.x, v[5] = y.y, v[6] = y.z, v[7] = y.w;
+    }
+    __device__ __forceinline__ void wait() const {}
+};
+
+// DST_TM: the step's destination stage (s - 1) is stage S-1 in tensor memory, else a shared-memory stage
+template <int T, bool DST_TM>
+struct SmCtx {
+    uint32_t sm_llr;  // shared address of this thread's element 0 of stage 0 (stage s starts 2^s - 1 elements further)
+    uint32_t sm_bits; // shared address of this thread's decision word 0
+    uint32_t tm;      // tensor-memory address of column 0 of stage S-1 in this warp's lane quarter
+    __device__ __forceinline__ SmView<T> sview(int s) const { return SmView<T>{ sm_llr + 4u * T * ((1u << s) - 1u) }; }
+    __device__ __forceinline__ void st(int s, int i, float v) const
+    {
+        if (DST_TM) {
+            __syncwarp();
+            tm_st1(tm + (uint32_t)i, __float_as_uint(v));
+        } else {
+            sts_f32(sm_llr + 4u * T * (((1u << s) - 1u) + (uint32_t)i), v);
+        }
+    }
+    __device__ __forceinline__ void st8(int s, int i, const float* v) const
+    {
+        if (DST_TM) {
+            tm_st8_f32(tm + (uint32_t)i, v);
+        } else {
+            const uint32_t a = sm_llr + 4u * T * (((1u << s) - 1u) + (uint32_t)i);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) sts_f32(a + 4u * T * k, v[k]);
+        }
+    }
+    __device__ __forceinline__ uint32_t bld(int w) const { return lds_w(sm_bits + 4u * T * (uint32_t)w); }
+    __device__ __forceinline__ void bst(int w, uint32_t v) const { sts_w(sm_bits + 4u * T * (uint32_t)w, v); }
+    __device__ __forceinline__ uint32_t bit(int i) const { return (bld(i >> 5) >> (i & 31)) & 1u; }
+    template <class Gen>
+    __device__ __forceinline__ void put_bits(int off, int n, const Gen& gen) const
+    {
+        if (n >= 32) {
+            for (int w = 0; w < (n >> 5); ++w) {
+                uint32_t v = 0;
+#pragma unroll 8
+                for (int k = 0; k < 32; ++k) v |= (gen(32 * w + k) & 1u) << k;
+                bst((off >> 5) + w, v);
+            }
+        } else {
+            uint32_t v = 0;
+            for (int k = 0; k < n; ++k) v |= (gen(k) & 1u) << k;
+            const int sh = off & 31;
+            const uint32_t m = lowmask(n) << sh;
+            bst(off >> 5, (bld(off >> 5) & ~m) | (v << sh));
+        }
+    }
+};
+
+// HAS_TM: stage S-1 lives in tensor memory (p.sm_top == S - 2); else every stage is in shared memory (p.sm_top == S - 1)
+template <int T, bool HAS_TM>
+__global__ void __launch_bounds__(T, 1) k_fastssc_f32_sm(const __grid_constant__ F32Params p)
+{
+    extern __shared__ __align__(16) uint32_t smem_sm[];
+    __shared__ uint32_t tm_base_s;
+    const int t = threadIdx.x;
+    uint32_t* crc_table = smem_sm; // 256 words
+    if (p.crc.width)
+        for (int i = t; i < 256; i += T) crc_table[i] = p.crc_table[i];
+    if (HAS_TM) {
+        if (t < 32) {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                             (uint32_t)__cvta_generic_to_shared(&tm_base_s)),
+                         "r"((uint32_t)p.sm_tm_cols));
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;");
+    }
+    __syncthreads();
+    if (HAS_TM) asm volatile("tcgen05.fence::after_thread_sync;");
+    const int S = p.S, top = p.sm_top, g0 = (2 << top) - 1;
+    uint32_t* bits_gen = smem_sm + 256 + (size_t)g0 * T + t;
+    SmCtx<T, false> cs;
+    cs.sm_llr = (uint32_t)__cvta_generic_to_shared(smem_sm + 256 + t);
+    cs.sm_bits = (uint32_t)__cvta_generic_to_shared(bits_gen);
+    cs.tm = HAS_TM ? tm_base_s + ((uint32_t)((t >> 5) & 3) << 21) : 0u; // lane field = 32 * (warp % 4), bits 31:16
+    SmCtx<T, true> ct;
+    ct.sm_llr = cs.sm_llr, ct.sm_bits = cs.sm_bits, ct.tm = cs.tm;
+    Ctx ic; // the int8 core's decision-word helpers (transform, gather) on the same words
+    ic.S = S;
+    ic.bits_kind = PK_SMEM;
+    ic.bits = bits_gen;
+    ic.bws = T;
+    const int N = 1 << S, kb = (p.K + 7) >> 3;
+    // warp-uniform frame loop: the tensor-memory accesses are warp-collective, so the lanes past the end of the batch
+    // decode the last frame again and keep the result to themselves
+    const unsigned long long w0 = (unsigned long long)blockIdx.x * T + (t & ~31);
+    for (unsigned long long fw = w0; fw < p.B; fw += (unsigned long long)gridDim.x * T) {
+        const unsigned long long fl = fw + (t & 31);
+        const bool live = fl < p.B;
+        const unsigned long long f = live ? fl : p.B - 1;
+        const float* row = p.llr + f * N;
+        for (int pc = 0;; ++pc) {
+            const uint32_t ins = p.code[pc];
+            const uint32_t op = instr_op(ins);
+            const int s = (int)instr_s(ins), off = (int)instr_off(ins);
+            if (op == FOP_END) break;
+            if (s <= top) {
+                fastssc_f32_step(cs, cs.sview(s), op, s, off);
+            } else if (s == S) {
+                if (HAS_TM) {
+                    fastssc_f32_step(ct, RowView{ row }, op, s, off);
+                    tm_wait_st();
+                } else {
+                    fastssc_f32_step(cs, RowView{ row }, op, s, off);
+                }
+            } else if (HAS_TM) {
+                fastssc_f32_step(cs, TmView{ cs.tm }, op, s, off);
+            }
+            __syncwarp();
+        }
+        if (!p.systematic) transform_bits_inplace(ic);
+        const bool res = extract_info(ic, p.runs, p.nruns, p.K, p.info + f * kb, p.crc, crc_table, live);
+        if (p.ok && live) p.ok[f] = res ? 1 : 0;
+    }
+    if (HAS_TM) {
+        asm volatile("tcgen05.fence::before_thread_sync;");
+        __syncthreads();
+        if (t < 32)
+            asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tm_base_s), "r"((uint32_t)p.sm_tm_cols));
+    }
+}
+
 // FloatContainer::insertLlr(const char*) (reference src/polarcode/bitcontainer.cpp:202-207): int8 -> float
 __global__ void __launch_bounds__(256) k_i8_to_f32(const int8_t* __restrict__ in, float* __restrict__ out, unsigned long long n)
 {
@@ -229,6 +430,21 @@ cudaError_t launch_i8_to_f32(const int8_t* d_in, float* d_out, size_t n, cudaStr
     if (g > 148 * 32) g = 148 * 32;
     k_i8_to_f32<<<(int)g, 256, 0, st>>>(d_in, d_out, n);
     return cudaGetLastError();
+}
+
+template <class K>
+static int sm_occ(K kern, const F32Launch& L)
+{
+    int n = 0;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.sm_smem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
+    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, L.sm_threads, L.sm_smem);
+    return e == cudaSuccess ? n : -1;
+}
+int fastssc_f32_sm_occupancy(const F32Launch& L)
+{
+    if (L.sm_threads == 128) return L.p.sm_tm_cols ? sm_occ(k_fastssc_f32_sm<128, true>, L) : sm_occ(k_fastssc_f32_sm<128, false>, L);
+    return L.p.sm_tm_cols ? sm_occ(k_fastssc_f32_sm<96, true>, L) : sm_occ(k_fastssc_f32_sm<96, false>, L);
 }
 
 cudaError_t launch_fastssc_f32(const F32Launch& L, const float* d_llr, uint8_t* d_info, uint8_t* d_ok, size_t B, cudaStream_t st)
@@ -248,6 +464,20 @@ cudaError_t launch_fastssc_f32(const F32Launch& L, const float* d_llr, uint8_t* 
         if (e != cudaSuccess) return e;
         k_fastssc_f32_g8<<<grid, L.g8_threads, L.g8_smem, st>>>(p);
         return cudaGetLastError();
+    }
+    if (L.sm) {
+        size_t nb = (B + L.sm_threads - 1) / L.sm_threads;
+        const int grid = (int)(nb < (size_t)L.sm_grid ? nb : (size_t)L.sm_grid);
+        auto go = [&](auto kern) -> cudaError_t {
+            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.sm_smem);
+            if (e == cudaSuccess)
+                e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
+            if (e != cudaSuccess) return e;
+            kern<<<grid, L.sm_threads, L.sm_smem, st>>>(p);
+            return cudaGetLastError();
+        };
+        if (L.sm_threads == 128) return L.p.sm_tm_cols ? go(k_fastssc_f32_sm<128, true>) : go(k_fastssc_f32_sm<128, false>);
+        return L.p.sm_tm_cols ? go(k_fastssc_f32_sm<96, true>) : go(k_fastssc_f32_sm<96, false>);
     }
     size_t ctas = (B + L.threads - 1) / L.threads;
     const int grid = (int)(ctas < (size_t)L.grid ? ctas : (size_t)L.grid);

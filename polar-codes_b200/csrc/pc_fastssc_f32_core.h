@@ -60,10 +60,21 @@ PC_HD float f_f32(float a, float b) { return u2f(((f2u(a) ^ f2u(b)) & 0x80000000
 PC_HD float g_f32(float a, float b, uint32_t bit) { return fadd(u2f(f2u(a) ^ (bit << 31)), b); }
 
 // strided view of a float array (thread-interleaved on the device, stride 1 on the host and for the channel row)
+// A view type V offers operator[](i), ld8(i, a) = eight consecutive elements (issued, not yet usable), wait() = the ld8
+// results are usable, and kBatch = element pairs an f / g loop keeps in flight (a multiple of 8).
 struct FView {
+    static constexpr int kBatch = 8;
     const float* p;
     size_t stride;
     PC_HD float operator[](int i) const { return p[(size_t)i * stride]; }
+    PC_HD void ld8(int i, float* a) const
+    {
+#ifdef __CUDA_ARCH__
+#pragma unroll
+#endif
+        for (int k = 0; k < 8; ++k) a[k] = p[(size_t)(i + k) * stride];
+    }
+    PC_HD void wait() const {}
 };
 
 struct FCtx {
@@ -75,6 +86,13 @@ struct FCtx {
     size_t bs;
     PC_HD FView stage(int s) const { return FView{ llr + (size_t)llr_off[s] * ls, ls }; }
     PC_HD void st(int s, int i, float v) const { llr[((size_t)llr_off[s] + i) * ls] = v; }
+    PC_HD void st8(int s, int i, const float* v) const
+    {
+#ifdef __CUDA_ARCH__
+#pragma unroll
+#endif
+        for (int k = 0; k < 8; ++k) llr[((size_t)llr_off[s] + i + k) * ls] = v[k];
+    }
     PC_HD uint32_t bld(int w) const { return bits[(size_t)w * bs]; }
     PC_HD void bst(int w, uint32_t v) const { bits[(size_t)w * bs] = v; }
     PC_HD uint32_t bit(int i) const { return (bld(i >> 5) >> (i & 31)) & 1u; }
@@ -101,7 +119,8 @@ struct FCtx {
 // ---- 8-lane helpers ------------------------------------------------------------------------------------------
 // lane-wise accumulation of the n/8 vectors of a node, starting from +0 (RepetitionDecoder fastssc_avx_float.cpp:273-281;
 // lanes >= n of a short node are zeroed first, RepetitionPrepare avx_float.h:238-243)
-PC_HD void accumulate8(const FView& in, int n, float (&s)[8])
+template <class V>
+PC_HD void accumulate8(const V& in, int n, float (&s)[8])
 {
     for (int k = 0; k < 8; ++k) s[k] = 0.0f;
     for (int i = 0; i < n; i += 8)
@@ -148,56 +167,95 @@ PC_HD uint32_t spc4_bits(const float (&y)[4])
 // Eight elements per step with all loads before the stores: `in` and the destination stage may alias as far as the
 // compiler can tell, so a rolled loop serialises load -> op -> store (one memory latency per element on the device,
 // where the stages live in a DRAM/L2 arena).
-template <class Op>
-PC_HD void fop_map(const FCtx& c, const FView& in, int s, const Op& op)
+template <class C, class V, class Op>
+PC_HD void fop_map(const C& c, const V& in, int s, const Op& op)
 {
     const int h = 1 << (s - 1);
-    if (h >= 8) {
+    constexpr int U = V::kBatch;
+    if (U > 8 && h >= U) {
+        for (int i = 0; i < h; i += U) {
+            float a[U], b[U];
+#ifdef __CUDA_ARCH__
+#pragma unroll
+#endif
+            for (int k = 0; k < U; k += 8) in.ld8(i + k, a + k), in.ld8(i + k + h, b + k);
+            in.wait();
+#ifdef __CUDA_ARCH__
+#pragma unroll
+#endif
+            for (int k = 0; k < U; ++k) a[k] = op(a[k], b[k], i + k);
+#ifdef __CUDA_ARCH__
+#pragma unroll
+#endif
+            for (int k = 0; k < U; k += 8) c.st8(s - 1, i + k, a + k);
+        }
+    } else if (h >= 8) {
         for (int i = 0; i < h; i += 8) {
             float a[8], b[8];
+            in.ld8(i, a), in.ld8(i + h, b);
+            in.wait();
 #ifdef __CUDA_ARCH__
 #pragma unroll
 #endif
-            for (int k = 0; k < 8; ++k) a[k] = in[i + k], b[k] = in[i + k + h];
-#ifdef __CUDA_ARCH__
-#pragma unroll
-#endif
-            for (int k = 0; k < 8; ++k) c.st(s - 1, i + k, op(a[k], b[k], i + k));
+            for (int k = 0; k < 8; ++k) a[k] = op(a[k], b[k], i + k);
+            c.st8(s - 1, i, a);
         }
     } else {
         for (int i = 0; i < h; ++i) c.st(s - 1, i, op(in[i], in[i + h], i));
     }
 }
-PC_HD void fop_f(const FCtx& c, const FView& in, int s)
+template <class C, class V>
+PC_HD void fop_f(const C& c, const V& in, int s)
 {
     fop_map(c, in, s, [](float a, float b, int) { return f_f32(a, b); });
 }
-PC_HD void fop_g(const FCtx& c, const FView& in, int s, int off)
+template <class C, class V>
+PC_HD void fop_g(const C& c, const V& in, int s, int off)
 {
     const int h = 1 << (s - 1);
-    if (h >= 8) { // the 8 decisions of a step sit in one word (off is a multiple of h)
-        for (int i = 0; i < h; i += 8) {
-            float a[8], b[8];
+    constexpr int U = V::kBatch; // <= 32: the decisions of a batch sit in one word (off is a multiple of h)
+    if (U > 8 && h >= U) {
+        for (int i = 0; i < h; i += U) {
+            float a[U], b[U];
             const uint32_t bw = c.bld((off + i) >> 5) >> ((off + i) & 31);
 #ifdef __CUDA_ARCH__
 #pragma unroll
 #endif
-            for (int k = 0; k < 8; ++k) a[k] = in[i + k], b[k] = in[i + k + h];
+            for (int k = 0; k < U; k += 8) in.ld8(i + k, a + k), in.ld8(i + k + h, b + k);
+            in.wait();
 #ifdef __CUDA_ARCH__
 #pragma unroll
 #endif
-            for (int k = 0; k < 8; ++k) c.st(s - 1, i + k, g_f32(a[k], b[k], (bw >> k) & 1u));
+            for (int k = 0; k < U; ++k) a[k] = g_f32(a[k], b[k], (bw >> k) & 1u);
+#ifdef __CUDA_ARCH__
+#pragma unroll
+#endif
+            for (int k = 0; k < U; k += 8) c.st8(s - 1, i + k, a + k);
+        }
+    } else if (h >= 8) { // the 8 decisions of a step sit in one word
+        for (int i = 0; i < h; i += 8) {
+            float a[8], b[8];
+            const uint32_t bw = c.bld((off + i) >> 5) >> ((off + i) & 31);
+            in.ld8(i, a), in.ld8(i + h, b);
+            in.wait();
+#ifdef __CUDA_ARCH__
+#pragma unroll
+#endif
+            for (int k = 0; k < 8; ++k) a[k] = g_f32(a[k], b[k], (bw >> k) & 1u);
+            c.st8(s - 1, i, a);
         }
     } else {
         for (int i = 0; i < h; ++i) c.st(s - 1, i, g_f32(in[i], in[i + h], c.bit(off + i)));
     }
 }
-PC_HD void fop_g0(const FCtx& c, const FView& in, int s)
+template <class C, class V>
+PC_HD void fop_g0(const C& c, const V& in, int s)
 {
     fop_map(c, in, s, [](float a, float b, int) { return fadd(a, b); });
 }
 // right child rate-1: decisions = sign(g); parent = [left ^ right, right]   (ROneNode::rightDecode :204-219)
-PC_HD void fop_g1(const FCtx& c, const FView& in, int s, int off)
+template <class C, class V>
+PC_HD void fop_g1(const C& c, const V& in, int s, int off)
 {
     const int h = 1 << (s - 1);
     if (h >= 32) {
@@ -206,10 +264,8 @@ PC_HD void fop_g1(const FCtx& c, const FView& in, int s, int off)
             uint32_t r = 0;
             for (int k0 = 0; k0 < 32; k0 += 8) {
                 float a[8], b[8];
-#ifdef __CUDA_ARCH__
-#pragma unroll
-#endif
-                for (int k = 0; k < 8; ++k) a[k] = in[32 * w + k0 + k], b[k] = in[32 * w + k0 + k + h];
+                in.ld8(32 * w + k0, a), in.ld8(32 * w + k0 + h, b);
+                in.wait();
 #ifdef __CUDA_ARCH__
 #pragma unroll
 #endif
@@ -229,7 +285,8 @@ PC_HD void fop_g1(const FCtx& c, const FView& in, int s, int off)
     }
 }
 // Combine / CombineBitsShort / Combine_0R (avx_float.h:193-236)
-PC_HD void fop_comb(const FCtx& c, int s, int off, bool zero_left)
+template <class C>
+PC_HD void fop_comb(const C& c, int s, int off, bool zero_left)
 {
     const int h = 1 << (s - 1);
     if (h >= 32) {
@@ -250,24 +307,28 @@ PC_HD void fop_comb(const FCtx& c, int s, int off, bool zero_left)
 }
 
 // ---- leaves ----------------------------------------------------------------------------------------------------
-PC_HD void fleaf_const(const FCtx& c, int s, int off, uint32_t b)
+template <class C>
+PC_HD void fleaf_const(const C& c, int s, int off, uint32_t b)
 {
     c.put_bits(off, 1 << s, [b](int) { return b; });
 }
 // RateOneDecoder :259-265: decisions = sign bits (-0.0 decodes to 1)
-PC_HD void fleaf_r1(const FCtx& c, const FView& in, int s, int off)
+template <class C, class V>
+PC_HD void fleaf_r1(const C& c, const V& in, int s, int off)
 {
     c.put_bits(off, 1 << s, [&in](int i) { return fsign(in[i]); });
 }
 // RepetitionDecoder :273-287
-PC_HD void fleaf_rep(const FCtx& c, const FView& in, int s, int off)
+template <class C, class V>
+PC_HD void fleaf_rep(const C& c, const V& in, int s, int off)
 {
     float acc[8];
     accumulate8(in, 1 << s, acc);
     fleaf_const(c, s, off, fsign(reduce_add8(acc)));
 }
 // DoubleRepetitionDecoder :303-332
-PC_HD void fleaf_drep(const FCtx& c, const FView& in, int s, int off)
+template <class C, class V>
+PC_HD void fleaf_drep(const C& c, const V& in, int s, int off)
 {
     const int n = 1 << s;
     float a[8];
@@ -285,7 +346,8 @@ PC_HD void fleaf_drep(const FCtx& c, const FView& in, int s, int off)
 }
 // SpcDecoder :342-373 (lanes >= n of a short node hold +inf, SpcPrepare avx_float.h:245-250): per vector the first
 // lane holding the vector minimum, across vectors strict '<'
-PC_HD void fleaf_spc(const FCtx& c, const FView& in, int s, int off)
+template <class C, class V>
+PC_HD void fleaf_spc(const C& c, const V& in, int s, int off)
 {
     const int n = 1 << s;
     uint32_t par = 0;
@@ -309,7 +371,8 @@ PC_HD void fleaf_spc(const FCtx& c, const FView& in, int s, int off)
 }
 // DoubleSpcDecoder :425-466 (n >= 16): per lane the LAST occurrence of the lane minimum (the "lt" compare of
 // avx_float.h:252-255 is a GT, so ties move the index), then the first even / odd lane holding the class minimum
-PC_HD void fleaf_dspc(const FCtx& c, const FView& in, int s, int off)
+template <class C, class V>
+PC_HD void fleaf_dspc(const C& c, const V& in, int s, int off)
 {
     const int n = 1 << s;
     float mv[8];
@@ -344,7 +407,8 @@ PC_HD void fleaf_dspc(const FCtx& c, const FView& in, int s, int off)
     });
 }
 // DoubleSpcDecoderShort8 :473-488 (n == 8): every lane equal to its class minimum flips when the class parity is odd
-PC_HD void fleaf_dspc8(const FCtx& c, const FView& in, int off)
+template <class C, class V>
+PC_HD void fleaf_dspc8(const C& c, const V& in, int off)
 {
     float a[8];
     uint32_t par[2] = { 0u, 0u };
@@ -366,7 +430,8 @@ PC_HD void fleaf_dspc8(const FCtx& c, const FView& in, int off)
 }
 // ZeroSpcDecoder :503-546 (n >= 16): the parity and the minimum come from left + right, but the stored value whose
 // sign becomes the decision is `right` (:519-520) -- reproduced as is
-PC_HD void fleaf_zspc(const FCtx& c, const FView& in, int s, int off)
+template <class C, class V>
+PC_HD void fleaf_zspc(const C& c, const V& in, int s, int off)
 {
     const int n = 1 << s, h = n >> 1;
     uint32_t par = 0;
@@ -394,7 +459,8 @@ PC_HD void fleaf_zspc(const FCtx& c, const FView& in, int s, int off)
     });
 }
 // ZeroSpcDecoderShort8 :556-565 and TripleRepetitionDecoder :572-589: SPC over y[j] = v[j] + v[j+4]
-PC_HD void fleaf_sum4_spc(const FCtx& c, const float (&v)[8], int s, int off)
+template <class C>
+PC_HD void fleaf_sum4_spc(const C& c, const float (&v)[8], int s, int off)
 {
     float y[4];
     for (int j = 0; j < 4; ++j) y[j] = fadd(v[j + 4], v[j]); // upper lanes of input + swaplane are what is stored
@@ -404,7 +470,8 @@ PC_HD void fleaf_sum4_spc(const FCtx& c, const float (&v)[8], int s, int off)
 // TypeFiveDecoder :762-792 (rep_then_spc == true) and RepetitionRateOneDecoderShort8 :718-739 (false): on the lane sums
 // v, a[j] = f(v[j], v[j+4]), rep = (a0 + a1) + (a2 + a3), y[j] = g(v[j], v[j+4], sign(rep)); pattern of 8 decisions
 // [rep ^ y, y] repeated over the node
-PC_HD void fleaf_rep_then(const FCtx& c, const float (&v)[8], int s, int off, bool spc)
+template <class C>
+PC_HD void fleaf_rep_then(const C& c, const float (&v)[8], int s, int off, bool spc)
 {
     float a[4], y[4];
     for (int j = 0; j < 4; ++j) a[j] = f_f32(v[j + 4], v[j]);
@@ -421,6 +488,41 @@ PC_HD void fleaf_rep_then(const FCtx& c, const float (&v)[8], int s, int off, bo
 }
 
 // ---- interpreter -------------------------------------------------------------------------------------------------
+// one node-program step on the input view `in` (C: where results go, V: where the node's LLRs are read)
+template <class C, class V>
+PC_HD void fastssc_f32_step(const C& c, const V& in, uint32_t op, int s, int off)
+{
+    switch (op) {
+    case FOP_F: fop_f(c, in, s); break;
+    case FOP_G: fop_g(c, in, s, off); break;
+    case FOP_G0: fop_g0(c, in, s); break;
+    case FOP_G1: fop_g1(c, in, s, off); break;
+    case FOP_COMB: fop_comb(c, s, off, false); break;
+    case FOP_COMB0: fop_comb(c, s, off, true); break;
+    case FOP_R0: fleaf_const(c, s, off, 0u); break;
+    case FOP_R1: fleaf_r1(c, in, s, off); break;
+    case FOP_REP: fleaf_rep(c, in, s, off); break;
+    case FOP_SPC: fleaf_spc(c, in, s, off); break;
+    case FOP_DREP: fleaf_drep(c, in, s, off); break;
+    case FOP_DSPC: fleaf_dspc(c, in, s, off); break;
+    case FOP_DSPC8: fleaf_dspc8(c, in, off); break;
+    case FOP_ZSPC: fleaf_zspc(c, in, s, off); break;
+    default: {
+        float v[8];
+        if (op == FOP_ZSPC8 || op == FOP_REPONE8) {
+            for (int k = 0; k < 8; ++k) v[k] = in[k];
+        } else {
+            accumulate8(in, 1 << s, v);
+        }
+        if (op == FOP_ZSPC8 || op == FOP_TREP)
+            fleaf_sum4_spc(c, v, s, off);
+        else
+            fleaf_rep_then(c, v, s, off, op == FOP_T5);
+        break;
+    }
+    }
+}
+
 PC_HD void fastssc_f32_run(const FCtx& c, const uint32_t* code, const float* row, bool staged_root)
 {
     const int S = c.S;
@@ -432,35 +534,7 @@ PC_HD void fastssc_f32_run(const FCtx& c, const uint32_t* code, const float* row
         const int s = (int)instr_s(ins), off = (int)instr_off(ins);
         if (op == FOP_END) break;
         const FView in = (s == S && !staged_root) ? FView{ row, 1 } : c.stage(s);
-        switch (op) {
-        case FOP_F: fop_f(c, in, s); break;
-        case FOP_G: fop_g(c, in, s, off); break;
-        case FOP_G0: fop_g0(c, in, s); break;
-        case FOP_G1: fop_g1(c, in, s, off); break;
-        case FOP_COMB: fop_comb(c, s, off, false); break;
-        case FOP_COMB0: fop_comb(c, s, off, true); break;
-        case FOP_R0: fleaf_const(c, s, off, 0u); break;
-        case FOP_R1: fleaf_r1(c, in, s, off); break;
-        case FOP_REP: fleaf_rep(c, in, s, off); break;
-        case FOP_SPC: fleaf_spc(c, in, s, off); break;
-        case FOP_DREP: fleaf_drep(c, in, s, off); break;
-        case FOP_DSPC: fleaf_dspc(c, in, s, off); break;
-        case FOP_DSPC8: fleaf_dspc8(c, in, off); break;
-        case FOP_ZSPC: fleaf_zspc(c, in, s, off); break;
-        default: {
-            float v[8];
-            if (op == FOP_ZSPC8 || op == FOP_REPONE8) {
-                for (int k = 0; k < 8; ++k) v[k] = in[k];
-            } else {
-                accumulate8(in, 1 << s, v);
-            }
-            if (op == FOP_ZSPC8 || op == FOP_TREP)
-                fleaf_sum4_spc(c, v, s, off);
-            else
-                fleaf_rep_then(c, v, s, off, op == FOP_T5);
-            break;
-        }
-        }
+        fastssc_f32_step(c, in, op, s, off);
     }
 }
 

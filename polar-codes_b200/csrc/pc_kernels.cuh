@@ -128,6 +128,8 @@ struct F32Params {
     float* arena;  // [elems][arena_stride]
     uint32_t* bits_arena; // [nbw][grid*threads]
     int g8_cw_words; // group-of-8 kernel: shared-memory words per codeword (elems + nbw, padded to 8 mod 32)
+    int sm_top;      // on-chip kernel: highest LLR stage kept in shared memory
+    int sm_tm_cols;  // on-chip kernel: tensor-memory columns of a CTA holding stage S-1 (0: every stage in shared memory)
 };
 
 struct F32Launch {
@@ -135,8 +137,12 @@ struct F32Launch {
     int threads, grid;
     int g8, g8_threads, g8_grid; // group-of-8 kernel (tree in shared memory) chosen for this code
     size_t g8_smem;
+    int sm, sm_threads, sm_grid; // on-chip kernel (k_fastssc_f32_sm): threads per CTA (96 / 128), CTAs
+    size_t sm_smem;
 };
 cudaError_t launch_fastssc_f32(const F32Launch& L, const float* d_llr, uint8_t* d_info, uint8_t* d_ok, size_t B, cudaStream_t st);
+// resident CTAs per SM of the on-chip kernel for this plan (registers, shared memory), <= 0 on error
+int fastssc_f32_sm_occupancy(const F32Launch& L);
 cudaError_t launch_i8_to_f32(const int8_t* d_in, float* d_out, size_t n, cudaStream_t st);
 
 cudaError_t const_pool_upload(int offset_words, const uint32_t* h_src, int nwords, cudaStream_t st);

@@ -259,6 +259,75 @@ __device__ __forceinline__ void scl_sort_packed2(const LN& c, const int (&v)[C],
     }
 }
 
+// The emulation for FLOAT metrics: a 64-bit key, high word = the metric mapped to an unsigned integer of the same order
+// (-0.0 is folded into +0.0 first, as the float compare treats them as equal), low word = ((0xFFFF - position) << 16) |
+// candidate index. One unsigned 64-bit maximum per pass replaces the (value, position) compare network and the separate
+// index array of scl_sort (which was 37 % of the executed instructions of k_scl_f32, profiles/r02_scl_f32_full_v3_T384.txt).
+__device__ __forceinline__ uint32_t f32_order_key(float x)
+{
+    const uint32_t u = __float_as_uint(__fadd_rn(x, 0.0f));
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float f32_from_order_key(uint32_t k) { return __uint_as_float((k & 0x80000000u) ? (k ^ 0x80000000u) : ~k); }
+__device__ __forceinline__ unsigned long long group_max64(unsigned long long m, int G)
+{
+    switch (G) {
+    case 32: m = max(m, __shfl_xor_sync(0xFFFFFFFFu, m, 16)); // fall through
+    case 16: m = max(m, __shfl_xor_sync(0xFFFFFFFFu, m, 8));  // fall through
+    case 8: m = max(m, __shfl_xor_sync(0xFFFFFFFFu, m, 4));   // fall through
+    case 4: m = max(m, __shfl_xor_sync(0xFFFFFFFFu, m, 2));   // fall through
+    case 2: m = max(m, __shfl_xor_sync(0xFFFFFFFFu, m, 1));   // fall through
+    default: break;
+    }
+    return m;
+}
+template <int C, class LN>
+__device__ __forceinline__ void scl_sort_key64(const LN& c, const float (&v)[C], int newP, float& out_val, int& out_idx)
+{
+    static_assert((C & (C - 1)) == 0, "C must be a power of two");
+    constexpr int LOGC = C == 2 ? 1 : (C == 4 ? 2 : 3);
+    typedef unsigned long long u64;
+    const int size = C * c.P, G = c.G;
+    u64 kv[C];
+#pragma unroll
+    for (int k = 0; k < C; ++k) {
+        const int pos = c.l * C + k;
+        kv[k] = pos < size ? (((u64)f32_order_key(v[k]) << 32) | ((u64)(0xFFFFu - (unsigned)pos) << 16) | (u64)pos) : 0ull;
+    }
+    const int lim = size - 1 < newP ? size - 1 : newP;
+    out_val = 0.0f;
+    out_idx = 0;
+    for (int li = 0; li * C < lim; ++li) {
+#pragma unroll
+        for (int ki = 0; ki < C; ++ki) {
+            const int i = li * C + ki;
+            if (i < lim) { // uniform
+                u64 m = kv[0];
+#pragma unroll
+                for (int k = 1; k < C; ++k) m = max(m, kv[k]);
+                m = group_max64(m, G);
+                const uint32_t lo = (uint32_t)m;
+                const int bp = (int)(0xFFFFu - (lo >> 16)), lm = bp >> LOGC, km = bp & (C - 1);
+                const u64 vi = __shfl_sync(0xFFFFFFFFu, kv[ki], li, G);
+                if (c.l == lm) put(kv, km, (vi & ~(0xFFFFull << 16)) | ((u64)(0xFFFFu - (unsigned)bp) << 16));
+                if (c.l == li) kv[ki] = 0ull; // consumed (also when the maximum already sat in slot i)
+                if (c.l == i) {
+                    out_val = f32_from_order_key((uint32_t)(m >> 32));
+                    out_idx = (int)(lo & 0xFFFFu);
+                }
+            }
+        }
+    }
+    if (lim < newP) { // size == newP: the last slot was never the target of a pass and keeps its content
+        const int lj = lim >> LOGC, kj = lim & (C - 1);
+        const u64 vj = __shfl_sync(0xFFFFFFFFu, sel(kv, kj), lj, G);
+        if (c.l == lim) {
+            out_val = f32_from_order_key((uint32_t)(vj >> 32));
+            out_idx = (int)((uint32_t)vj & 0xFFFFu);
+        }
+    }
+}
+
 // Indices[] bookkeeping of findWeakLlrs (arrayfuncs.h:209-231): the first four entries plus a patch list for
 // positions >= 4 (at most four swaps happen). swap(i, bp) is called once per pass with i < 4.
 struct WeakIdx {

@@ -467,7 +467,7 @@ __device__ __forceinline__ void sclf_rep(FLane& c, const SclFParams& p, int s, i
     const int newP = 2 * c.P < p.L ? 2 * c.P : p.L;
     float val;
     int idx;
-    scl_sort<2>(c, v, newP, val, idx);
+    scl_sort_key64<2>(c, v, newP, val, idx);
     const bool live = c.l < newP;
     const int sp = live ? idx >> 1 : 0;
     scl_fork(c, sp, val, newP);
@@ -497,7 +497,7 @@ __device__ __forceinline__ void sclf_r1(FLane& c, const SclFParams& p, int s, in
     const int newP = 4 * c.P < p.L ? 4 * c.P : p.L;
     float val;
     int idx;
-    scl_sort<4>(c, v, newP, val, idx);
+    scl_sort_key64<4>(c, v, newP, val, idx);
     const bool live = c.l < newP;
     const int sp = live ? idx >> 2 : 0;
     int fi[4];
@@ -539,7 +539,7 @@ __device__ __forceinline__ void sclf_spc(FLane& c, const SclFParams& p, int s, i
     const int newP = 8 * c.P < p.L ? 8 * c.P : p.L;
     float val;
     int idx;
-    scl_sort<8>(c, v, newP, val, idx);
+    scl_sort_key64<8>(c, v, newP, val, idx);
     const bool live = c.l < newP;
     const int sp = live ? idx >> 3 : 0;
     int fi[4];
