@@ -7,7 +7,7 @@ top = int(sys.argv[2]) if len(sys.argv) > 2 else 40
 raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--print-source", "cuda,sass", "--csv"], capture_output=True, text=True).stdout
 fname, rows, total = "?", [], 0
 for r in csv.reader(io.StringIO(raw)):
-    if len(r) >= 2 and r[0] == "File Name":
+    if len(r) >= 2 and r[0] in ("File Name", "File Path"):
         fname = r[1].split("/")[-1]
         continue
     if len(r) < 8 or r[0] in ("", "Line No"):
