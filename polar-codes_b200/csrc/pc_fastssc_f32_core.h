@@ -56,7 +56,13 @@ PC_HD float fabs_(float x) { return u2f(f2u(x) & 0x7FFFFFFFu); }
 // _mm256_min_ps lane: returns the second operand unless a < b (so NaN -> b)
 PC_HD float fmin_ps(float a, float b) { return a < b ? a : b; }
 // _mm256_polarf_ps / _mm256_polarg_ps (avx_float.h:55-81)
+// (on the device the minimum of the two magnitudes is one FMNMX with |.| operand modifiers; fminf and fmin_ps differ
+// only for NaN, which a magnitude of a finite or infinite LLR is not)
+#ifdef __CUDA_ARCH__
+PC_HD float f_f32(float a, float b) { return u2f(((f2u(a) ^ f2u(b)) & 0x80000000u) | f2u(fminf(fabsf(a), fabsf(b)))); }
+#else
 PC_HD float f_f32(float a, float b) { return u2f(((f2u(a) ^ f2u(b)) & 0x80000000u) | f2u(fmin_ps(fabs_(a), fabs_(b)))); }
+#endif
 PC_HD float g_f32(float a, float b, uint32_t bit) { return fadd(u2f(f2u(a) ^ (bit << 31)), b); }
 
 // strided view of a float array (thread-interleaved on the device, stride 1 on the host and for the channel row)

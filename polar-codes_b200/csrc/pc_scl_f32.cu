@@ -554,7 +554,12 @@ __device__ __forceinline__ void sclf_spc(FLane& c, const SclFParams& p, int s, i
 }
 
 template <int BM, int TT>
-__global__ void __launch_bounds__(TT ? TT : 384, 1) k_scl_f32(const __grid_constant__ SclFParams p)
+// Launch bounds: the tensor-memory plans run ONE CTA of TT (or, for an odd PC_SCLF_T, up to 384) lanes per SM and may use
+// the registers that leaves; the shared-memory plans (short codes: CTAs of <= 128 lanes, up to eight per SM) are held to
+// the 96-100 registers of five resident CTAs -- without the second bound they compiled to 138 registers, three CTAs per
+// SM, and N = 64 L = 4 fell from 10.9 to 7.9 Gbit/s (profiles/r02_c15_bisect.txt).
+__global__ void __launch_bounds__(TT ? TT : ((BM & BM_TMEM) ? 384 : 128), (TT || (BM & BM_TMEM)) ? 1 : 5)
+    k_scl_f32(const __grid_constant__ SclFParams p)
 {
     using FLane = FLaneT<BM, TT>;
     extern __shared__ __align__(16) uint32_t smem[];
