@@ -10,7 +10,7 @@
  *   pc_code_set_crc         Decoder/Encoder::setErrorDetection              decoder.cpp:133-136, src/polarcode/encoding/encoder.cpp
  *   pc_code_set_systematic  Decoder/Encoder::setSystematic                  decoder.h:118, encoder.h
  *   pc_decode_batch         Decoder::decode_vector(const char* | const float*, void*)   decoder.cpp:154-181   (B codewords per call)
- *   pc_decode_soft_batch    Decoder::getSoftCodeword / getSoftInformation   decoder.cpp:147-152 (int8 Fast-SSC)
+ *   pc_decode_soft_batch    Decoder::getSoftCodeword / getSoftInformation   decoder.cpp:147-152 (int8 Fast-SSC; _f32: fp32 Fast-SSC)
  *   pc_encode_batch         Encoder::encode_vector(void*, void*)            src/polarcode/encoding/encoder.cpp:79-90
  *   pc_crc_generate_batch   ErrorDetection::Detector::generate              include/polarcode/errordetection/errordetector.h:57-63
  *   pc_crc_check_batch      Detector::check                                 errordetector.h:65-70
@@ -130,6 +130,15 @@ int pc_decode_soft_batch(pc_code* c, const void* d_llr, int llr_is_float, int8_t
                          void* stream);
 int pc_decode_soft_batch_host(pc_code* c, const void* h_llr, int llr_is_float, int8_t* h_soft_code, int8_t* h_soft_info,
                               size_t B);
+/* The same getters for the fp32 Fast-SSC decoder ('float', L = 1): FloatContainer::getSoftBits / getSoftInformation
+ * (src/polarcode/bitcontainer.cpp:294-297, 331-339) -- the bit container as 32-bit FLOAT PATTERNS, bit for bit what the
+ * reference holds: leaves write LLR-valued floats (+inf for frozen blocks), combine steps XOR the patterns
+ * (include/polarcode/decoding/avx_float.h:190-236), so only the sign bit of an inner word is meaningful and a word may be a
+ * NaN pattern -- compare as uint32. d_soft_code[B][N] and / or d_soft_info[B][K] float32; either may be NULL. */
+int pc_decode_soft_batch_f32(pc_code* c, const void* d_llr, int llr_is_float, float* d_soft_code, float* d_soft_info, size_t B,
+                             void* stream);
+int pc_decode_soft_batch_f32_host(pc_code* c, const void* h_llr, int llr_is_float, float* h_soft_code, float* h_soft_info,
+                                  size_t B);
 
 /* Encode B info blocks of ceil(K/8) bytes. The detector's check bytes are generated into the tail of a
  * device-side copy of each block (the reference writes them into the caller's buffer,

@@ -15,7 +15,8 @@
 // a usable GPU throws std::runtime_error.
 //
 // Soft outputs: getSoftCodeword / getSoftInformation are served for the 'char' Fast-SSC decoder by a second kernel that
-// keeps the bit container as bytes (pc_fastssc_i8_soft.cu); the float and list decoders' containers are not kept.
+// keeps the bit container as bytes (pc_fastssc_i8_soft.cu), the fp32 Fast-SSC one as float patterns (k_fastssc_f32_soft);
+// the list decoders' containers are not kept.
 // Not carried over: the BitContainer accessors (inputContainer / outputContainer), Encoder::setCodeword / setCharCodeword /
 // setFloatCodeword / clearFrozenBits (hooks the reference's own decoders use for non-systematic output; the kernels do
 // that step on the device), the 'scan' kind and CMAC detectors.
@@ -403,12 +404,19 @@ protected:
     std::vector<char> mCharLlr;
     bool mSignalIsFloat = false;
 
-    void soft(int8_t* code, int8_t* info)
+    // pData: N (code) / K (info) int8 values for the 'char' Fast-SSC decoder, float values for the 'float' one
+    void soft(void* code, void* info)
     {
-        if (mKind != PC_DEC_FASTSSC_I8) throw std::logic_error("soft outputs are available for the 'char' Fast-SSC decoder only");
+        if (mKind != PC_DEC_FASTSSC_I8 && mKind != PC_DEC_FASTSSC_F32)
+            throw std::logic_error("soft outputs are available for the 'char' and 'float' Fast-SSC decoders only");
         const void* llr = mSignalIsFloat ? static_cast<const void*>(mFloatLlr.data()) : static_cast<const void*>(mCharLlr.data());
         if ((mSignalIsFloat ? mFloatLlr.size() : mCharLlr.size()) != mBlockLength) throw std::logic_error("no signal set");
-        detail::check(pc_decode_soft_batch_host(mCode, llr, mSignalIsFloat ? 1 : 0, code, info, 1));
+        if (mKind == PC_DEC_FASTSSC_I8)
+            detail::check(pc_decode_soft_batch_host(mCode, llr, mSignalIsFloat ? 1 : 0, static_cast<int8_t*>(code),
+                                                    static_cast<int8_t*>(info), 1));
+        else
+            detail::check(pc_decode_soft_batch_f32_host(mCode, llr, mSignalIsFloat ? 1 : 0, static_cast<float*>(code),
+                                                        static_cast<float*>(info), 1));
     }
 
 public:
@@ -470,16 +478,21 @@ public:
     {
         detail::check(pc_decode_batch(mCode, d_llr, llrIsFloat ? 1 : 0, d_info, d_ok, B, stream));
     }
-    /// decoder.cpp:147-152: the bit container after the last decode() as bytes (N int8 values for the 'char' Fast-SSC
-    /// decoder; other kinds throw std::logic_error -- their containers hold floats / list paths the kernels do not keep).
-    /// The container is recomputed on the device from the signal of the last setSignal()/decode_vector().
-    void getSoftCodeword(void* pData) { soft(static_cast<int8_t*>(pData), nullptr); }
-    /// the container bytes at the information positions (K int8 values)
-    void getSoftInformation(void* pData) { soft(nullptr, static_cast<int8_t*>(pData)); }
-    /// batch forms, DEVICE buffers: d_soft_code[B][N], d_soft_info[B][K] (either may be null)
+    /// decoder.cpp:147-152: the bit container after the last decode(): N int8 values for the 'char' Fast-SSC decoder
+    /// (CharContainer::getSoftBits), N floats for the 'float' one (FloatContainer::getSoftBits -- inner words are XORs of
+    /// float patterns, only their sign is meaningful). The list decoders throw std::logic_error: their containers belong
+    /// to paths the kernels do not keep. Recomputed on the device from the signal of the last setSignal()/decode_vector().
+    void getSoftCodeword(void* pData) { soft(pData, nullptr); }
+    /// the container values at the information positions (K values)
+    void getSoftInformation(void* pData) { soft(nullptr, pData); }
+    /// batch forms, DEVICE buffers: d_soft_code[B][N], d_soft_info[B][K] (either may be null); int8 for 'char', float for 'float'
     void soft_batch_device(const void* d_llr, bool llrIsFloat, int8_t* d_soft_code, int8_t* d_soft_info, size_t B, void* stream = nullptr)
     {
         detail::check(pc_decode_soft_batch(mCode, d_llr, llrIsFloat ? 1 : 0, d_soft_code, d_soft_info, B, stream));
+    }
+    void soft_batch_device(const void* d_llr, bool llrIsFloat, float* d_soft_code, float* d_soft_info, size_t B, void* stream = nullptr)
+    {
+        detail::check(pc_decode_soft_batch_f32(mCode, d_llr, llrIsFloat ? 1 : 0, d_soft_code, d_soft_info, B, stream));
     }
     size_t duration_ns() { return mDecoderDuration; }
     std::vector<unsigned> frozenBits() { return mFrozenBits; }

@@ -150,6 +150,33 @@ int ref_decode_soft(int N, const unsigned* frozen, int nf, int systematic, const
     }
 }
 
+// The same getters of the 'float' Fast-SSC decoder (FloatContainer::getSoftBits / getSoftInformation,
+// bitcontainer.cpp:294-297, 331-339): soft_code float[B][N], soft_info float[B][K] (either may be null). Returns 0 or -1.
+int ref_decode_soft_f32(int N, const unsigned* frozen, int nf, int systematic, const float* llr, long B, float* soft_code,
+                        float* soft_info)
+{
+    try {
+        auto fz = mkfrozen(frozen, nf);
+        const int K = N - nf;
+        Decoding::Decoder* dec = Decoding::create(N, 1, fz, std::string("float"));
+        dec->setSystematic(systematic != 0);
+        std::vector<unsigned char> tmp((K + 7) / 8 + 64);
+        std::vector<float> sc(N < 8 ? 8 : N);
+        for (long i = 0; i < B; ++i) {
+            dec->decode_vector(llr + i * N, tmp.data());
+            if (soft_code) {
+                dec->getSoftCodeword(sc.data());
+                memcpy(soft_code + i * N, sc.data(), sizeof(float) * N);
+            }
+            if (soft_info) dec->getSoftInformation(soft_info + i * K);
+        }
+        delete dec;
+        return 0;
+    } catch (...) {
+        return -1;
+    }
+}
+
 // info: uint8[B][ceil(K/8)] (a private copy is made per frame because encode() writes the CRC in place,
 // butterfly_fip_packed.cpp:47-49; the copy incl. CRC is returned through info_out when non-null).
 double ref_encode_batch(int N, const unsigned* frozen, int nf, int crc_bits, const char* crc_type,

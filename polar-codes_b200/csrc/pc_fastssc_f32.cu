@@ -151,7 +151,7 @@ __device__ __forceinline__ void fastssc_f32_run_g8(const FCtx& c, int g, const u
             case FOP_G1: fop_g1(c, in, s, off); break;
             case FOP_COMB: fop_comb(c, s, off, false); break;
             case FOP_COMB0: fop_comb(c, s, off, true); break;
-            case FOP_R0: fleaf_const(c, s, off, 0u); break;
+            case FOP_R0: fleaf_fill(c, s, off, 0x7F800000u); break;
             case FOP_R1: fleaf_r1(c, in, s, off); break;
             case FOP_REP: fleaf_rep(c, in, s, off); break;
             case FOP_SPC: fleaf_spc(c, in, s, off); break;
@@ -296,6 +296,7 @@ struct RowView { // the channel row in global memory, contiguous and 16-byte ali
 // DST_TM: the step's destination stage (s - 1) is stage S-1 in tensor memory, else a shared-memory stage
 template <int T, bool DST_TM>
 struct SmCtx {
+    static constexpr bool kSoft = false;
     uint32_t sm_llr;  // shared address of this thread's element 0 of stage 0 (stage s starts 2^s - 1 elements further)
     uint32_t sm_bits; // shared address of this thread's decision word 0
     uint32_t tm;      // tensor-memory address of column 0 of stage S-1 in this warp's lane quarter
@@ -339,6 +340,11 @@ struct SmCtx {
             const uint32_t m = lowmask(n) << sh;
             bst(off >> 5, (bld(off >> 5) & ~m) | (v << sh));
         }
+    }
+    template <class Gen>
+    __device__ __forceinline__ void put_vals(int off, int n, const Gen& gen) const
+    {
+        put_bits(off, n, [&gen](int i) { return gen(i) >> 31; });
     }
 };
 
@@ -414,6 +420,58 @@ __global__ void __launch_bounds__(T, 1) k_fastssc_f32_sm(const __grid_constant__
         if (t < 32)
             asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tm_base_s), "r"((uint32_t)p.sm_tm_cols));
     }
+}
+
+// ---- soft outputs: Decoder::getSoftCodeword / getSoftInformation of the float decoder (decoder.cpp:147-152) -----------
+// FloatContainer::getSoftBits (bitcontainer.cpp:294-297) hands out the decoder's bit container: N floats whose SIGN is the
+// decision. Leaves write LLR-valued floats (R0 +inf, R1 the LLRs, REP the sum, SPC the LLRs with the flipped one negated,
+// the 8-lane specials their own patterns), and every combine step XORs the 32-bit PATTERNS (avx_float.h:190-236), so the
+// words of an inner node are not meaningful numbers (they can be NaN patterns) -- they are reproduced bit for bit anyway.
+// The arena kernel's thread-per-codeword form with N more words per thread for that container; the packed decision
+// words are kept next to it (the g steps read them), so the hard decisions are those of the other kernels.
+__global__ void __launch_bounds__(128) k_fastssc_f32_soft(const __grid_constant__ F32Params p, float* __restrict__ soft_code,
+                                                          float* __restrict__ soft_info, const uint32_t* __restrict__ lut)
+{
+    const int T = blockDim.x, t = threadIdx.x;
+    const size_t GT = (size_t)gridDim.x * T, gt = (size_t)blockIdx.x * T + t, AS = p.arena_stride;
+    FSoftCtx c;
+    c.S = p.S;
+    c.llr_off = p.llr_off;
+    c.llr = p.arena + gt;
+    c.ls = AS;
+    c.bits = p.bits_arena + gt;
+    c.bs = AS;
+    const int N = 1 << p.S;
+    c.soft = p.bits_arena + (size_t)p.nbw * AS + gt;
+    c.ss = AS;
+    for (unsigned long long f = gt; f < p.B; f += GT) {
+        const float* row = p.llr + f * N;
+        if (p.staged_root)
+            for (int i = 0; i < N; ++i) c.st(p.S, i, row[i]);
+        for (int pc = 0;; ++pc) {
+            const uint32_t ins = p.code[pc];
+            const uint32_t op = instr_op(ins);
+            const int s = (int)instr_s(ins), off = (int)instr_off(ins);
+            if (op == FOP_END) break;
+            const FView in = (s == p.S && !p.staged_root) ? FView{ row, 1 } : c.stage(s);
+            fastssc_f32_step(c, in, op, s, off);
+        }
+        if (soft_code) {
+            uint32_t* out = reinterpret_cast<uint32_t*>(soft_code) + f * (unsigned long long)N;
+            for (int i = 0; i < N; ++i) out[i] = c.soft[(size_t)i * AS];
+        }
+        if (soft_info) { // FloatContainer::getSoftInformation bitcontainer.cpp:331-339
+            uint32_t* out = reinterpret_cast<uint32_t*>(soft_info) + f * (unsigned long long)p.K;
+            for (int k = 0; k < p.K; ++k) out[k] = c.soft[(size_t)__ldg(lut + k) * AS];
+        }
+    }
+}
+
+cudaError_t launch_fastssc_f32_soft(const F32Params& p, int grid, int threads, float* d_soft_code, float* d_soft_info, const uint32_t* d_lut,
+                                    cudaStream_t st)
+{
+    k_fastssc_f32_soft<<<grid, threads, 0, st>>>(p, d_soft_code, d_soft_info, d_lut);
+    return cudaGetLastError();
 }
 
 // FloatContainer::insertLlr(const char*) (reference src/polarcode/bitcontainer.cpp:202-207): int8 -> float

@@ -84,6 +84,7 @@ struct FView {
 };
 
 struct FCtx {
+    static constexpr bool kSoft = false; // true: the context also keeps the reference's float bit container (FSoftCtx)
     int S;
     const int* llr_off; // element offset of stage s inside the thread's LLR space (s < S, or s <= S when staged)
     float* llr;         // element 0 of the thread's LLR space
@@ -120,6 +121,55 @@ struct FCtx {
             bst(off >> 5, (bld(off >> 5) & ~m) | (v << sh));
         }
     }
+    // a leaf's result as the FLOAT PATTERNS the reference stores in its bit container (the decision is the sign bit);
+    // the hard-decision contexts keep the sign only
+    template <class Gen>
+    PC_HD void put_vals(int off, int n, const Gen& gen) const
+    {
+        put_bits(off, n, [&gen](int i) { return gen(i) >> 31; });
+    }
+};
+
+// ---- soft-output context: the reference's float bit container next to the packed decisions (k_fastssc_f32_soft) ---
+struct FSoftCtx : FCtx {
+    static constexpr bool kSoft = true;
+    uint32_t* soft; // element i of the thread's float bit container at soft[i * ss]
+    size_t ss;
+    template <class Gen>
+    PC_HD void put_vals(int off, int n, const Gen& gen) const
+    {
+        for (int i0 = 0; i0 < n; i0 += 32) {
+            const int m = n - i0 < 32 ? n - i0 : 32;
+            uint32_t v = 0;
+            for (int k = 0; k < m; ++k) {
+                const uint32_t x = gen(i0 + k);
+                soft[(size_t)(off + i0 + k) * ss] = x;
+                v |= (x >> 31) << k;
+            }
+            if (m == 32) {
+                bst((off + i0) >> 5, v);
+            } else {
+                const int sh = off & 31;
+                const uint32_t msk = lowmask(m) << sh;
+                bst(off >> 5, (bld(off >> 5) & ~msk) | (v << sh));
+            }
+        }
+    }
+    // ROneNode::rightDecode :204-219: right = the g value, left ^= right (patterns)
+    PC_HD void soft_g1(int off, int h, int i, uint32_t gv) const
+    {
+        soft[(size_t)(off + h + i) * ss] = gv;
+        soft[(size_t)(off + i) * ss] ^= gv;
+    }
+    // Combine / CombineBitsShort / Combine_0R
+    PC_HD void soft_comb(int off, int h, bool zero_left) const
+    {
+        for (int i = 0; i < h; ++i) {
+            const uint32_t r = soft[(size_t)(off + h + i) * ss];
+            uint32_t* l = soft + (size_t)(off + i) * ss;
+            *l = zero_left ? r : (*l ^ r);
+        }
+    }
 };
 
 // ---- 8-lane helpers ------------------------------------------------------------------------------------------
@@ -151,20 +201,16 @@ PC_HD int minidx8(const float (&a)[8], float& mn)
     return idx;
 }
 // _mm256_spc_right4_ps (avx_float.h:294-308) on 4 values: parity over the 4 signs; EVERY lane whose magnitude equals
-// the minimum is flipped (ties flip several). Returns the 4 decisions.
-PC_HD uint32_t spc4_bits(const float (&y)[4])
+// the minimum is flipped (ties flip several). Returns the 4 stored values.
+PC_HD void spc4_vals(const float (&y)[4], uint32_t (&out)[4])
 {
     float m = fabs_(y[0]);
-    uint32_t par = 0, bits = 0;
+    uint32_t par = 0;
     for (int k = 0; k < 4; ++k) {
         m = fmin_ps(fabs_(y[k]), m);
         par ^= fsign(y[k]);
-        bits |= fsign(y[k]) << k;
     }
-    if (par)
-        for (int k = 0; k < 4; ++k)
-            if (fabs_(y[k]) == m) bits ^= 1u << k;
-    return bits;
+    for (int k = 0; k < 4; ++k) out[k] = f2u(y[k]) ^ ((par && fabs_(y[k]) == m) ? 0x80000000u : 0u);
 }
 
 // ---- internal nodes --------------------------------------------------------------------------------------------
@@ -275,7 +321,11 @@ PC_HD void fop_g1(const C& c, const V& in, int s, int off)
 #ifdef __CUDA_ARCH__
 #pragma unroll
 #endif
-                for (int k = 0; k < 8; ++k) r |= fsign(g_f32(a[k], b[k], (left >> (k0 + k)) & 1u)) << (k0 + k);
+                for (int k = 0; k < 8; ++k) {
+                    const float gv = g_f32(a[k], b[k], (left >> (k0 + k)) & 1u);
+                    r |= fsign(gv) << (k0 + k);
+                    if constexpr (C::kSoft) c.soft_g1(off, h, 32 * w + k0 + k, f2u(gv));
+                }
             }
             c.bst((off >> 5) + w, left ^ r);
             c.bst(((off + h) >> 5) + w, r);
@@ -284,7 +334,11 @@ PC_HD void fop_g1(const C& c, const V& in, int s, int off)
         const int sh = off & 31;
         uint32_t word = c.bld(off >> 5);
         uint32_t r = 0;
-        for (int k = 0; k < h; ++k) r |= fsign(g_f32(in[k], in[k + h], (word >> (sh + k)) & 1u)) << k;
+        for (int k = 0; k < h; ++k) {
+            const float gv = g_f32(in[k], in[k + h], (word >> (sh + k)) & 1u);
+            r |= fsign(gv) << k;
+            if constexpr (C::kSoft) c.soft_g1(off, h, k, f2u(gv));
+        }
         word ^= r << sh;
         word = (word & ~(lowmask(h) << (sh + h))) | (r << (sh + h));
         c.bst(off >> 5, word);
@@ -295,6 +349,7 @@ template <class C>
 PC_HD void fop_comb(const C& c, int s, int off, bool zero_left)
 {
     const int h = 1 << (s - 1);
+    if constexpr (C::kSoft) c.soft_comb(off, h, zero_left);
     if (h >= 32) {
         for (int w = 0; w < (h >> 5); ++w) {
             const uint32_t r = c.bld(((off + h) >> 5) + w);
@@ -313,16 +368,19 @@ PC_HD void fop_comb(const C& c, int s, int off, bool zero_left)
 }
 
 // ---- leaves ----------------------------------------------------------------------------------------------------
+// Every leaf hands its result to the context as the float patterns the reference writes into its bit container (the
+// decision is the sign bit): the hard-decision contexts keep the signs, the soft-output context the whole words.
+// RateZeroDecoder :247 fills +inf; RepetitionDecoder :273-287 the sum
 template <class C>
-PC_HD void fleaf_const(const C& c, int s, int off, uint32_t b)
+PC_HD void fleaf_fill(const C& c, int s, int off, uint32_t pattern)
 {
-    c.put_bits(off, 1 << s, [b](int) { return b; });
+    c.put_vals(off, 1 << s, [pattern](int) { return pattern; });
 }
-// RateOneDecoder :259-265: decisions = sign bits (-0.0 decodes to 1)
+// RateOneDecoder :259-265: the LLRs themselves (-0.0 decodes to 1)
 template <class C, class V>
 PC_HD void fleaf_r1(const C& c, const V& in, int s, int off)
 {
-    c.put_bits(off, 1 << s, [&in](int i) { return fsign(in[i]); });
+    c.put_vals(off, 1 << s, [&in](int i) { return f2u(in[i]); });
 }
 // RepetitionDecoder :273-287
 template <class C, class V>
@@ -330,9 +388,10 @@ PC_HD void fleaf_rep(const C& c, const V& in, int s, int off)
 {
     float acc[8];
     accumulate8(in, 1 << s, acc);
-    fleaf_const(c, s, off, fsign(reduce_add8(acc)));
+    fleaf_fill(c, s, off, f2u(reduce_add8(acc)));
 }
-// DoubleRepetitionDecoder :303-332
+// DoubleRepetitionDecoder :303-332 (n >= 8: every lane of the stored vector is its class sum -- the lanes add the same
+// four numbers in orders that differ only by commutation)
 template <class C, class V>
 PC_HD void fleaf_drep(const C& c, const V& in, int s, int off)
 {
@@ -347,11 +406,11 @@ PC_HD void fleaf_drep(const C& c, const V& in, int s, int off)
         even = fadd(fadd(fadd(a[0], a[2]), a[4]), a[6]);
         odd = fadd(fadd(fadd(a[1], a[3]), a[5]), a[7]);
     }
-    const uint32_t be = fsign(even), bo = fsign(odd);
-    c.put_bits(off, n, [be, bo](int i) { return (i & 1) ? bo : be; });
+    const uint32_t ve = f2u(even), vo = f2u(odd);
+    c.put_vals(off, n, [ve, vo](int i) { return (i & 1) ? vo : ve; });
 }
 // SpcDecoder :342-373 (lanes >= n of a short node hold +inf, SpcPrepare avx_float.h:245-250): per vector the first
-// lane holding the vector minimum, across vectors strict '<'
+// lane holding the vector minimum, across vectors strict '<'; the stored value is the LLR, sign flipped at the minimum
 template <class C, class V>
 PC_HD void fleaf_spc(const C& c, const V& in, int s, int off)
 {
@@ -373,7 +432,7 @@ PC_HD void fleaf_spc(const C& c, const V& in, int s, int off)
             minAbs = t;
         }
     }
-    c.put_bits(off, n, [&in, par, minIdx](int i) { return fsign(in[i]) ^ ((i == minIdx) ? par : 0u); });
+    c.put_vals(off, n, [&in, par, minIdx](int i) { return f2u(in[i]) ^ ((i == minIdx) ? (par << 31) : 0u); });
 }
 // DoubleSpcDecoder :425-466 (n >= 16): per lane the LAST occurrence of the lane minimum (the "lt" compare of
 // avx_float.h:252-255 is a GT, so ties move the index), then the first even / odd lane holding the class minimum
@@ -407,9 +466,9 @@ PC_HD void fleaf_dspc(const C& c, const V& in, int s, int off)
         idx[q] = mi[lane];
     }
     const int ie = idx[0], io = idx[1];
-    const uint32_t pe = par[0], po = par[1];
-    c.put_bits(off, n, [&in, ie, io, pe, po](int i) {
-        return fsign(in[i]) ^ ((i == ie) ? pe : 0u) ^ ((i == io) ? po : 0u);
+    const uint32_t pe = par[0] << 31, po = par[1] << 31;
+    c.put_vals(off, n, [&in, ie, io, pe, po](int i) {
+        return f2u(in[i]) ^ ((i == ie) ? pe : 0u) ^ ((i == io) ? po : 0u);
     });
 }
 // DoubleSpcDecoderShort8 :473-488 (n == 8): every lane equal to its class minimum flips when the class parity is odd
@@ -428,10 +487,10 @@ PC_HD void fleaf_dspc8(const C& c, const V& in, int off)
         for (int k = q; k < 8; k += 2) m[q] = fmin_ps(a[k], m[q]);
     }
     const float m0 = m[0], m1 = m[1];
-    const uint32_t p0 = par[0], p1 = par[1];
-    c.put_bits(off, 8, [&in, m0, m1, p0, p1](int i) {
+    const uint32_t p0 = par[0] << 31, p1 = par[1] << 31;
+    c.put_vals(off, 8, [&in, m0, m1, p0, p1](int i) {
         const float mm = (i & 1) ? m1 : m0;
-        return fsign(in[i]) ^ ((fabs_(in[i]) == mm) ? ((i & 1) ? p1 : p0) : 0u);
+        return f2u(in[i]) ^ ((fabs_(in[i]) == mm) ? ((i & 1) ? p1 : p0) : 0u);
     });
 }
 // ZeroSpcDecoder :503-546 (n >= 16): the parity and the minimum come from left + right, but the stored value whose
@@ -459,23 +518,26 @@ PC_HD void fleaf_zspc(const C& c, const V& in, int s, int off)
             }
         }
     }
-    c.put_bits(off, n, [&in, h, par, minIdx](int i) {
+    c.put_vals(off, n, [&in, h, par, minIdx](int i) {
         const int j = i >= h ? i - h : i;
-        return fsign(in[j + h]) ^ ((j == minIdx) ? par : 0u);
+        return f2u(in[j + h]) ^ ((j == minIdx) ? (par << 31) : 0u);
     });
 }
-// ZeroSpcDecoderShort8 :556-565 and TripleRepetitionDecoder :572-589: SPC over y[j] = v[j] + v[j+4]
+// ZeroSpcDecoderShort8 :556-565 and TripleRepetitionDecoder :572-589: SPC over y[j] = v[j] + v[j+4]; the stored vector is
+// the SPC result of the upper four lanes in both halves
 template <class C>
 PC_HD void fleaf_sum4_spc(const C& c, const float (&v)[8], int s, int off)
 {
     float y[4];
     for (int j = 0; j < 4; ++j) y[j] = fadd(v[j + 4], v[j]); // upper lanes of input + swaplane are what is stored
-    const uint32_t b = spc4_bits(y);
-    c.put_bits(off, 1 << s, [b](int i) { return (b >> (i & 3)) & 1u; });
+    uint32_t o[4];
+    spc4_vals(y, o);
+    const uint32_t o0 = o[0], o1 = o[1], o2 = o[2], o3 = o[3];
+    c.put_vals(off, 1 << s, [o0, o1, o2, o3](int i) { return (i & 2) ? ((i & 1) ? o3 : o2) : ((i & 1) ? o1 : o0); });
 }
 // TypeFiveDecoder :762-792 (rep_then_spc == true) and RepetitionRateOneDecoderShort8 :718-739 (false): on the lane sums
-// v, a[j] = f(v[j], v[j+4]), rep = (a0 + a1) + (a2 + a3), y[j] = g(v[j], v[j+4], sign(rep)); pattern of 8 decisions
-// [rep ^ y, y] repeated over the node
+// v, a[j] = f(v[j], v[j+4]), rep = (a0 + a1) + (a2 + a3), y[j] = g(v[j], v[j+4], sign(rep)) (through the SPC for type
+// five); the stored vector of 8, repeated over the node, is [+-1.0 with sign(rep) ^ sign(y[j]), y[j]]
 template <class C>
 PC_HD void fleaf_rep_then(const C& c, const float (&v)[8], int s, int off, bool spc)
 {
@@ -484,13 +546,16 @@ PC_HD void fleaf_rep_then(const C& c, const float (&v)[8], int s, int off, bool 
     const float rep = fadd(fadd(a[0], a[1]), fadd(a[2], a[3]));
     const uint32_t rb = fsign(rep);
     for (int j = 0; j < 4; ++j) y[j] = g_f32(v[j], v[j + 4], rb);
-    uint32_t yb = 0;
+    uint32_t o[4];
     if (spc)
-        yb = spc4_bits(y);
+        spc4_vals(y, o);
     else
-        for (int j = 0; j < 4; ++j) yb |= fsign(y[j]) << j;
-    const uint32_t pat = ((rb ? 0xFu : 0u) ^ yb) | (yb << 4);
-    c.put_bits(off, 1 << s, [pat](int i) { return (pat >> (i & 7)) & 1u; });
+        for (int j = 0; j < 4; ++j) o[j] = f2u(y[j]);
+    const uint32_t rs = rb << 31, o0 = o[0], o1 = o[1], o2 = o[2], o3 = o[3];
+    c.put_vals(off, 1 << s, [rs, o0, o1, o2, o3](int i) {
+        const uint32_t yv = (i & 2) ? ((i & 1) ? o3 : o2) : ((i & 1) ? o1 : o0);
+        return (i & 4) ? yv : (0x3F800000u | ((yv ^ rs) & 0x80000000u));
+    });
 }
 
 // ---- interpreter -------------------------------------------------------------------------------------------------
@@ -505,7 +570,7 @@ PC_HD void fastssc_f32_step(const C& c, const V& in, uint32_t op, int s, int off
     case FOP_G1: fop_g1(c, in, s, off); break;
     case FOP_COMB: fop_comb(c, s, off, false); break;
     case FOP_COMB0: fop_comb(c, s, off, true); break;
-    case FOP_R0: fleaf_const(c, s, off, 0u); break;
+    case FOP_R0: fleaf_fill(c, s, off, 0x7F800000u); break;
     case FOP_R1: fleaf_r1(c, in, s, off); break;
     case FOP_REP: fleaf_rep(c, in, s, off); break;
     case FOP_SPC: fleaf_spc(c, in, s, off); break;

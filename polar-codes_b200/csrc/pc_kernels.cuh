@@ -143,6 +143,9 @@ struct F32Launch {
 cudaError_t launch_fastssc_f32(const F32Launch& L, const float* d_llr, uint8_t* d_info, uint8_t* d_ok, size_t B, cudaStream_t st);
 // resident CTAs per SM of the on-chip kernel for this plan (registers, shared memory), <= 0 on error
 int fastssc_f32_sm_occupancy(const F32Launch& L);
+// soft-output form (pc_decode_soft_batch_f32): p.arena / p.bits_arena laid out for grid * threads threads with N more words per thread
+cudaError_t launch_fastssc_f32_soft(const F32Params& p, int grid, int threads, float* d_soft_code, float* d_soft_info, const uint32_t* d_lut,
+                                    cudaStream_t st);
 cudaError_t launch_i8_to_f32(const int8_t* d_in, float* d_out, size_t n, cudaStream_t st);
 
 cudaError_t const_pool_upload(int offset_words, const uint32_t* h_src, int nwords, cudaStream_t st);

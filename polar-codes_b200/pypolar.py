@@ -161,18 +161,23 @@ class PolarDecoder(_Code):
         return (out, ok) if return_ok else out
 
     def decode_soft_batch(self, llrs):
-        """[B, N] int8 (or float32, quantised like decode_vector does) -> (soft codeword int8 [B, N], soft information
-        int8 [B, K]): Decoder::getSoftCodeword / getSoftInformation (decoder.cpp:147-152) after decode(), for every row.
-        int8 Fast-SSC ('char', L = 1) only. numpy in -> numpy out; torch CUDA tensor in -> CUDA tensors out."""
+        """[B, N] LLRs -> (soft codeword [B, N], soft information [B, K]): Decoder::getSoftCodeword / getSoftInformation
+        (decoder.cpp:147-152) after decode(), for every row. 'char' Fast-SSC (L = 1): int8 containers (float32 input is
+        quantised like decode_vector does); 'float' Fast-SSC (L = 1): float32 containers, bit for bit the reference's
+        patterns (inner words are XORs of float patterns -- compare them through .view(uint32)). Other kinds raise.
+        numpy in -> numpy out; torch CUDA tensor in -> CUDA tensors out."""
+        isf = self._kind == capi.PC_DEC_FASTSSC_F32
+        fn_dev = lib().pc_decode_soft_batch_f32 if isf else lib().pc_decode_soft_batch
+        fn_host = lib().pc_decode_soft_batch_f32_host if isf else lib().pc_decode_soft_batch_host
         if hasattr(llrs, "is_cuda") and llrs.is_cuda:
             import torch
             llrs = llrs.contiguous()
             B = llrs.shape[0]
-            sc = torch.empty((B, self._N), dtype=torch.int8, device=llrs.device)
-            si = torch.empty((B, self._K), dtype=torch.int8, device=llrs.device)
+            dt = torch.float32 if isf else torch.int8
+            sc = torch.empty((B, self._N), dtype=dt, device=llrs.device)
+            si = torch.empty((B, self._K), dtype=dt, device=llrs.device)
             st = torch.cuda.current_stream(llrs.device).cuda_stream
-            check(lib().pc_decode_soft_batch(self._h, ptr(llrs), int(llrs.dtype == torch.float32), ptr(sc), ptr(si), B,
-                                             ctypes.c_void_p(st)))
+            check(fn_dev(self._h, ptr(llrs), int(llrs.dtype == torch.float32), ptr(sc), ptr(si), B, ctypes.c_void_p(st)))
             return sc, si
         a = np.asarray(llrs)
         if a.ndim != 2 or a.shape[1] != self._N:
@@ -181,8 +186,9 @@ class PolarDecoder(_Code):
             a = a.astype(np.float32, copy=False)
         a = np.ascontiguousarray(a)
         B = a.shape[0]
-        sc, si = np.empty((B, self._N), np.int8), np.empty((B, self._K), np.int8)
-        check(lib().pc_decode_soft_batch_host(self._h, ptr(a), int(a.dtype == np.float32), ptr(sc), ptr(si), B))
+        dt = np.float32 if isf else np.int8
+        sc, si = np.empty((B, self._N), dt), np.empty((B, self._K), dt)
+        check(fn_host(self._h, ptr(a), int(a.dtype == np.float32), ptr(sc), ptr(si), B))
         return sc, si
 
     def decode_vector(self, array):

@@ -112,6 +112,27 @@ int cxx_decode(int N, int L, const unsigned* frozen, int nf, const char* kind, i
 }
 // Puncturer (puncturer.h:37-101): positions, then puncture<float>, puncturePacked, depuncture<float> of one vector
 // each; status 5 = std::out_of_range (checked before logic_error, its base class)
+// Decoder::getSoftCodeword / getSoftInformation after decode_vector, per row (the container type follows the decoder:
+// int8 for 'char', float for 'float'); elem = bytes per container element
+int cxx_soft(int N, int L, const unsigned* frozen, int nf, const char* kind, int is_float, const void* llr, long B, void* soft_code,
+             void* soft_info, int elem)
+{
+    return guarded([&] {
+        std::vector<unsigned> fz(frozen, frozen + nf);
+        std::unique_ptr<Decoding::Decoder> dec(Decoding::create((size_t)N, (size_t)L, fz, kind));
+        const size_t K = dec->infoLength();
+        std::vector<unsigned char> out((K + 7) / 8 + 8);
+        for (long i = 0; i < B; ++i) {
+            if (is_float)
+                dec->decode_vector(static_cast<const float*>(llr) + i * N, out.data());
+            else
+                dec->decode_vector(static_cast<const char*>(llr) + i * N, out.data());
+            dec->getSoftCodeword(static_cast<char*>(soft_code) + (size_t)i * N * elem);
+            dec->getSoftInformation(static_cast<char*>(soft_info) + (size_t)i * K * elem);
+        }
+    });
+}
+
 int cxx_puncturer(long blockLength, const unsigned* frozen, int nf, unsigned* positions, long* parent, const float* in,
                   float* punctured, const unsigned char* packed_in, unsigned char* packed_out, float* depunctured)
 {

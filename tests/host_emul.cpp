@@ -129,6 +129,48 @@ int emul_fastssc_f32_decode(int N, const unsigned* frozen, int nf, int systemati
     return 0;
 }
 
+// the fp32 core with the soft-output context (the float bit container of Decoder::getSoftCodeword) on the host
+int emul_fastssc_f32_soft(int N, const unsigned* frozen, int nf, const float* llr, long B, uint32_t* soft_code)
+{
+    FloatProgram fp;
+    const char* msg = nullptr;
+    if (!compile_fastssc_f32(N, frozen, nf, fp, &msg)) return 3;
+    const int S = fp.S;
+    std::vector<int> off(S + 2, 0);
+    int w = 0;
+    for (int s = 0; s <= S; ++s) {
+        off[s] = w;
+        w += 1 << s;
+    }
+    std::vector<float> llrs(w + 8);
+    std::vector<uint32_t> bits((N + 31) / 32 + 1), soft(N);
+    for (long i = 0; i < B; ++i) {
+        FSoftCtx c;
+        c.S = S;
+        c.llr_off = off.data();
+        c.llr = llrs.data();
+        c.ls = 1;
+        c.bits = bits.data();
+        c.bs = 1;
+        c.soft = soft.data();
+        c.ss = 1;
+        std::fill(bits.begin(), bits.end(), 0u);
+        const float* row = llr + i * N;
+        if (fp.staged_root)
+            for (int k = 0; k < N; ++k) c.st(S, k, row[k]);
+        for (size_t pc = 0;; ++pc) {
+            const uint32_t ins = fp.code[pc];
+            const uint32_t op = instr_op(ins);
+            const int s = (int)instr_s(ins), o = (int)instr_off(ins);
+            if (op == FOP_END) break;
+            const FView in = (s == S && !fp.staged_root) ? FView{ row, 1 } : c.stage(s);
+            fastssc_f32_step(c, in, op, s, o);
+        }
+        memcpy(soft_code + i * N, soft.data(), 4 * (size_t)N);
+    }
+    return 0;
+}
+
 int emul_program(int N, const unsigned* frozen, int nf, uint32_t* code, int cap)
 {
     FastSscProgram p;

@@ -42,6 +42,9 @@ def lib():
         L.ref_decode_soft.restype = ctypes.c_int
         L.ref_decode_soft.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_long,
                                       ctypes.c_void_p, ctypes.c_void_p]
+        L.ref_decode_soft_f32.restype = ctypes.c_int
+        L.ref_decode_soft_f32.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_long,
+                                      ctypes.c_void_p, ctypes.c_void_p]
         L.ref_quantize.restype = ctypes.c_int
         L.ref_quantize.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_long, ctypes.c_void_p]
         L.ref_puncturer.restype = ctypes.c_long
@@ -91,6 +94,17 @@ def decode_soft(N, frozen, llr, systematic=True):
     sc, si = np.zeros((B, N), np.int8), np.zeros((B, K), np.int8)
     if lib().ref_decode_soft(N, _p(frozen), len(frozen), int(systematic), _p(llr), B, _p(sc), _p(si)) < 0:
         raise RuntimeError("reference soft decode failed")
+    return sc, si
+
+
+def decode_soft_f32(N, frozen, llr, systematic=True):
+    """the same getters of the 'float' Fast-SSC decoder: float32 [B, N] / [B, K], to be compared as uint32 patterns"""
+    frozen = np.ascontiguousarray(frozen, dtype=np.uint32)
+    llr = np.ascontiguousarray(llr, dtype=np.float32)
+    B, K = llr.shape[0], N - len(frozen)
+    sc, si = np.zeros((B, N), np.float32), np.zeros((B, K), np.float32)
+    if lib().ref_decode_soft_f32(N, _p(frozen), len(frozen), int(systematic), _p(llr), B, _p(sc), _p(si)) < 0:
+        raise RuntimeError("reference float soft decode failed")
     return sc, si
 
 

@@ -142,3 +142,23 @@ def test_cxx_puncturer_matches_reference(cxx, ref):
     assert np.array_equal(packed, ref.puncturer(M, f, "packed", bits[None])[0])
     assert np.array_equal(dep, ref.puncturer(M, f, "depuncture", punct[None])[0])
     assert cxx.cxx_puncturer(100, _p(f), 10, _p(pos), ctypes.byref(parent), _p(x), _p(punct), _p(bits), _p(packed), _p(dep)) == 5
+
+
+@pytest.mark.gpu
+def test_cxx_soft_getters_match_reference(cxx, ref):
+    """getSoftCodeword / getSoftInformation of the class mirror: int8 container for 'char', float patterns for 'float';
+    the list decoders throw std::logic_error"""
+    N, K = 256, 128
+    fz = np.ascontiguousarray(ref.frozen_bits(N, K, 0.0), dtype=np.uint32)
+    rng = np.random.default_rng(9)
+    y = (3.0 * (1.0 + 0.8 * rng.standard_normal((24, N)))).astype(np.float32)
+    sc, si = np.zeros((24, N), np.float32), np.zeros((24, K), np.float32)
+    assert cxx.cxx_soft(N, 1, _p(fz), len(fz), b"float", 1, _p(y), ctypes.c_long(24), _p(sc), _p(si), 4) == 0
+    esc, esi = ref.decode_soft_f32(N, fz, y)
+    assert np.array_equal(sc.view(np.uint32), esc.view(np.uint32)) and np.array_equal(si.view(np.uint32), esi.view(np.uint32))
+    q = np.clip(np.rint(y * 4), -128, 127).astype(np.int8)
+    bc, bi = np.zeros((24, N), np.int8), np.zeros((24, K), np.int8)
+    assert cxx.cxx_soft(N, 1, _p(fz), len(fz), b"char", 0, _p(q), ctypes.c_long(24), _p(bc), _p(bi), 1) == 0
+    ebc, ebi = ref.decode_soft(N, fz, q)
+    assert np.array_equal(bc, ebc) and np.array_equal(bi, ebi)
+    assert cxx.cxx_soft(N, 4, _p(fz), len(fz), b"char", 0, _p(q), ctypes.c_long(1), _p(bc), _p(bi), 1) == 2

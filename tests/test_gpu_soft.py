@@ -1,4 +1,4 @@
-"""Soft outputs of the int8 Fast-SSC decoder: Decoder::getSoftCodeword / getSoftInformation
+"""Soft outputs of the int8 and fp32 Fast-SSC decoders: Decoder::getSoftCodeword / getSoftInformation
 (reference src/polarcode/decoding/decoder.cpp:147-152) byte for byte against the unmodified reference, plus the
 reference's own soft-output KATs (test/polarcode/decodingtest.cpp:83-156: REP / DoubleREP saturation)."""
 import numpy as np
@@ -60,7 +60,44 @@ def test_soft_device_tensors_and_float_input(pcb, ref):
 
 def test_soft_refused_for_other_kinds(pcb, ref):
     fz = ref.frozen_bits(256, 128, 0.0)
-    for kind, L in (("float", 1), ("char", 4), ("mixed", 4)):
+    for kind, L in (("float", 4), ("char", 4), ("mixed", 4)):
         dec = pcb.PolarDecoder(256, L, list(fz), kind)
         with pytest.raises(Exception, match="soft outputs"):
             dec.decode_soft_batch(np.zeros((2, 256), np.int8))
+
+
+@pytest.mark.parametrize("N,K", [(8, 4), (32, 16), (64, 40), (128, 100), (256, 128), (512, 256), (1024, 512), (1024, 900), (1024, 100),
+                                 (2048, 1024), (4096, 2048)])
+def test_float_soft_outputs_match_reference(pcb, ref, N, K):
+    """getSoftCodeword / getSoftInformation of the 'float' Fast-SSC decoder: the float bit container as 32-bit patterns"""
+    rng = np.random.default_rng(11 * N + K)
+    fz = ref.frozen_bits(N, K, 0.0)
+    dec = pcb.PolarDecoder(N, 1, list(fz), "float")
+    llr = np.concatenate([(a * (1.0 + s * rng.standard_normal((300, N)))).astype(np.float32) for a, s in ((2.0, 1.0), (8.0, 0.7), (1.0, 3.0))] +
+                         [rng.choice(np.array([0.0, -0.0, 1.0, -1.0, 2.5], np.float32), (100, N))])
+    sc, si = dec.decode_soft_batch(llr)
+    esc, esi = ref.decode_soft_f32(N, fz, llr)
+    bad = (sc.view(np.uint32) != esc.view(np.uint32)).any(axis=1)
+    assert not bad.any(), f"soft codeword differs in {bad.sum()} frames"
+    assert np.array_equal(si.view(np.uint32), esi.view(np.uint32))
+    # the hard decisions are the signs of that container
+    out = dec.decode_batch(llr)
+    exp, _ = ref.decode_batch(N, 1, fz, "float", llr, crc_bits=8)
+    assert np.array_equal(out, exp)
+
+
+def test_float_soft_device_tensors_int8_input_and_c2_batch(pcb, ref):
+    import torch
+    N, K = 1024, 512
+    fz = ref.frozen_bits(N, K, 0.0)
+    dec = pcb.PolarDecoder(N, 1, list(fz), "float")
+    rng = np.random.default_rng(5)
+    y = (4.0 * 10 ** 0.2 * (1.0 + 0.79 * rng.standard_normal((4096, N)))).astype(np.float32)
+    sc, si = dec.decode_soft_batch(torch.from_numpy(y).cuda())
+    esc, esi = ref.decode_soft_f32(N, fz, y)
+    assert np.array_equal(sc.cpu().numpy().view(np.uint32), esc.view(np.uint32))
+    assert np.array_equal(si.cpu().numpy().view(np.uint32), esi.view(np.uint32))
+    q = np.clip(np.rint(y[:512] * 4), -128, 127).astype(np.int8)  # FloatContainer::insertLlr(const char*): int8 -> float
+    sc8, _ = dec.decode_soft_batch(q)
+    esc8, _ = ref.decode_soft_f32(N, fz, q.astype(np.float32))
+    assert np.array_equal(sc8.view(np.uint32), esc8.view(np.uint32))

@@ -83,7 +83,7 @@ def emul():
     so = os.path.join(build, "libhost_emul.so")
     srcs = [os.path.join(ROOT, "tests", "host_emul.cpp"), os.path.join(ROOT, "polar-codes_b200", "csrc", "pc_program.cpp")]
     deps = srcs + [os.path.join(ROOT, "polar-codes_b200", "csrc", f) for f in
-                   ("pc_fastssc_i8_core.h", "pc_swar.h", "pc_crc.h", "pc_program.h")]
+                   ("pc_fastssc_i8_core.h", "pc_fastssc_f32_core.h", "pc_swar.h", "pc_crc.h", "pc_program.h")]
     if not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(d) for d in deps):
         subprocess.check_call(["g++", "-std=c++17", "-O2", "-fPIC", "-shared", "-ffp-contract=off", "-o", so] + srcs)
     return ctypes.CDLL(so)
@@ -139,3 +139,28 @@ def test_swar_primitives_exhaustive(orc):
     out = np.where((a < 0) ^ (b < 0), -mag, mag)
     assert np.array_equal(out.astype(np.int8), orc.f_i8(a.astype(np.int8), b.astype(np.int8)))
     assert (x + y).max() <= 255 and (m + 1 + np.abs(m - 1)).max() <= 254
+
+
+@pytest.mark.parametrize("N,K", [(8, 4), (16, 8), (32, 16), (64, 40), (128, 100), (256, 128), (512, 256), (1024, 512), (1024, 900),
+                                 (1024, 100), (2048, 1024)])
+def test_float_soft_container_on_host_vs_reference(emul, ref, N, K):
+    """the fp32 core with its soft-output context (FSoftCtx, what k_fastssc_f32_soft runs per thread) on the CPU against
+    FloatContainer::getSoftBits of the unmodified reference, compared as 32-bit patterns (inner words are XORs of floats)"""
+    rng = np.random.default_rng(7 * N + K)
+    for dsnr in (0.0, 2.0):
+        fz = np.ascontiguousarray(ref.frozen_bits(N, K, dsnr), dtype=np.uint32)
+        llr = np.concatenate([(a * (1.0 + s * rng.standard_normal((40, N)))).astype(np.float32) for a, s in ((2.0, 1.0), (8.0, 0.7), (1.0, 3.0))] +
+                             [rng.choice(np.array([0.0, -0.0, 1.0, -1.0, 2.5], np.float32), (40, N))])
+        B = llr.shape[0]
+        got = np.zeros((B, N), np.uint32)
+        vp = ctypes.c_void_p
+        r = emul.emul_fastssc_f32_soft(N, fz.ctypes.data_as(vp), len(fz), llr.ctypes.data_as(vp), ctypes.c_long(B), got.ctypes.data_as(vp))
+        if r == 3:
+            with pytest.raises(RuntimeError):
+                ref.decode_soft_f32(N, fz, llr)
+            continue
+        assert r == 0
+        esc, _ = ref.decode_soft_f32(N, fz, llr)
+        exp = esc.view(np.uint32)
+        bad = (got != exp).any(axis=1)
+        assert not bad.any(), f"{bad.sum()} of {B} frames differ, first: frame {np.argmax(bad)} at {np.nonzero(got[np.argmax(bad)] != exp[np.argmax(bad)])[0][:8]}"
