@@ -255,15 +255,39 @@ __device__ __forceinline__ void tm_st8_f32(uint32_t taddr, const float* a)
                  : "memory");
 }
 
-template <int T>
-struct SmView { // a stage in shared memory
+__device__ __forceinline__ void lds4_f32(uint32_t a, float* v)
+{
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]) : "r"(a));
+}
+__device__ __forceinline__ void sts4_f32(uint32_t a, const float* v)
+{
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]) : "memory");
+}
+// QUAD layout of the shared-memory stages: elements 4q .. 4q+3 of a thread are 16 contiguous bytes, quad q of thread t at
+// byte 16 (q T + t) of the stage, so the f / g loops move four elements per LDS.128 / STS.128 (a warp access is 512
+// contiguous bytes, conflict-free) and a scalar access costs one shift / mask more. Stages 0 and 1 take a quad each,
+// stage s >= 2 takes 2^(s-2): quad offset of stage s = sm_quad_off(s).
+__device__ __forceinline__ uint32_t sm_quad_off(int s) { return s < 2 ? (uint32_t)s : (1u << (s - 2)) + 1u; }
+
+template <int T, bool QUAD>
+struct SmView { // a stage in shared memory (QUAD: the quad layout above; else element i of a thread at byte 4 T i)
     static constexpr int kBatch = 8;
-    uint32_t a; // shared address of this thread's element 0
-    __device__ __forceinline__ float operator[](int i) const { return lds_f32(a + 4u * T * (uint32_t)i); }
-    __device__ __forceinline__ void ld8(int i, float* v) const
+    uint32_t a; // shared address of this thread's element 0 of the stage
+    __device__ __forceinline__ float operator[](int i) const
     {
+        if (QUAD) return lds_f32(a + 16u * T * ((uint32_t)i >> 2) + 4u * ((uint32_t)i & 3u));
+        return lds_f32(a + 4u * T * (uint32_t)i);
+    }
+    __device__ __forceinline__ void ld8(int i, float* v) const // i is a multiple of 8
+    {
+        if (QUAD) {
+            const uint32_t q = a + 16u * T * ((uint32_t)i >> 2);
+            lds4_f32(q, v);
+            lds4_f32(q + 16u * T, v + 4);
+        } else {
 #pragma unroll
-        for (int k = 0; k < 8; ++k) v[k] = lds_f32(a + 4u * T * (uint32_t)(i + k));
+            for (int k = 0; k < 8; ++k) v[k] = lds_f32(a + 4u * T * (uint32_t)(i + k));
+        }
     }
     __device__ __forceinline__ void wait() const {}
 };
@@ -294,20 +318,28 @@ struct RowView { // the channel row in global memory, contiguous and 16-byte ali
 };
 
 // DST_TM: the step's destination stage (s - 1) is stage S-1 in tensor memory, else a shared-memory stage
-template <int T, bool DST_TM>
+template <int T, bool DST_TM, bool QUAD>
 struct SmCtx {
     static constexpr bool kSoft = false;
-    uint32_t sm_llr;  // shared address of this thread's element 0 of stage 0 (stage s starts 2^s - 1 elements further)
+    uint32_t sm_llr;  // shared address of this thread's element 0 of stage 0 (stage s starts sm_quad_off(s) quads /
+                      // 2^s - 1 elements further)
     uint32_t sm_bits; // shared address of this thread's decision word 0
     uint32_t tm;      // tensor-memory address of column 0 of stage S-1 in this warp's lane quarter
-    __device__ __forceinline__ SmView<T> sview(int s) const { return SmView<T>{ sm_llr + 4u * T * ((1u << s) - 1u) }; }
+    __device__ __forceinline__ uint32_t sbase(int s) const
+    {
+        return QUAD ? sm_llr + 16u * T * sm_quad_off(s) : sm_llr + 4u * T * ((1u << s) - 1u);
+    }
+    __device__ __forceinline__ SmView<T, QUAD> sview(int s) const { return SmView<T, QUAD>{ sbase(s) }; }
     __device__ __forceinline__ void st(int s, int i, float v) const
     {
         if (DST_TM) {
             __syncwarp();
             tm_st1(tm + (uint32_t)i, __float_as_uint(v));
         } else {
-            sts_f32(sm_llr + 4u * T * (((1u << s) - 1u) + (uint32_t)i), v);
+            if (QUAD)
+                sts_f32(sbase(s) + 16u * T * ((uint32_t)i >> 2) + 4u * ((uint32_t)i & 3u), v);
+            else
+                sts_f32(sbase(s) + 4u * T * (uint32_t)i, v);
         }
     }
     __device__ __forceinline__ void st8(int s, int i, const float* v) const
@@ -315,9 +347,15 @@ struct SmCtx {
         if (DST_TM) {
             tm_st8_f32(tm + (uint32_t)i, v);
         } else {
-            const uint32_t a = sm_llr + 4u * T * (((1u << s) - 1u) + (uint32_t)i);
+            if (QUAD) {
+                const uint32_t a = sbase(s) + 16u * T * ((uint32_t)i >> 2); // i is a multiple of 8
+                sts4_f32(a, v);
+                sts4_f32(a + 16u * T, v + 4);
+            } else {
+                const uint32_t a = sbase(s) + 4u * T * (uint32_t)i;
 #pragma unroll
-            for (int k = 0; k < 8; ++k) sts_f32(a + 4u * T * k, v[k]);
+                for (int k = 0; k < 8; ++k) sts_f32(a + 4u * T * k, v[k]);
+            }
         }
     }
     __device__ __forceinline__ uint32_t bld(int w) const { return lds_w(sm_bits + 4u * T * (uint32_t)w); }
@@ -349,7 +387,10 @@ struct SmCtx {
 };
 
 // HAS_TM: stage S-1 lives in tensor memory (p.sm_top == S - 2); else every stage is in shared memory (p.sm_top == S - 1)
-template <int T, bool HAS_TM>
+// QUAD: quad layout of the shared-memory stages. Measured (profiles/r02_c24_perf.txt): N = 256 68.2 -> 78.8 Gbit/s,
+// N = 128 80.6 -> 91.4, N = 64 77.8 -> 87.5; N = 512 (45.2 against 42.8 ... 48.5) and N = 1024 with stage S-1 in tensor
+// memory (48.0 against 46.2 ... 49.3) move inside their run-to-run spread; the tensor-memory plan keeps the plain layout.
+template <int T, bool HAS_TM, bool QUAD>
 __global__ void __launch_bounds__(T, 1) k_fastssc_f32_sm(const __grid_constant__ F32Params p)
 {
     extern __shared__ __align__(16) uint32_t smem_sm[];
@@ -369,13 +410,13 @@ __global__ void __launch_bounds__(T, 1) k_fastssc_f32_sm(const __grid_constant__
     }
     __syncthreads();
     if (HAS_TM) asm volatile("tcgen05.fence::after_thread_sync;");
-    const int S = p.S, top = p.sm_top, g0 = (2 << top) - 1;
+    const int S = p.S, top = p.sm_top, g0 = 4 * ((1 << (top - 1)) + 1); // float words per thread (the quad layout's count, either layout)
     uint32_t* bits_gen = smem_sm + 256 + (size_t)g0 * T + t;
-    SmCtx<T, false> cs;
-    cs.sm_llr = (uint32_t)__cvta_generic_to_shared(smem_sm + 256 + t);
+    SmCtx<T, false, QUAD> cs;
+    cs.sm_llr = (uint32_t)__cvta_generic_to_shared(smem_sm + 256 + (QUAD ? 4 * t : t));
     cs.sm_bits = (uint32_t)__cvta_generic_to_shared(bits_gen);
     cs.tm = HAS_TM ? tm_base_s + ((uint32_t)((t >> 5) & 3) << 21) : 0u; // lane field = 32 * (warp % 4), bits 31:16
-    SmCtx<T, true> ct;
+    SmCtx<T, true, QUAD> ct;
     ct.sm_llr = cs.sm_llr, ct.sm_bits = cs.sm_bits, ct.tm = cs.tm;
     Ctx ic; // the int8 core's decision-word helpers (transform, gather) on the same words
     ic.S = S;
@@ -490,6 +531,19 @@ cudaError_t launch_i8_to_f32(const int8_t* d_in, float* d_out, size_t n, cudaStr
     return cudaGetLastError();
 }
 
+// the instantiation a plan names: CTA size 96 / 128, stage S-1 in tensor memory or not, quad layout or not
+template <class F>
+static auto sm_dispatch(const F32Launch& L, F&& f)
+{
+    const bool tm = L.p.sm_tm_cols != 0, quad = L.sm_quad != 0;
+    if (L.sm_threads == 128) {
+        if (tm) return quad ? f(k_fastssc_f32_sm<128, true, true>) : f(k_fastssc_f32_sm<128, true, false>);
+        return quad ? f(k_fastssc_f32_sm<128, false, true>) : f(k_fastssc_f32_sm<128, false, false>);
+    }
+    if (tm) return quad ? f(k_fastssc_f32_sm<96, true, true>) : f(k_fastssc_f32_sm<96, true, false>);
+    return quad ? f(k_fastssc_f32_sm<96, false, true>) : f(k_fastssc_f32_sm<96, false, false>);
+}
+
 template <class K>
 static int sm_occ(K kern, const F32Launch& L)
 {
@@ -501,8 +555,7 @@ static int sm_occ(K kern, const F32Launch& L)
 }
 int fastssc_f32_sm_occupancy(const F32Launch& L)
 {
-    if (L.sm_threads == 128) return L.p.sm_tm_cols ? sm_occ(k_fastssc_f32_sm<128, true>, L) : sm_occ(k_fastssc_f32_sm<128, false>, L);
-    return L.p.sm_tm_cols ? sm_occ(k_fastssc_f32_sm<96, true>, L) : sm_occ(k_fastssc_f32_sm<96, false>, L);
+    return sm_dispatch(L, [&](auto kern) { return sm_occ(kern, L); });
 }
 
 cudaError_t launch_fastssc_f32(const F32Launch& L, const float* d_llr, uint8_t* d_info, uint8_t* d_ok, size_t B, cudaStream_t st)
@@ -534,8 +587,7 @@ cudaError_t launch_fastssc_f32(const F32Launch& L, const float* d_llr, uint8_t* 
             kern<<<grid, L.sm_threads, L.sm_smem, st>>>(p);
             return cudaGetLastError();
         };
-        if (L.sm_threads == 128) return L.p.sm_tm_cols ? go(k_fastssc_f32_sm<128, true>) : go(k_fastssc_f32_sm<128, false>);
-        return L.p.sm_tm_cols ? go(k_fastssc_f32_sm<96, true>) : go(k_fastssc_f32_sm<96, false>);
+        return sm_dispatch(L, go);
     }
     size_t ctas = (B + L.threads - 1) / L.threads;
     const int grid = (int)(ctas < (size_t)L.grid ? ctas : (size_t)L.grid);

@@ -138,6 +138,7 @@ struct F32Launch {
     int g8, g8_threads, g8_grid; // group-of-8 kernel (tree in shared memory) chosen for this code
     size_t g8_smem;
     int sm, sm_threads, sm_grid; // on-chip kernel (k_fastssc_f32_sm): threads per CTA (96 / 128), CTAs
+    int sm_quad;                 // its shared-memory stages in the quad layout
     size_t sm_smem;
 };
 cudaError_t launch_fastssc_f32(const F32Launch& L, const float* d_llr, uint8_t* d_info, uint8_t* d_ok, size_t B, cudaStream_t st);
