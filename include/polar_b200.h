@@ -183,6 +183,16 @@ int pc_depuncture_batch(const pc_puncturer* p, const void* d_in, void* d_out, in
 /* puncturePacked: MSB-first packed bits, d_in[B][Np/8] -> d_out[B][M/8] (both lengths multiples of 8) */
 int pc_puncture_packed_batch(const pc_puncturer* p, const uint8_t* d_in, uint8_t* d_out, size_t B, void* stream);
 
+/* Allocation-free decode. No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The fp32 Fast-SSC decode of pc_decode_batch (kind PC_DEC_FASTSSC_F32, float32 LLRs on the device, same outputs bit for
+ * bit) with its per-thread scratch in a file-scope device array of 32 MiB that every GPU loading the library holds until
+ * exit; the call itself performs no cudaMalloc / cudaFree (pc_code_create / pc_code_set_crc, called earlier, do).
+ * Limits: block length N <= 4096 (PC_ERR_UNSUPPORTED beyond, and for other decoder kinds); any B (the grid strides).
+ * All calls on a device share the array, which keeps the previous call's contents (nothing in it needs to start at
+ * zero): calls that overlap on the GPU -- two streams, two host threads -- race; serialise them. Asynchronous on `stream`. */
+int pc_decode_batch_f32_static(pc_code* c, const float* d_llr, uint8_t* d_info, uint8_t* d_ok, size_t B, void* stream);
+
 /* device memory helpers so that non-CUDA hosts (ctypes, cgo, JNI) can drive the library alone */
 void* pc_device_alloc(size_t bytes);
 void pc_device_free(void* d);

@@ -65,6 +65,7 @@ SIGNATURES = {
     "pc_decode_soft_batch_host": (_i, [_vp, _vp, _i, _vp, _vp, _sz]),
     "pc_decode_soft_batch_f32": (_i, [_vp, _vp, _i, _vp, _vp, _sz, _vp]),
     "pc_decode_soft_batch_f32_host": (_i, [_vp, _vp, _i, _vp, _vp, _sz]),
+    "pc_decode_batch_f32_static": (_i, [_vp, _vp, _vp, _vp, _sz, _vp]),
     "pc_encode_batch": (_i, [_vp, _vp, _vp, _vp, _sz, _vp]),
     "pc_encode_batch_host": (_i, [_vp, _vp, _vp, _vp, _sz]),
     "pc_crc_generate_batch": (_i, [_i, _vp, _i, _sz, _vp]),
