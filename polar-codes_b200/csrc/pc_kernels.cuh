@@ -98,6 +98,7 @@ struct SclFParams {
     // tensor memory for the decision words (offsets carry kTmem), see SclParams
     int tm_alloc_cols, tm_cols_thread, scr_off, lockstep;
     int virt_top;     // LLR stage S-1 is not stored: its consumers recompute it from the channel row (pc_scl_f32.cu FgSrc)
+    int arena_quad;   // arena LLR stages in the quad layout (pc_scl_f32.cu FLaneT::View)
 };
 struct SclFLaunch {
     SclFParams p;

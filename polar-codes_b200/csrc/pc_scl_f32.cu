@@ -38,6 +38,8 @@ struct FLaneT {
     uint32_t* sm;   // smem base + tid (word w at sm[w * T])
     float* ar;      // arena base + global lane id (element e at ar[e * AS])
     size_t AS;
+    size_t gl3;     // 3 x global lane id (quad layout of the arena stages, see View)
+    int aq;         // arena LLR stages in the quad layout
     uint32_t tm;    // tensor-memory address of this thread's column 0
     int T, G, l;    // threads per CTA, lanes per group, lane index inside the group
     int P;          // live paths (uniform)
@@ -74,17 +76,34 @@ struct FLaneT {
         if (BM & BM_TMEM) tm_wait_st();
     }
     // LLR stage s (off = p.llr_off[s]) in lane `owner`'s space, resolved once per node step
+    // quad: an arena stage in the QUAD layout (p.arena_quad): elements 4q .. 4q+3 of a lane are 16 contiguous bytes, quad q
+    // of lane L at float (q AS + L) * 4 of the stage, so the f / g loops move four elements per 16-byte access (a warp
+    // access is 512 contiguous bytes); `stride` is then the distance between a lane's quads (4 AS).
     struct View {
         float* p;
         uint32_t stride; // element index * stride stays below 2^32 (the planner bounds the arena at 1 GiB)
-        __device__ __forceinline__ float operator[](int i) const { return p[(uint32_t)i * stride]; }
-        __device__ __forceinline__ void set(int i, float v) const { p[(uint32_t)i * stride] = v; }
+        uint32_t quad;
+        __device__ __forceinline__ float operator[](int i) const
+        {
+            return quad ? p[((uint32_t)i >> 2) * stride + ((uint32_t)i & 3u)] : p[(uint32_t)i * stride];
+        }
+        __device__ __forceinline__ void set(int i, float v) const
+        {
+            if (quad)
+                p[((uint32_t)i >> 2) * stride + ((uint32_t)i & 3u)] = v;
+            else
+                p[(uint32_t)i * stride] = v;
+        }
+        // four elements starting at i (a multiple of 4) of a quad view
+        __device__ __forceinline__ float4 ld4(int i) const { return *reinterpret_cast<const float4*>(p + ((uint32_t)i >> 2) * stride); }
+        __device__ __forceinline__ void st4(int i, const float4& v) const { *reinterpret_cast<float4*>(p + ((uint32_t)i >> 2) * stride) = v; }
     };
     __device__ __forceinline__ View view(int s, int off, uint32_t owner) const
     {
         const ptrdiff_t d = (int)owner - l;
-        if (s <= smem_top) return View{ reinterpret_cast<float*>(sm) + (size_t)off * T + d, (uint32_t)T };
-        return View{ ar + (size_t)off * AS + d, (uint32_t)AS };
+        if (s <= smem_top) return View{ reinterpret_cast<float*>(sm) + (size_t)off * T + d, (uint32_t)T, 0u };
+        if (aq) return View{ ar + (size_t)off * AS + gl3 + 4 * d, 4u * (uint32_t)AS, 1u };
+        return View{ ar + (size_t)off * AS + d, (uint32_t)AS, 0u };
     }
     // the lane's OWN stage in shared memory with the compile-time CTA size: 32-bit shared address, element i at + 4 TT i
     struct SView {
@@ -105,14 +124,14 @@ struct FLaneT {
     {
         const ptrdiff_t d = (int)owner - l;
         if (s <= smem_top) return __uint_as_float(sm[(size_t)(off + i) * T + d]);
-        return ar[(size_t)(off + i) * AS + d];
+        return view(s, off, owner)[i];
     }
     __device__ __forceinline__ void lst(int s, int off, int i, float v) const
     {
         if (s <= smem_top)
             sm[(size_t)(off + i) * T] = __float_as_uint(v);
         else
-            ar[(size_t)(off + i) * AS] = v;
+            view(s, off, (uint32_t)l).set(i, v);
     }
 };
 
@@ -190,6 +209,14 @@ __device__ __forceinline__ void fg_block(const FLane& c, FgSrc<FLane>& src, cons
                     }
                 }
             }
+        } else if (src.mode == 0 && src.v.quad) {
+            // a stored arena stage in the quad layout: one 16-byte load per four elements
+#pragma unroll
+            for (int u = 0; u < UNR; u += 4) {
+                const float4 va = src.v.ld4(j + u), vb = src.v.ld4(h + j + u);
+                a[u] = va.x, a[u + 1] = va.y, a[u + 2] = va.z, a[u + 3] = va.w;
+                b[u] = vb.x, b[u + 1] = vb.y, b[u + 2] = vb.z, b[u + 3] = vb.w;
+            }
         } else {
             src.bits_for(j, 0);
             src.bits_for(h + j, 1);
@@ -208,8 +235,13 @@ __device__ __forceinline__ void fg_block(const FLane& c, FgSrc<FLane>& src, cons
             for (int u = 0; u < UNR; ++u) r[u] = f_f32(a[u], b[u]);
         }
         if (active) {
+            if (dst.quad) {
 #pragma unroll
-            for (int u = 0; u < UNR; ++u) dst.set(j + u, r[u]);
+                for (int u = 0; u < UNR; u += 4) dst.st4(j + u, make_float4(r[u], r[u + 1], r[u + 2], r[u + 3]));
+            } else {
+#pragma unroll
+                for (int u = 0; u < UNR; ++u) dst.set(j + u, r[u]);
+            }
         }
     }
 }
@@ -237,6 +269,14 @@ __device__ __forceinline__ void sclf_fg_single(FLane& c, const SclFParams& p, in
         }
         if (j < h) {
             float a[8], b[8], r[8];
+            if (mode == 0 && src.quad) {
+#pragma unroll
+                for (int u = 0; u < 8; u += 4) {
+                    const float4 va = src.ld4(j + u), vb = src.ld4(h + j + u);
+                    a[u] = va.x, a[u + 1] = va.y, a[u + 2] = va.z, a[u + 3] = va.w;
+                    b[u] = vb.x, b[u + 1] = vb.y, b[u + 2] = vb.z, b[u + 3] = vb.w;
+                }
+            } else
 #pragma unroll
             for (int u = 0; u < 8; ++u) {
                 if (mode == 0) {
@@ -252,8 +292,13 @@ __device__ __forceinline__ void sclf_fg_single(FLane& c, const SclFParams& p, in
             }
 #pragma unroll
             for (int u = 0; u < 8; ++u) r[u] = IS_G ? g_f32(a[u], b[u], (bword >> ((j & 31) + u)) & 1u) : f_f32(a[u], b[u]);
+            if (dst.quad) {
+                dst.st4(j, make_float4(r[0], r[1], r[2], r[3]));
+                dst.st4(j + 4, make_float4(r[4], r[5], r[6], r[7]));
+            } else {
 #pragma unroll
-            for (int u = 0; u < 8; ++u) dst.set(j + u, r[u]);
+                for (int u = 0; u < 8; ++u) dst.set(j + u, r[u]);
+            }
         }
     }
     c.own_llr.set(s - 1, (uint32_t)c.l);
@@ -583,6 +628,8 @@ __global__ void __launch_bounds__(TT ? TT : ((BM & BM_TMEM) ? 384 : 128), (TT ||
     c.sm = smem + 256 + t;
     c.ar = p.arena + ((size_t)blockIdx.x * T + t);
     c.AS = p.arena_stride;
+    c.gl3 = 3 * ((size_t)blockIdx.x * T + t);
+    c.aq = p.arena_quad;
     c.tm = (BM & BM_TMEM) ? tm_base_s + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)((warp >> 2) * p.tm_cols_thread) : 0u;
     c.T = T;
     c.G = p.G;
@@ -815,6 +862,7 @@ static int plan_scl_f32_smem(int S, int K, int L, bool root_leaf, size_t smem_ma
     p.words = w;
     p.smem_top = smem_top;
     p.arena_elems = e;
+    p.arena_quad = (smem_top >= 1 && !getenv("PC_SCLF_NOQUAD")) ? 1 : 0; // every arena LLR stage then holds whole quads at a quad offset
     p.tm_alloc_cols = 0;
     p.tm_cols_thread = 0;
     p.scr_off = p.bitL_off[S]; // non-systematic extraction works on the (free) left buffer of the top stage
@@ -913,6 +961,7 @@ int plan_scl_f32(int S, int K, int L, bool root_leaf, bool virt_ok, size_t smem_
             p.words = w;
             p.smem_top = smem_top;
             p.arena_elems = e;
+            p.arena_quad = (smem_top >= 1 && !getenv("PC_SCLF_NOQUAD")) ? 1 : 0;
             p.tm_alloc_cols = tm_alloc;
             p.tm_cols_thread = tm_cols;
             p.scr_off = scr;
