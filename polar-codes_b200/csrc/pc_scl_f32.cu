@@ -598,7 +598,8 @@ __device__ __forceinline__ void sclf_spc(FLane& c, const SclFParams& p, int s, i
     set_side(c, s, side);
 }
 
-template <int BM, int TT>
+// GG: lanes per group as a compile-time constant (0 = run-time p.G), as in k_scl_i8
+template <int BM, int TT, int GG = 0>
 // Launch bounds: the tensor-memory plans run ONE CTA of TT (or, for an odd PC_SCLF_T, up to 384) lanes per SM and may use
 // the registers that leaves; the shared-memory plans (short codes: CTAs of <= 128 lanes, up to eight per SM) are held to
 // the 96-100 registers of five resident CTAs -- without the second bound they compiled to 138 registers, three CTAs per
@@ -632,16 +633,17 @@ __global__ void __launch_bounds__(TT ? TT : ((BM & BM_TMEM) ? 384 : 128), (TT ||
     c.aq = p.arena_quad;
     c.tm = (BM & BM_TMEM) ? tm_base_s + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)((warp >> 2) * p.tm_cols_thread) : 0u;
     c.T = T;
-    c.G = p.G;
-    c.l = t & (p.G - 1);
+    const int G = GG ? GG : p.G;
+    c.G = G;
+    c.l = t & (G - 1);
     c.smem_top = p.smem_top;
-    const int gpc = T / p.G; // codewords per CTA
+    const int gpc = T / G; // codewords per CTA
     const int N = 1 << p.S, kb = (p.K + 7) >> 3;
-    const unsigned gmask = (p.G == 32 ? 0xFFFFFFFFu : ((1u << p.G) - 1u)) << ((t & 31) & ~(p.G - 1));
+    const unsigned gmask = (G == 32 ? 0xFFFFFFFFu : ((1u << G) - 1u)) << ((t & 31) & ~(G - 1));
     const unsigned long long B = p.count ? *p.count : p.B;
     const unsigned long long nbatch = (B + gpc - 1) / gpc; // 0 when there is nothing to do: straight to the dealloc
     for (unsigned long long bi = blockIdx.x; bi < nbatch; bi += gridDim.x) {
-        const unsigned long long fl = bi * gpc + (unsigned long long)(t / p.G);
+        const unsigned long long fl = bi * gpc + (unsigned long long)(t / G);
         const bool live_frame = fl < B;
         unsigned long long f = live_frame ? fl : B - 1;
         if (p.frame_idx) f = p.frame_idx[f];
@@ -672,7 +674,7 @@ __global__ void __launch_bounds__(TT ? TT : ((BM & BM_TMEM) ? 384 : 128), (TT ||
             // other lanes' buffers are read by the next step; `lockstep` keeps the CTA's warps on the same program step
             // (the kernel is ~90 KB of SASS; free-running warps thrash the instruction caches, see pc_scl_i8.cu)
             c.st_fence();
-            if (p.lockstep)
+            if (GG || p.lockstep)
                 __syncthreads();
             else
                 __syncwarp();
@@ -746,6 +748,8 @@ cudaError_t launch_scl_f32(const SclFLaunch& L, const float* d_llr, uint8_t* d_i
         case 256: kern = k_scl_f32<BM_TMEM, 256>; break;
         default: kern = k_scl_f32<BM_TMEM, 0>; break;
         }
+        // the metric's L = 8 (5 ... 8) at the default CTA size: group size and lockstep fold at compile time
+        if (L.threads == 384 && p.G == 8 && p.lockstep == 1 && !getenv("PC_SCL_GRT")) kern = k_scl_f32<BM_TMEM, 384, 8>;
     }
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes);
     // several CTAs per SM only fit when the L1/shared split is at its shared-memory maximum; a single CTA keeps the

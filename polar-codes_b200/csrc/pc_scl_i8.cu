@@ -39,10 +39,12 @@ __device__ __forceinline__ void sts_u32(uint32_t a, uint32_t v) { asm volatile("
 // BM: BM_ARENA some decision words live in the arena (long codes), BM_TMEM in tensor memory; 0 = no flag tests.
 // TT: threads per CTA as a compile-time constant (0 = run-time): word w of a lane's shared-memory column sits at byte
 // offset 4 TT w, an immediate of the load when w and TT are known
-template <int BM, int TT>
+template <int BM, int TT, int GG = 0>
 struct LaneT {
     static constexpr int kTT = TT;
+    static constexpr int kGG = GG; // lanes per group when known at compile time (launch_scl_i8 picks it only with sort2 and lockstep on)
     uint32_t* sm;   // smem base + tid (word w at sm[w * T])
+    uint32_t sm32;  // the same as a 32-bit shared address
     uint32_t* ar;   // arena base + global lane id (word w at ar[w * AS])
     size_t AS;
     uint32_t tm;    // tensor-memory address of this thread's column 0 (lane quarter of its warp + column base)
@@ -61,6 +63,7 @@ struct LaneT {
             return __shfl_sync(0xFFFFFFFFu, v, (int)owner, G);
         }
         if ((BM & BM_ARENA) && (word & kArena)) return ar[(size_t)(word & (kArena - 1)) * AS + ((int)owner - l)];
+        if (TT) return lds_u32(sm32 + 4u * ((uint32_t)word * (uint32_t)TT + (uint32_t)((int)owner - l)));
         return sm[(size_t)word * T + ((int)owner - l)];
     }
     __device__ __forceinline__ void st(int word, uint32_t v) const
@@ -69,6 +72,8 @@ struct LaneT {
             tm_st1(tm + (uint32_t)(word & 0xFFFF), v); // completion is awaited by st_fence(), once per step
         } else if ((BM & BM_ARENA) && (word & kArena))
             ar[(size_t)(word & (kArena - 1)) * AS] = v;
+        else if (TT)
+            sts_u32(sm32 + 4u * (uint32_t)word * (uint32_t)TT, v);
         else
             sm[(size_t)word * T] = v;
     }
@@ -85,6 +90,8 @@ struct LaneT {
         __device__ __forceinline__ uint32_t operator[](int w) const { return p[(uint32_t)w * stride]; }
         __device__ __forceinline__ void set(int w, uint32_t v) const { p[(uint32_t)w * stride] = v; }
     };
+    // (Measured and not adopted: shared-address views for every access when all LLR stages sit in shared memory -- the
+    // same 9.20 Gbit/s as these generic views, profiles/r02_c33_perf.txt; the decision-word ld / st above do use them.)
     __device__ __forceinline__ View view(int off, uint32_t owner) const
     {
         const ptrdiff_t d = (int)owner - l;
@@ -103,7 +110,7 @@ struct LaneT {
     __device__ __forceinline__ void with_own_view(int off, F&& f) const
     {
         if (TT != 0 && !(off & kArena))
-            f(SView{ (uint32_t)__cvta_generic_to_shared(sm) + 4u * (uint32_t)(TT ? TT : 1) * (uint32_t)off });
+            f(SView{ sm32 + 4u * (uint32_t)(TT ? TT : 1) * (uint32_t)off });
         else
             f(view(off, (uint32_t)l));
     }
@@ -187,7 +194,7 @@ __device__ __forceinline__ void scl_fg(Lane& c, const SclParams& p, int s, const
         // offsets are immediates (the view path below pays a multiply-add per access, 12 % of the executed
         // instructions in ncu r02_scl_i8_v1)
         constexpr uint32_t ES = 4u * (uint32_t)Lane::kTT;
-        const uint32_t smb = (uint32_t)__cvta_generic_to_shared(c.sm);
+        const uint32_t smb = c.sm32;
         const uint32_t sa = smb + ES * (uint32_t)p.llr_off[s] + 4u * (uint32_t)((int)o - c.l), da = smb + ES * (uint32_t)p.llr_off[s - 1];
         const int hw = h >> 2;
         uint32_t bword = 0;
@@ -467,7 +474,7 @@ __device__ __forceinline__ void scl_rep(Lane& c, const SclParams& p, int s, int 
     }
     const int newP = 2 * c.P < p.L ? 2 * c.P : p.L;
     int val, idx;
-    if (p.sort2)
+    if (Lane::kGG || p.sort2)
         scl_sort_packed2<2>(c, v, newP, val, idx);
     else
         scl_sort_packed<2>(c, v, newP, val, idx);
@@ -497,7 +504,7 @@ __device__ __forceinline__ void scl_r1(Lane& c, const SclParams& p, int s, int s
     __syncwarp();
     const int newP = 4 * c.P < p.L ? 4 * c.P : p.L;
     int val, idx;
-    if (p.sort2)
+    if (Lane::kGG || p.sort2)
         scl_sort_packed2<4>(c, v, newP, val, idx);
     else
         scl_sort_packed<4>(c, v, newP, val, idx);
@@ -542,7 +549,7 @@ __device__ __forceinline__ void scl_spc(Lane& c, const SclParams& p, int s, int 
     __syncwarp();
     const int newP = 8 * c.P < p.L ? 8 * c.P : p.L;
     int val, idx;
-    if (p.sort2)
+    if (Lane::kGG || p.sort2)
         scl_sort_packed2<8>(c, v, newP, val, idx);
     else
         scl_sort_packed<8>(c, v, newP, val, idx);
@@ -559,10 +566,12 @@ __device__ __forceinline__ void scl_spc(Lane& c, const SclParams& p, int s, int 
     set_side(c, s, side);
 }
 
-template <int BM, int TT>
+// GG: lanes per group as a compile-time constant (0 = run-time p.G): the shuffle widths, the group-maximum tree of the
+// sorts and the lane arithmetic then fold
+template <int BM, int TT, int GG = 0>
 __global__ void __launch_bounds__(512, 1) k_scl_i8(const __grid_constant__ SclParams p)
 {
-    using Lane = LaneT<BM, TT>;
+    using Lane = LaneT<BM, TT, GG>;
     extern __shared__ __align__(16) uint32_t smem[];
     __shared__ uint32_t tm_base_s;
     const int T = blockDim.x, t = threadIdx.x, warp = t >> 5;
@@ -582,20 +591,22 @@ __global__ void __launch_bounds__(512, 1) k_scl_i8(const __grid_constant__ SclPa
     if (BM & BM_TMEM) asm volatile("tcgen05.fence::after_thread_sync;");
     Lane c;
     c.sm = smem + 256 + t;
+    c.sm32 = (uint32_t)__cvta_generic_to_shared(c.sm);
     c.ar = p.arena + ((size_t)blockIdx.x * T + t);
     c.AS = p.arena_stride;
     // a warp reaches the 32 tensor-memory lanes of its quarter (warp % 4); warps sharing a quarter are stacked along columns
     c.tm = (BM & BM_TMEM) ? tm_base_s + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)((warp >> 2) * p.tm_cols_thread) : 0u;
     c.T = T;
-    c.G = p.G;
-    c.l = t & (p.G - 1);
-    const int gpc = T / p.G; // codewords per CTA
+    const int G = GG ? GG : p.G;
+    c.G = G;
+    c.l = t & (G - 1);
+    const int gpc = T / G; // codewords per CTA
     const int N = 1 << p.S, kb = (p.K + 7) >> 3;
-    const unsigned gmask = (p.G == 32 ? 0xFFFFFFFFu : ((1u << p.G) - 1u)) << ((t & 31) & ~(p.G - 1));
+    const unsigned gmask = (G == 32 ? 0xFFFFFFFFu : ((1u << G) - 1u)) << ((t & 31) & ~(G - 1));
     const unsigned long long nfr = p.count ? *p.count : p.B;
     const unsigned long long nbatch = (nfr + gpc - 1) / gpc; // 0 when there is nothing to do: straight to the dealloc
     for (unsigned long long bi = blockIdx.x; bi < nbatch; bi += gridDim.x) {
-        const unsigned long long fl = bi * gpc + (unsigned long long)(t / p.G);
+        const unsigned long long fl = bi * gpc + (unsigned long long)(t / G);
         const bool live_frame = fl < nfr;
         unsigned long long f = live_frame ? fl : nfr - 1;
         if (p.frame_idx) f = p.frame_idx[f];
@@ -633,7 +644,7 @@ __global__ void __launch_bounds__(512, 1) k_scl_i8(const __grid_constant__ SclPa
             // 130 KB of SASS, and warps spread over the program (ncu r02_scl_i8_v0: `no_instruction` 5.3 cycles per
             // issue with 16 free-running warps) thrash the instruction caches; in step, a fetched line serves all warps.
             c.st_fence();
-            if (p.lockstep)
+            if (GG || p.lockstep)
                 __syncthreads();
             else
                 __syncwarp();
@@ -701,6 +712,8 @@ cudaError_t launch_scl_i8(const SclLaunch& L, const int8_t* d_llr, uint8_t* d_in
     const bool ba = (p.bitR_off[p.S] & kArena) != 0;
     void (*kern)(SclParams) = ba ? k_scl_i8<BM_ARENA, 0> : k_scl_i8<BM_SMEM, 0>;
     if (p.tm_alloc_cols) kern = L.threads == 512 ? k_scl_i8<BM_TMEM, 512> : (L.threads == 256 ? k_scl_i8<BM_TMEM, 256> : k_scl_i8<BM_TMEM, 0>);
+    if (p.tm_alloc_cols && L.threads == 512 && p.G == 8 && p.sort2 && p.lockstep == 1 && !getenv("PC_SCL_GRT"))
+        kern = k_scl_i8<BM_TMEM, 512, 8>; // the metric's L = 8 (5 ... 8): group size, sort form and lockstep fold at compile time
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes);
     // several CTAs per SM only fit when the L1/shared split is at its shared-memory maximum; a single CTA keeps the
     // default split (the rest stays L1 for the channel rows and the arena)
