@@ -674,7 +674,7 @@ __global__ void __launch_bounds__(TT ? TT : ((BM & BM_TMEM) ? 384 : 128), (TT ||
             // other lanes' buffers are read by the next step; `lockstep` keeps the CTA's warps on the same program step
             // (the kernel is ~90 KB of SASS; free-running warps thrash the instruction caches, see pc_scl_i8.cu)
             c.st_fence();
-            if (GG || p.lockstep)
+            if ((GG && (BM & BM_TMEM)) || p.lockstep)
                 __syncthreads();
             else
                 __syncwarp();
@@ -749,7 +749,12 @@ cudaError_t launch_scl_f32(const SclFLaunch& L, const float* d_llr, uint8_t* d_i
         default: kern = k_scl_f32<BM_TMEM, 0>; break;
         }
         // the metric's L = 8 (5 ... 8) at the default CTA size: group size and lockstep fold at compile time
-        if (L.threads == 384 && p.G == 8 && p.lockstep == 1 && !getenv("PC_SCL_GRT")) kern = k_scl_f32<BM_TMEM, 384, 8>;
+        if (L.threads == 384 && p.lockstep == 1 && !getenv("PC_SCL_GRT")) {
+            if (p.G == 8) kern = k_scl_f32<BM_TMEM, 384, 8>;
+            if (p.G == 32) kern = k_scl_f32<BM_TMEM, 384, 32>; // BASELINE config 4
+        }
+    } else if (!ba && p.G == 4 && !getenv("PC_SCL_GRT")) {
+        kern = k_scl_f32<BM_SMEM, 0, 4>; // BASELINE config 1: N = 64, L = 4 ('mixed' second pass)
     }
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes);
     // several CTAs per SM only fit when the L1/shared split is at its shared-memory maximum; a single CTA keeps the

@@ -474,7 +474,7 @@ __device__ __forceinline__ void scl_rep(Lane& c, const SclParams& p, int s, int 
     }
     const int newP = 2 * c.P < p.L ? 2 * c.P : p.L;
     int val, idx;
-    if (Lane::kGG || p.sort2)
+    if (Lane::kGG == 8 || p.sort2)
         scl_sort_packed2<2>(c, v, newP, val, idx);
     else
         scl_sort_packed<2>(c, v, newP, val, idx);
@@ -504,7 +504,7 @@ __device__ __forceinline__ void scl_r1(Lane& c, const SclParams& p, int s, int s
     __syncwarp();
     const int newP = 4 * c.P < p.L ? 4 * c.P : p.L;
     int val, idx;
-    if (Lane::kGG || p.sort2)
+    if (Lane::kGG == 8 || p.sort2)
         scl_sort_packed2<4>(c, v, newP, val, idx);
     else
         scl_sort_packed<4>(c, v, newP, val, idx);
@@ -549,7 +549,7 @@ __device__ __forceinline__ void scl_spc(Lane& c, const SclParams& p, int s, int 
     __syncwarp();
     const int newP = 8 * c.P < p.L ? 8 * c.P : p.L;
     int val, idx;
-    if (Lane::kGG || p.sort2)
+    if (Lane::kGG == 8 || p.sort2)
         scl_sort_packed2<8>(c, v, newP, val, idx);
     else
         scl_sort_packed<8>(c, v, newP, val, idx);
@@ -644,7 +644,7 @@ __global__ void __launch_bounds__(512, 1) k_scl_i8(const __grid_constant__ SclPa
             // 130 KB of SASS, and warps spread over the program (ncu r02_scl_i8_v0: `no_instruction` 5.3 cycles per
             // issue with 16 free-running warps) thrash the instruction caches; in step, a fetched line serves all warps.
             c.st_fence();
-            if (GG || p.lockstep)
+            if ((GG && (BM & BM_TMEM)) || p.lockstep)
                 __syncthreads();
             else
                 __syncwarp();
@@ -712,8 +712,12 @@ cudaError_t launch_scl_i8(const SclLaunch& L, const int8_t* d_llr, uint8_t* d_in
     const bool ba = (p.bitR_off[p.S] & kArena) != 0;
     void (*kern)(SclParams) = ba ? k_scl_i8<BM_ARENA, 0> : k_scl_i8<BM_SMEM, 0>;
     if (p.tm_alloc_cols) kern = L.threads == 512 ? k_scl_i8<BM_TMEM, 512> : (L.threads == 256 ? k_scl_i8<BM_TMEM, 256> : k_scl_i8<BM_TMEM, 0>);
-    if (p.tm_alloc_cols && L.threads == 512 && p.G == 8 && p.sort2 && p.lockstep == 1 && !getenv("PC_SCL_GRT"))
-        kern = k_scl_i8<BM_TMEM, 512, 8>; // the metric's L = 8 (5 ... 8): group size, sort form and lockstep fold at compile time
+    // group size (and with it sort form and lockstep) at compile time for the list sizes of the metric (L = 5 ... 8) and of
+    // BASELINE config 4 (L = 17 ... 32)
+    if (p.tm_alloc_cols && L.threads == 512 && p.lockstep == 1 && !getenv("PC_SCL_GRT")) {
+        if (p.G == 8 && p.sort2) kern = k_scl_i8<BM_TMEM, 512, 8>;
+        if (p.G == 32 && !p.sort2) kern = k_scl_i8<BM_TMEM, 512, 32>;
+    }
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes);
     // several CTAs per SM only fit when the L1/shared split is at its shared-memory maximum; a single CTA keeps the
     // default split (the rest stays L1 for the channel rows and the arena)
