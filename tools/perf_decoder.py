@@ -18,10 +18,11 @@ info = torch.empty((B, (K + 7) // 8), dtype=torch.uint8, device="cuda")
 Lb = pcb.capi.lib(); ptr = pcb.capi.ptr
 amp = 4.0 * 10 ** (ebn0 / 10) if (isf and kind != "amixed") else 10.0
 pcb.capi.check(Lb.pc_awgn_generate(dec._h, 1, 0, ebn0, amp, int(isf), ptr(llr), ptr(info), B, None))
-out, ok = dec.decode_batch(llr, return_ok=True)
+for _ in range(3):  # the first launches after a pause run 20-40 % slower (tools/launch_times.py)
+    out, ok = dec.decode_batch(llr, return_ok=True)
 torch.cuda.synchronize()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-reps = 5
+reps = 10
 e0.record()
 for _ in range(reps):
     out, ok = dec.decode_batch(llr, return_ok=True)
