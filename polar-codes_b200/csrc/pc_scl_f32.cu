@@ -749,6 +749,7 @@ cudaError_t launch_scl_f32(const SclFLaunch& L, const float* d_llr, uint8_t* d_i
         default: kern = k_scl_f32<BM_TMEM, 0>; break;
         }
         // the metric's L = 8 (5 ... 8) at the default CTA size: group size and lockstep fold at compile time
+        if (L.threads == 512 && p.G == 8 && p.lockstep == 1 && !getenv("PC_SCL_GRT")) kern = k_scl_f32<BM_TMEM, 512, 8>;
         if (L.threads == 384 && p.lockstep == 1 && !getenv("PC_SCL_GRT")) {
             if (p.G == 8) kern = k_scl_f32<BM_TMEM, 384, 8>;
             if (p.G == 32) kern = k_scl_f32<BM_TMEM, 384, 32>; // BASELINE config 4
@@ -905,9 +906,12 @@ int plan_scl_f32(int S, int K, int L, bool root_leaf, bool virt_ok, size_t smem_
     while (G < L) G <<= 1;
     // measured at N = 1024, L = 8 (profiles/r02_c4_perf.txt): T = 256 2.79 Gbit/s (58 MB arena, DRAM traffic 4.3x the
     // algorithmic bytes), 320 2.55, 384 3.32 (87 MB arena, 17x, still only 0.47 TB/s), 512 3.34 (stage 6 leaves shared memory)
-    int T = 384;
+    // with the quad arena layout and the group size at compile time (profiles/r02_c40_perf.txt): 384 lanes 4.35 Gbit/s, 512 lanes
+    // 4.38 (N = 512 K = 128: 2.81 / 3.02); the 512-lane form has a G = 8 instantiation only, other list sizes keep 384
+    int T = G == 8 ? 512 : 384;
     if (const char* e = getenv("PC_SCLF_T")) T = atoi(e);
     if (T < 32 || T > 512 || (T % 32) != 0 || (T % G) != 0) T = 384;
+    if (T > 384 && T != 512) T = 384; // the run-time-size instantiation is bounded at 384 threads
     const bool lockstep = getenv("PC_SCL_LOCKSTEP") ? atoi(getenv("PC_SCL_LOCKSTEP")) != 0 : true;
     bool virt = virt_ok && !root_leaf && S >= 7;
     if (const char* e = getenv("PC_SCLF_VIRT")) virt = virt && atoi(e) != 0;
