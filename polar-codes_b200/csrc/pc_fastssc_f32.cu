@@ -440,11 +440,28 @@ __global__ void __launch_bounds__(T, 1) k_fastssc_f32_sm(const __grid_constant__
             if (s <= top) {
                 fastssc_f32_step(cs, cs.sview(s), op, s, off);
             } else if (s == S) {
+                // the root is never a leaf here (plan_f32 keeps staged roots on the arena kernel): internal steps only,
+                // which spares this instance of the view the whole leaf zoo (a third of the kernel's code)
+                const RowView in{ row };
                 if (HAS_TM) {
-                    fastssc_f32_step(ct, RowView{ row }, op, s, off);
+                    switch (op) {
+                    case FOP_F: fop_f(ct, in, s); break;
+                    case FOP_G: fop_g(ct, in, s, off); break;
+                    case FOP_G0: fop_g0(ct, in, s); break;
+                    case FOP_G1: fop_g1(cs, in, s, off); break;
+                    case FOP_COMB: fop_comb(cs, s, off, false); break;
+                    default: fop_comb(cs, s, off, true); break;
+                    }
                     tm_wait_st();
                 } else {
-                    fastssc_f32_step(cs, RowView{ row }, op, s, off);
+                    switch (op) {
+                    case FOP_F: fop_f(cs, in, s); break;
+                    case FOP_G: fop_g(cs, in, s, off); break;
+                    case FOP_G0: fop_g0(cs, in, s); break;
+                    case FOP_G1: fop_g1(cs, in, s, off); break;
+                    case FOP_COMB: fop_comb(cs, s, off, false); break;
+                    default: fop_comb(cs, s, off, true); break;
+                    }
                 }
             } else if (HAS_TM) {
                 fastssc_f32_step(cs, TmView{ cs.tm }, op, s, off);
