@@ -752,6 +752,7 @@ cudaError_t launch_scl_f32(const SclFLaunch& L, const float* d_llr, uint8_t* d_i
         if (L.threads == 512 && p.G == 8 && p.lockstep == 1 && !getenv("PC_SCL_GRT")) kern = k_scl_f32<BM_TMEM, 512, 8>;
         if (L.threads == 384 && p.lockstep == 1 && !getenv("PC_SCL_GRT")) {
             if (p.G == 8) kern = k_scl_f32<BM_TMEM, 384, 8>;
+            if (p.G == 4) kern = k_scl_f32<BM_TMEM, 384, 4>;
             if (p.G == 32) kern = k_scl_f32<BM_TMEM, 384, 32>; // BASELINE config 4
         }
     } else if (!ba && p.G == 4 && !getenv("PC_SCL_GRT")) {

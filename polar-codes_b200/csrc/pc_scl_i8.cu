@@ -474,7 +474,7 @@ __device__ __forceinline__ void scl_rep(Lane& c, const SclParams& p, int s, int 
     }
     const int newP = 2 * c.P < p.L ? 2 * c.P : p.L;
     int val, idx;
-    if (Lane::kGG == 8 || p.sort2)
+    if ((Lane::kGG && Lane::kGG <= 8) || p.sort2)
         scl_sort_packed2<2>(c, v, newP, val, idx);
     else
         scl_sort_packed<2>(c, v, newP, val, idx);
@@ -504,7 +504,7 @@ __device__ __forceinline__ void scl_r1(Lane& c, const SclParams& p, int s, int s
     __syncwarp();
     const int newP = 4 * c.P < p.L ? 4 * c.P : p.L;
     int val, idx;
-    if (Lane::kGG == 8 || p.sort2)
+    if ((Lane::kGG && Lane::kGG <= 8) || p.sort2)
         scl_sort_packed2<4>(c, v, newP, val, idx);
     else
         scl_sort_packed<4>(c, v, newP, val, idx);
@@ -549,7 +549,7 @@ __device__ __forceinline__ void scl_spc(Lane& c, const SclParams& p, int s, int 
     __syncwarp();
     const int newP = 8 * c.P < p.L ? 8 * c.P : p.L;
     int val, idx;
-    if (Lane::kGG == 8 || p.sort2)
+    if ((Lane::kGG && Lane::kGG <= 8) || p.sort2)
         scl_sort_packed2<8>(c, v, newP, val, idx);
     else
         scl_sort_packed<8>(c, v, newP, val, idx);
@@ -716,6 +716,7 @@ cudaError_t launch_scl_i8(const SclLaunch& L, const int8_t* d_llr, uint8_t* d_in
     // BASELINE config 4 (L = 17 ... 32)
     if (p.tm_alloc_cols && L.threads == 512 && p.lockstep == 1 && !getenv("PC_SCL_GRT")) {
         if (p.G == 8 && p.sort2) kern = k_scl_i8<BM_TMEM, 512, 8>;
+        if (p.G == 4 && p.sort2) kern = k_scl_i8<BM_TMEM, 512, 4>; // pcsim's listlength sweep: L = 3, 4
         if (p.G == 32 && !p.sort2) kern = k_scl_i8<BM_TMEM, 512, 32>;
     }
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes);
