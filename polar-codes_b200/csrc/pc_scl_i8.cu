@@ -357,12 +357,30 @@ __device__ __forceinline__ void scl_find_weak(const Lane& c, int off, int n, int
         if (nw <= 256) {
             // first minimum of [i, n) as the minimum of 16-bit keys (|llr| << 8 | word index), one running minimum per
             // byte lane (VIMNMX.U16x2); excluded bytes are forced to 0xFF, above every |llr| <= 127
-            uint32_t me = 0xFFFFFFFFu, mo = 0xFFFFFFFFu;
-            for (int w = 0; w < nw; ++w) {
-                uint32_t x = v[w];
-                if (w == 0) x |= bytemask(i) | (n < 4 ? ~bytemask(n) : 0u);
-                me = __vminu2(me, __byte_perm(x, (uint32_t)w, 0x2404));
-                mo = __vminu2(mo, __byte_perm(x, (uint32_t)w, 0x3414));
+            // word 0 (the only one with excluded bytes) peeled, the rest four words per round (nw is a power of two)
+            const uint32_t x0 = v[0] | bytemask(i) | (n < 4 ? ~bytemask(n) : 0u);
+            uint32_t me = __byte_perm(x0, 0u, 0x2404), mo = __byte_perm(x0, 0u, 0x3414);
+            if (nw >= 4) {
+#pragma unroll
+                for (int u = 1; u < 4; ++u) {
+                    const uint32_t x = v[u];
+                    me = __vminu2(me, __byte_perm(x, (uint32_t)u, 0x2404));
+                    mo = __vminu2(mo, __byte_perm(x, (uint32_t)u, 0x3414));
+                }
+                for (int w = 4; w < nw; w += 4) {
+                    uint32_t x[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) x[u] = v[w + u];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        me = __vminu2(me, __byte_perm(x[u], (uint32_t)(w + u), 0x2404));
+                        mo = __vminu2(mo, __byte_perm(x[u], (uint32_t)(w + u), 0x3414));
+                    }
+                }
+            } else if (nw == 2) {
+                const uint32_t x = v[1];
+                me = __vminu2(me, __byte_perm(x, 1u, 0x2404));
+                mo = __vminu2(mo, __byte_perm(x, 1u, 0x3414));
             }
             uint32_t best = 0xFFFFFFFFu;
 #pragma unroll
