@@ -359,7 +359,9 @@ __device__ __forceinline__ void sclf_fg(FLane& c, const SclFParams& p, int s, co
         // UNR elements per step, all loads first (source and destination may alias as far as the compiler knows, so
         // a rolled loop serialises load -> f/g -> store; the big stages live in the L2 arena and want many loads in
         // flight); the channel row as 16-byte loads
-        if (h >= 8)
+        if (h >= 16 && src.mode == 0 && src.v.quad)
+            fg_block<IS_G, 16>(c, src, dst, active, h, lb, ol); // a stored arena stage: eight 16-byte loads in flight per lane
+        else if (h >= 8)
             fg_block<IS_G, 8>(c, src, dst, active, h, lb, ol);
         else
             fg_block<IS_G, 4>(c, src, dst, active, h, lb, ol);
