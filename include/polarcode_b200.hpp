@@ -17,9 +17,9 @@
 // Soft outputs: getSoftCodeword / getSoftInformation are served for the 'char' Fast-SSC decoder by a second kernel that
 // keeps the bit container as bytes (pc_fastssc_i8_soft.cu), the fp32 Fast-SSC one as float patterns (k_fastssc_f32_soft);
 // the list decoders' containers are not kept.
-// Not carried over: the BitContainer accessors (inputContainer / outputContainer), Encoder::setCodeword / setCharCodeword /
-// setFloatCodeword / clearFrozenBits (hooks the reference's own decoders use for non-systematic output; the kernels do
-// that step on the device), the 'scan' kind and CMAC detectors.
+// Encoder::setCodeword / setCharCodeword / setFloatCodeword / clearFrozenBits (the hooks the reference's own decoders use
+// for non-systematic output) are mirrored on top of a frozen-set-free code whose encoder is the bare polar transform.
+// Not carried over: the BitContainer accessors (inputContainer / outputContainer), the 'scan' kind and CMAC detectors.
 #ifndef POLARCODE_B200_HPP
 #define POLARCODE_B200_HPP
 #include <algorithm>
@@ -280,6 +280,33 @@ protected:
 public:
     pc_code* handle() const { return mCode; } ///< for direct C-ABI calls (streams, device buffers)
 };
+
+// a code of block length N without frozen bits, non-systematic, no detector: its encoder is the bare polar transform
+class XformHandle
+{
+    pc_code* mCode = nullptr;
+    size_t mN = 0;
+
+public:
+    XformHandle() {}
+    XformHandle(const XformHandle&) {}
+    XformHandle& operator=(const XformHandle&) { return *this; }
+    ~XformHandle()
+    {
+        if (mCode) pc_code_destroy(mCode);
+    }
+    pc_code* get(size_t N)
+    {
+        if (mCode && mN == N) return mCode;
+        if (mCode) pc_code_destroy(mCode);
+        mCode = pc_code_create((int)N, nullptr, 0, PC_DEC_FASTSSC_I8, 1);
+        if (!mCode) throw std::runtime_error(pc_last_error());
+        mN = N;
+        check(pc_code_set_crc(mCode, PC_CRC_NONE));
+        check(pc_code_set_systematic(mCode, 0));
+        return mCode;
+    }
+};
 } // namespace detail
 
 namespace Encoding {
@@ -357,6 +384,64 @@ public:
     }
     void getInformation(void* pData) { std::memcpy(pData, mInfoOut.data(), informationByteSize()); }
     void getEncodedData(void* pData) { std::memcpy(pData, mCodeword.data(), mBlockLength / 8); }
+
+    /// encoder.cpp:56-77: the "codeword ready" hooks the reference's decoders use for non-systematic output. The next
+    /// encode() skips detector and information scatter and transforms the N bits given here (x F^(x)n; systematic:
+    /// transform, clear the frozen positions, transform again -- butterfly_fip_packed.cpp:45-59).
+    /// setCodeword: N / 8 packed bytes (MSB first); setCharCodeword: N bytes whose MSB is the bit
+    /// (PackedContainer::insertCharBits bitcontainer.cpp:959-973); setFloatCodeword: N floats whose sign is the bit
+    /// (insertLlr :975-992). (For N < 256 the reference's insertCharBits writes to the wrong end of its 256-bit vector;
+    /// that defect is not reproduced: all three forms mean "bit i of the codeword" here.)
+    void setCodeword(void* pData)
+    {
+        xmInputData = static_cast<unsigned char*>(pData);
+        std::memcpy(mCodeword.data(), pData, mBlockLength / 8);
+        mCodewordReady = true;
+    }
+    void setCharCodeword(void* cData)
+    {
+        const unsigned char* in = static_cast<const unsigned char*>(cData);
+        for (size_t byte = 0; byte < mBlockLength / 8; ++byte) {
+            unsigned char b = 0;
+            for (unsigned bit = 0; bit < 8; ++bit) b |= (unsigned char)((in[byte * 8 + bit] & 0x80) >> bit);
+            mCodeword[byte] = b;
+        }
+        mCodewordReady = true;
+    }
+    void setFloatCodeword(void* fData)
+    {
+        const unsigned char* in = static_cast<const unsigned char*>(fData); // sign bit = MSB of byte 3 (little endian)
+        for (size_t byte = 0; byte < mBlockLength / 8; ++byte) {
+            unsigned char b = 0;
+            for (unsigned bit = 0; bit < 8; ++bit) b |= (unsigned char)((in[4 * (byte * 8 + bit) + 3] & 0x80) >> bit);
+            mCodeword[byte] = b;
+        }
+        mCodewordReady = true;
+    }
+    /// PackedContainer::resetFrozenBits (:1004-1010) on the held codeword
+    void clearFrozenBits()
+    {
+        for (unsigned f : mFrozenBits) mCodeword[f >> 3] &= (unsigned char)~(0x80u >> (f & 7));
+    }
+
+protected:
+    // x -> x F^(x)n of the held codeword on the device: a non-systematic encode of a code without frozen bits
+    detail::XformHandle mXform;
+    void transformHeld()
+    {
+        std::vector<unsigned char> out(mBlockLength / 8 + 1);
+        detail::check(pc_encode_batch_host(mXform.get(mBlockLength), mCodeword.data(), out.data(), nullptr, 1));
+        std::memcpy(mCodeword.data(), out.data(), mBlockLength / 8);
+    }
+    void encodeHeld()
+    {
+        transformHeld();
+        if (mSystematic) {
+            clearFrozenBits();
+            transformHeld();
+        }
+        mCodewordReady = false;
+    }
 };
 
 // butterfly_fip_packed.h:25-49
@@ -379,6 +464,7 @@ public:
     /// (:47-49); this does the same so that a caller that reads them back keeps working.
     void encode()
     {
+        if (mCodewordReady) return encodeHeld();
         if (!xmInputData) throw std::logic_error("ButterflyFipPacked::encode(): no information set");
         detail::check(pc_encode_batch_host(mCode, xmInputData, mCodeword.data(), mInfoOut.data(), 1));
         std::memcpy(xmInputData, mInfoOut.data(), informationByteSize());

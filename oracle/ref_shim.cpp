@@ -177,6 +177,29 @@ int ref_decode_soft_f32(int N, const unsigned* frozen, int nf, int systematic, c
     }
 }
 
+// Encoder::setCodeword / setCharCodeword / setFloatCodeword (+ clearFrozenBits), encode(), getEncodedData (encoder.cpp:56-77).
+// form 0 packed bytes, 1 chars, 2 floats. Returns 0 or -1.
+int ref_encode_codeword(int N, const unsigned* frozen, int nf, int systematic, int form, int clear, void* in, unsigned char* out)
+{
+    try {
+        auto fz = mkfrozen(frozen, nf);
+        Encoding::ButterflyFipPacked enc(N, fz);
+        enc.setSystematic(systematic != 0);
+        if (form == 0)
+            enc.setCodeword(in);
+        else if (form == 1)
+            enc.setCharCodeword(in);
+        else
+            enc.setFloatCodeword(in);
+        if (clear) enc.clearFrozenBits();
+        enc.encode();
+        enc.getEncodedData(out);
+        return 0;
+    } catch (...) {
+        return -1;
+    }
+}
+
 // info: uint8[B][ceil(K/8)] (a private copy is made per frame because encode() writes the CRC in place,
 // butterfly_fip_packed.cpp:47-49; the copy incl. CRC is returned through info_out when non-null).
 double ref_encode_batch(int N, const unsigned* frozen, int nf, int crc_bits, const char* crc_type,

@@ -133,6 +133,26 @@ int cxx_soft(int N, int L, const unsigned* frozen, int nf, const char* kind, int
     });
 }
 
+// Encoder::setCodeword / setCharCodeword / setFloatCodeword (+ clearFrozenBits) followed by encode() and getEncodedData:
+// form 0 packed bytes, 1 chars (MSB = bit), 2 floats (sign = bit); `clear` calls clearFrozenBits() before encode()
+int cxx_encode_codeword(int N, const unsigned* frozen, int nf, int systematic, int form, int clear, void* in, unsigned char* out)
+{
+    return guarded([&] {
+        std::vector<unsigned> fz(frozen, frozen + nf);
+        Encoding::ButterflyFipPacked enc((size_t)N, fz);
+        enc.setSystematic(systematic != 0);
+        if (form == 0)
+            enc.setCodeword(in);
+        else if (form == 1)
+            enc.setCharCodeword(in);
+        else
+            enc.setFloatCodeword(in);
+        if (clear) enc.clearFrozenBits();
+        enc.encode();
+        enc.getEncodedData(out);
+    });
+}
+
 int cxx_puncturer(long blockLength, const unsigned* frozen, int nf, unsigned* positions, long* parent, const float* in,
                   float* punctured, const unsigned char* packed_in, unsigned char* packed_out, float* depunctured)
 {

@@ -162,3 +162,29 @@ def test_cxx_soft_getters_match_reference(cxx, ref):
     ebc, ebi = ref.decode_soft(N, fz, q)
     assert np.array_equal(bc, ebc) and np.array_equal(bi, ebi)
     assert cxx.cxx_soft(N, 4, _p(fz), len(fz), b"char", 0, _p(q), ctypes.c_long(1), _p(bc), _p(bi), 1) == 2
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("N,K", [(256, 128), (1024, 512), (2048, 1500)])
+def test_cxx_encoder_codeword_hooks_match_reference(cxx, ref, N, K):
+    """Encoder::setCodeword / setCharCodeword / setFloatCodeword / clearFrozenBits (encoder.cpp:56-77) + encode():
+    the transform of a ready codeword, both modes, against the unmodified reference (N >= 256: below that the
+    reference's insertCharBits misplaces the bits in its 256-bit vector)"""
+    import refshim
+    L = refshim.lib()
+    L.ref_encode_codeword.restype = ctypes.c_int
+    L.ref_encode_codeword.argtypes = [ctypes.c_int, VP, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, VP, VP]
+    fz = np.ascontiguousarray(ref.frozen_bits(N, K, 0.0), dtype=np.uint32)
+    rng = np.random.default_rng(N)
+    bits = rng.integers(0, 2, N, dtype=np.uint8)
+    packed = np.packbits(bits, bitorder="big")
+    chars = np.where(bits == 1, rng.integers(-128, 0, N), rng.integers(0, 128, N)).astype(np.int8)
+    floats = np.where(bits == 1, -1.0, 1.0).astype(np.float32) * rng.uniform(0.1, 5.0, N).astype(np.float32)
+    for syst in (0, 1):
+        for clear in (0, 1):
+            for form, arr in ((0, packed), (1, chars), (2, floats)):
+                got, exp = np.zeros(N // 8, np.uint8), np.zeros(N // 8, np.uint8)
+                a1, a2 = arr.copy(), arr.copy()
+                assert cxx.cxx_encode_codeword(N, _p(fz), len(fz), syst, form, clear, _p(a1), _p(got)) == 0
+                assert L.ref_encode_codeword(N, _p(fz), len(fz), syst, form, clear, _p(a2), _p(exp)) == 0
+                assert np.array_equal(got, exp), (N, K, syst, clear, form)
