@@ -48,7 +48,7 @@ KINDS = {
                "char", 8, 16, False, 1 << 16),
     "scl_f32": ("decoded info Gbit/s, N=1024 K=512 CRC-SCL L=8 fp32",
                 "metric's 2nd half: N=1024 K=512 CRC-16 SCL L=8 fp32 'float', BB dSNR 0, BPSK/AWGN 2 dB, LLR = 4 Eb/N0 y",
-                "float", 8, 16, True, 1 << 15),
+                "float", 8, 16, True, 1 << 16),  # 6.9 waves of 148 x 64 frames (2^15 = 3.5 waves leaves the fourth round 46 % full)
 }
 
 
@@ -433,11 +433,11 @@ def main():
                     "frames_per_gpu_per_step": frames, "steps": reps,
                     "bler": float((o != tx).any(dim=1).float().mean().item())}
         secondary = {
-            "adaptive_l8_fp32_crc16": plain("mixed", 8, 16, 1 << 17, True),
+            "adaptive_l8_fp32_crc16": plain("mixed", 8, 16, 1 << 18, True),
             # pcsim's L > 1 decoders at precision 8 / 832 (simulator.cpp:721-733): Fast-SSC int8, failures to the list kernel
             "adaptive_l8_int8_crc16": plain(capi.PC_DEC_ADAPTIVE_I8, 8, 16, 1 << 18, False),
-            "adaptive_l8_int8_fp32_crc16": plain(capi.PC_DEC_ADAPTIVE_MIXED, 8, 16, 1 << 17, True),
-            "fastssc_fp32_crc8": plain("float", 1, 8, 1 << 17, True),
+            "adaptive_l8_int8_fp32_crc16": plain(capi.PC_DEC_ADAPTIVE_MIXED, 8, 16, 1 << 18, True),
+            "fastssc_fp32_crc8": plain("float", 1, 8, 1 << 18, True),
         }
 
     if rank == 0:

@@ -1,10 +1,6 @@
 set -x
 mkdir -p gpurun_out
-P="timeout 200 python tools/perf_decoder.py"
-{
-for k in 1 2 3 4 8 16; do
-echo "== lockstep period $k"
-PC_SCL_LOCKSTEP=$k $P 1024 512 8 char 16 65536 2.0 | tail -1
-PC_SCL_LOCKSTEP=$k $P 1024 512 8 float 16 32768 2.0 | tail -1
-done
-} > gpurun_out/r02_c21_lockstep.log 2>&1
+python bench.py --steps 20 --warmup 3 > gpurun_out/r02_bench_v6.json 2> gpurun_out/bench_err.log
+python bench.py --impl reference --steps 5 --warmup 1 > gpurun_out/r02_bench_ref_v6.json 2> gpurun_out/bench_ref_err.log
+python bench.py --kind scl_f32 --steps 20 --warmup 3 --no-secondary > gpurun_out/r02_bench_sclf32_v1.json 2>> gpurun_out/bench_err.log
+python bench.py --kind scl_i8 --steps 20 --warmup 3 --no-secondary > gpurun_out/r02_bench_scli8_v1.json 2>> gpurun_out/bench_err.log

@@ -4,7 +4,7 @@ P="python tools/perf_decoder.py"
 $P 1024 512 1 char 8 1048576 2.0
 $P 1024 512 1 float 8 262144 2.0
 $P 1024 512 8 char 16 65536 2.0
-$P 1024 512 8 float 16 32768 2.0
+$P 1024 512 8 float 16 65536 2.0
 $P 1024 512 8 mixed 16 262144 2.0
 $P 1024 512 8 achar 16 262144 2.0
 $P 1024 512 8 amixed 16 262144 2.0
