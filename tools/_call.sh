@@ -1,6 +1,8 @@
+# the round's standard GPU validation call (run on the GPU box through gpurun): tests, both bench arms, launch list
 set -x
 mkdir -p gpurun_out
-python bench.py --steps 20 --warmup 3 > gpurun_out/r02_bench_v6.json 2> gpurun_out/bench_err.log
-python bench.py --impl reference --steps 5 --warmup 1 > gpurun_out/r02_bench_ref_v6.json 2> gpurun_out/bench_ref_err.log
-python bench.py --kind scl_f32 --steps 20 --warmup 3 --no-secondary > gpurun_out/r02_bench_sclf32_v1.json 2>> gpurun_out/bench_err.log
-python bench.py --kind scl_i8 --steps 20 --warmup 3 --no-secondary > gpurun_out/r02_bench_scli8_v1.json 2>> gpurun_out/bench_err.log
+timeout 1800 python -m pytest tests -m gpu -x -q > gpurun_out/tests.log 2>&1; echo "tests rc=$?" >> gpurun_out/tests.log
+python bench.py --impl reference --steps 5 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref_err.log
+python bench.py --steps 20 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench_err.log
+ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 1 > gpurun_out/ncu_bench.log 2>&1
+python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/smoke.log 2>&1
