@@ -435,7 +435,7 @@ def main():
         secondary = {
             "adaptive_l8_fp32_crc16": plain("mixed", 8, 16, 1 << 18, True),
             # pcsim's L > 1 decoders at precision 8 / 832 (simulator.cpp:721-733): Fast-SSC int8, failures to the list kernel
-            "adaptive_l8_int8_crc16": plain(capi.PC_DEC_ADAPTIVE_I8, 8, 16, 1 << 18, False),
+            "adaptive_l8_int8_crc16": plain(capi.PC_DEC_ADAPTIVE_I8, 8, 16, 1 << 20, False),  # 6.9 waves of the first pass
             "adaptive_l8_int8_fp32_crc16": plain(capi.PC_DEC_ADAPTIVE_MIXED, 8, 16, 1 << 18, True),
             "fastssc_fp32_crc8": plain("float", 1, 8, 1 << 18, True),
         }
