@@ -271,7 +271,7 @@ __device__ __forceinline__ uint32_t sm_quad_off(int s) { return s < 2 ? (uint32_
 
 template <int T, bool QUAD>
 struct SmView { // a stage in shared memory (QUAD: the quad layout above; else element i of a thread at byte 4 T i)
-    static constexpr int kBatch = 8;
+    static constexpr int kBatch = 16;
     uint32_t a; // shared address of this thread's element 0 of the stage
     __device__ __forceinline__ float operator[](int i) const
     {
@@ -292,7 +292,7 @@ struct SmView { // a stage in shared memory (QUAD: the quad layout above; else e
     __device__ __forceinline__ void wait() const {}
 };
 struct TmView { // stage S-1 in tensor memory
-    static constexpr int kBatch = 16;
+    static constexpr int kBatch = 32;
     uint32_t t; // tensor-memory address of this warp's lane quarter, column of element 0
     __device__ __forceinline__ float operator[](int i) const
     {
