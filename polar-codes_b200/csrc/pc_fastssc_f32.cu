@@ -388,8 +388,8 @@ struct SmCtx {
 
 // HAS_TM: stage S-1 lives in tensor memory (p.sm_top == S - 2); else every stage is in shared memory (p.sm_top == S - 1)
 // QUAD: quad layout of the shared-memory stages. Measured (profiles/r02_c24_perf.txt): N = 256 68.2 -> 78.8 Gbit/s,
-// N = 128 80.6 -> 91.4, N = 64 77.8 -> 87.5; N = 512 (45.2 against 42.8 ... 48.5) and N = 1024 with stage S-1 in tensor
-// memory (48.0 against 46.2 ... 49.3) move inside their run-to-run spread; the tensor-memory plan keeps the plain layout.
+// N = 128 80.6 -> 91.4, N = 64 77.8 -> 87.5; with the 16-element rounds also N = 1024 next to the tensor-memory stage
+// (51.9 -> 53.3, profiles/r02_c66_perf.txt), so every plan uses it (PC_F32_SM_QUAD=0 selects the plain layout).
 template <int T, bool HAS_TM, bool QUAD>
 __global__ void __launch_bounds__(T, 1) k_fastssc_f32_sm(const __grid_constant__ F32Params p)
 {
